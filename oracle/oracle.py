@@ -1,0 +1,226 @@
+"""oracle/oracle.py -- TEST INFRASTRUCTURE, not product code.
+
+ctypes front end of oracle/_build/liboracle.so (stencil_oracle.c + decomp_oracle.c) plus the
+numpy restatement of the halo exchange and of the process-grid helpers.  It is the checker
+for the CUDA path.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may
+import it; the product (bricklib_b200/) never does.
+
+PINNED against the compiled reference: see tests/test_oracle_golden.py + oracle/gen_golden.py.
+
+Exchange restated from include/brick-mpi.h:466-495 (BrickDecomp::exchange): for every region
+i, rank r receives (ghost[i].len - pads)*step elements at dat[(ghost[i].pos+first_pad)*step]
+from rank_map_r[ghost[i].neighbor]; that peer sends the same count from
+dat[(skin[i].pos+first_pad)*step] (tag i pairs them).  Process grid from weak/args.cpp:105-115
+(MPI_Dims_create + periodic MPI_Cart_create; ranks row-major per the MPI standard).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIBPATH = os.path.join(HERE, "_build", "liboracle.so")
+
+SKIN3D_GOOD = [  # src/brick-mpi.cpp:25-52
+    (1,), (1, -3), (1, 2, -3), (1, 2), (1, 2, 3), (2, 3), (2,), (2, -3), (-1, 2, -3), (-1, 2),
+    (-1, 2, 3), (-1, 3), (-1,), (-3,), (-1, -3), (-1, -2, -3), (-1, -2), (-1, -2, 3), (-2, 3),
+    (-2,), (-2, -3), (1, -2, -3), (1, -2), (1, -2, 3), (1, 3), (3,)]
+
+
+def bitset(elems):
+    s = 0
+    for d in elems:
+        s ^= 1 << (31 - d if d < 0 else d)
+    return s
+
+
+def bitset_neg(s):
+    return ((s & ((1 << 32) - 1)) << 31) | (s >> 31)
+
+
+class _Region(C.Structure):
+    _fields_ = [("neighbor", C.c_uint64), ("skin_st", C.c_uint), ("skin_ed", C.c_uint),
+                ("pos", C.c_uint), ("len", C.c_uint), ("first_pad", C.c_uint), ("last_pad", C.c_uint)]
+
+
+_REGION_DT = np.dtype([("neighbor", np.uint64), ("skin_st", np.uint32), ("skin_ed", np.uint32),
+                       ("pos", np.uint32), ("len", np.uint32), ("first_pad", np.uint32),
+                       ("last_pad", np.uint32)], align=True)
+
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", HERE, "oracle"])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIBPATH):
+            build()
+        L = C.CDLL(LIBPATH)
+        vp, u32p, f64p = C.c_void_p, C.POINTER(C.c_uint), C.POINTER(C.c_double)
+        L.oracle_points.restype = C.c_int
+        L.oracle_points.argtypes = [C.c_int, vp, vp, vp]
+        L.oracle_brick_sweep.restype = C.c_int
+        L.oracle_brick_sweep.argtypes = [C.c_int, vp, vp, C.c_long, vp, C.c_long, vp, C.c_long, vp]
+        L.oracle_array_sweep.restype = C.c_int
+        L.oracle_array_sweep.argtypes = [C.c_int, vp, vp] + [C.c_long] * 9 + [vp]
+        L.oracle_copy_brick.argtypes = [C.c_int, vp, vp, vp, vp, vp, vp, C.c_long]
+        L.oracle_decomp_build.restype = vp
+        L.oracle_decomp_build.argtypes = [vp, C.c_uint, vp, C.c_int, C.c_int, C.c_long, C.c_long]
+        L.oracle_decomp_free.argtypes = [vp]
+        L.oracle_decomp_nbricks.restype = C.c_uint
+        L.oracle_decomp_nbricks.argtypes = [vp]
+        L.oracle_decomp_nregions.restype = C.c_int
+        L.oracle_decomp_nregions.argtypes = [vp]
+        L.oracle_decomp_get.argtypes = [vp] * 7
+        L.oracle_rank_map.argtypes = [vp] * 4
+        L.oracle_init_grid.argtypes = [vp] * 3
+        L.oracle_allneighbors.restype = C.c_int
+        L.oracle_allneighbors.argtypes = [vp]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def points(which, coeff=None):
+    off = np.zeros((125, 3), np.int32)
+    c = np.zeros(125, np.float64)
+    cin = None if coeff is None else np.ascontiguousarray(coeff, np.float64)
+    n = lib().oracle_points(which, _p(cin), _p(off), _p(c))
+    if n < 0:
+        raise ValueError("unknown stencil %r" % (which,))
+    return off[:n].copy(), c[:n].copy()
+
+
+def brick_sweep(which, adj, blist, inp, out, in_step=512, out_step=512, coeff=None):
+    """out[b] = stencil(inp) for b in blist; inp/out are 1-D float64 views starting at the
+    field offset (row-major 8x8x8 bricks)."""
+    adj = np.ascontiguousarray(adj, np.uint32)
+    blist = np.ascontiguousarray(blist, np.uint32)
+    cin = None if coeff is None else np.ascontiguousarray(coeff, np.float64)
+    assert inp.dtype == np.float64 and out.dtype == np.float64
+    r = lib().oracle_brick_sweep(which, _p(adj), _p(blist), blist.size, _p(inp), in_step, _p(out),
+                                 out_step, _p(cin))
+    if r:
+        raise ValueError("unknown stencil %r" % (which,))
+    return out
+
+
+def array_sweep(which, inp, out, box, coeff=None):
+    s2, s1, s0 = inp.shape
+    cin = None if coeff is None else np.ascontiguousarray(coeff, np.float64)
+    r = lib().oracle_array_sweep(which, _p(inp), _p(out), s0, s1, s2, *[int(x) for x in box], _p(cin))
+    if r:
+        raise ValueError("unknown stencil %r" % (which,))
+    return out
+
+
+def copy_brick(to_brick, dim, pad, ghost, arr, grid, bdat, step=512):
+    d, p, g = (np.asarray(x, np.int64) for x in (dim, pad, ghost))
+    grid = np.ascontiguousarray(grid, np.uint32)
+    lib().oracle_copy_brick(1 if to_brick else 0, _p(d), _p(p), _p(g), _p(arr), _p(grid), _p(bdat), step)
+
+
+def init_grid(dimlist):
+    d = np.asarray(dimlist, np.int64)
+    n = int(d[0] * d[1] * d[2])
+    grid = np.zeros(n, np.uint32)
+    adj = np.zeros((n, 27), np.uint32)
+    lib().oracle_init_grid(_p(d), _p(grid), _p(adj))
+    return grid.reshape(int(d[2]), int(d[1]), int(d[0])), adj
+
+
+def allneighbors():
+    out = np.zeros(27, np.uint64)
+    lib().oracle_allneighbors(_p(out))
+    return [int(x) for x in out]
+
+
+class Decomp(object):
+    """Restated BrickDecomp<3,8,8,8>(dims, depth).initialize(skinlist)."""
+
+    def __init__(self, dims, depth=8, skinlist=None, page_align=False, pagesize=4096, brick_bytes=4096):
+        L = lib()
+        skinlist = SKIN3D_GOOD if skinlist is None else skinlist
+        sk = np.array([bitset(s) if not isinstance(s, int) else s for s in skinlist], np.uint64)
+        d = np.asarray(dims, np.uint32)
+        h = L.oracle_decomp_build(_p(d), depth, _p(sk), len(sk), int(page_align), pagesize, brick_bytes)
+        self.dims = tuple(int(x) for x in dims)
+        self.depth = depth
+        self.skinlist = [int(x) for x in sk]
+        self.nbricks = L.oracle_decomp_nbricks(h)
+        nr = L.oracle_decomp_nregions(h)
+        t = [x // 8 + 2 * (depth // 8) for x in self.dims]
+        self.tdims = t
+        self.sep_pos = np.zeros(3, np.uint32)
+        grid = np.zeros(t[0] * t[1] * t[2], np.uint32)
+        self.adj = np.zeros((self.nbricks, 27), np.uint32)
+        ghost = np.zeros(nr, _REGION_DT)
+        skin = np.zeros(nr, _REGION_DT)
+        assert _REGION_DT.itemsize == C.sizeof(_Region)
+        self.skin_size = np.zeros(len(sk), np.int64)
+        L.oracle_decomp_get(h, _p(self.sep_pos), _p(grid), _p(self.adj), _p(ghost), _p(skin),
+                            _p(self.skin_size))
+        L.oracle_decomp_free(h)
+        self.grid = grid.reshape(t[2], t[1], t[0])
+        self.ghost = ghost
+        self.skin = skin
+
+    def regions(self, name):
+        r = self.ghost if name == "ghost" else self.skin
+        return {k: r[k].copy() for k in r.dtype.names}
+
+
+def rank_map(procdims, coo):
+    keys = np.zeros(27, np.uint64)
+    ranks = np.zeros(27, np.int32)
+    pd, cc = np.asarray(procdims, np.int32), np.asarray(coo, np.int32)
+    lib().oracle_rank_map(_p(pd), _p(cc), _p(keys), _p(ranks))
+    return {int(k): int(r) for k, r in zip(keys, ranks)}
+
+
+def dims_create(nnodes, ndims=3):
+    """MPI_Dims_create(nnodes, ndims, {0..}): balanced factors, non-increasing
+    (8 -> 2x2x2, 4 -> 2x2x1, 2 -> 2x1x1, 6 -> 3x2x1, 1 -> 1x1x1)."""
+    primes, n, p = [], nnodes, 2
+    while n > 1:
+        while n % p == 0:
+            primes.append(p)
+            n //= p
+        p += 1
+    dims = [1] * ndims
+    for f in sorted(primes, reverse=True):
+        dims[dims.index(min(dims))] *= f
+    return sorted(dims, reverse=True)
+
+
+def cart_coords(rank, procdims):
+    coo = []
+    for n in reversed(procdims):
+        coo.append(rank % n)
+        rank //= n
+    return list(reversed(coo))
+
+
+def exchange(storages, dec, procdims, step=512):
+    """In-place emulation of BrickDecomp::exchange on P virtual ranks (row-major ranks on a
+    periodic procdims grid).  storages[r] is rank r's 1-D float64 brick storage."""
+    P = len(storages)
+    snap = [s.copy() for s in storages]  # MPI semantics: every send buffer is the pre-exchange skin
+    for r in range(P):
+        rm = rank_map(procdims, cart_coords(r, procdims))
+        for i in range(len(dec.ghost)):
+            g, s = dec.ghost[i], dec.skin[i]
+            src = rm[int(g["neighbor"])]
+            n = (int(g["len"]) - int(g["first_pad"]) - int(g["last_pad"])) * step
+            d0 = (int(g["pos"]) + int(g["first_pad"])) * step
+            s0 = (int(s["pos"]) + int(s["first_pad"])) * step
+            storages[r][d0:d0 + n] = snap[src][s0:s0 + n]
+    return storages
