@@ -1,0 +1,291 @@
+"""ctypes binding of the C ABI in include/bricks_b200.h (libbricks_b200.so).
+
+This is the only way Python reaches the CUDA path: there is no CPU fallback.  Loading fails
+loudly when the library has not been built (__graft_entry__.build()).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIBPATH = os.path.join(HERE, "lib", "libbricks_b200.so")
+
+ST_7PT_COEFF, ST_7PT, ST_13PT, ST_25PT, ST_125PT = 0, 7, 13, 25, 125
+STREAM_COMPUTE, STREAM_COMM = 0, 1
+#: ghost-zone sweeps per exchange, stencils/fake.h:39-344 (ST_ITER) -- GZ / radius
+ST_ITER = {ST_7PT: 8, ST_13PT: 4, ST_25PT: 2, ST_125PT: 4, ST_7PT_COEFF: 8}
+RADIUS = {ST_7PT: 1, ST_13PT: 2, ST_25PT: 4, ST_125PT: 2, ST_7PT_COEFF: 1}
+
+
+class BricksError(RuntimeError):
+    pass
+
+
+class RegionLink(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("len", C.c_size_t)]
+
+
+_lib = None
+
+_vp, _vpp = C.c_void_p, C.POINTER(C.c_void_p)
+_SIGS = {
+    "bricks_last_error": (C.c_char_p, []),
+    "bricks_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "bricks_ctx_create": (C.c_int, [C.c_int, _vpp]),
+    "bricks_ctx_destroy": (C.c_int, [_vp]),
+    "bricks_ctx_device": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "bricks_malloc": (C.c_int, [_vp, _vpp, C.c_size_t]),
+    "bricks_free": (C.c_int, [_vp, _vp]),
+    "bricks_memset": (C.c_int, [_vp, _vp, C.c_int, C.c_size_t]),
+    "bricks_host_alloc": (C.c_int, [_vpp, C.c_size_t]),
+    "bricks_host_free": (C.c_int, [_vp]),
+    "bricks_h2d": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
+    "bricks_d2h": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
+    "bricks_d2d": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
+    "bricks_sync": (C.c_int, [_vp, C.c_int]),
+    "bricks_stream_wait": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "bricks_stream_handle": (C.c_int, [_vp, C.c_int, _vpp]),
+    "bricks_timer_start": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "bricks_timer_stop": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "bricks_timer_elapsed_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
+    "bricks_plan_create": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint, C.c_int, _vp, _vpp]),
+    "bricks_plan_destroy": (C.c_int, [_vp]),
+    "bricks_plan_device_tables": (C.c_int, [_vp, _vpp, _vpp]),
+    "bricks_stencil": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
+    "bricks_stencil_naive": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
+    "bricks_launch_count": (C.c_int, [C.POINTER(C.c_ulonglong)]),
+    "bricks_links_upload": (C.c_int, [_vp, _vp, C.c_int, _vpp]),
+    "bricks_copy_regions": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "bricks_comm_unique_id": (C.c_int, [_vp]),
+    "bricks_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "bricks_comm_destroy": (C.c_int, [_vp]),
+    "bricks_exchange_create": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vpp]),
+    "bricks_exchange_destroy": (C.c_int, [_vp]),
+    "bricks_exchange_run": (C.c_int, [_vp, _vp, C.c_int]),
+    # include/bricks_b200_probe.h
+    "bricks_probe_dfma": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
+    "bricks_probe_copy": (C.c_int, [_vp, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
+    "bricks_probe_read": (C.c_int, [_vp, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
+    "bricks_probe_mio": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "bricks_probe_tma_image": (C.c_int, [_vp, _vp, C.c_uint, C.c_size_t, C.c_uint, _vp]),
+}
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIBPATH):
+            raise BricksError("libbricks_b200.so is not built (run __graft_entry__.build()); "
+                              "there is no CPU fallback")
+        L = C.CDLL(LIBPATH, mode=C.RTLD_GLOBAL)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise BricksError("bricks_b200 error %d: %s" % (rc, lib().bricks_last_error().decode()))
+
+
+def _np_ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Context(object):
+    """One device.  Mirrors the role of the gpu* macros of include/brick-cuda.h."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        check(lib().bricks_ctx_create(device, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib().bricks_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    # memory -----------------------------------------------------------------
+    def malloc(self, nbytes):
+        p = C.c_void_p()
+        check(lib().bricks_malloc(self._h, C.byref(p), nbytes))
+        return p.value
+
+    def free(self, dptr):
+        check(lib().bricks_free(self._h, C.c_void_p(dptr)))
+
+    def memset(self, dptr, value, nbytes):
+        check(lib().bricks_memset(self._h, C.c_void_p(dptr), value, nbytes))
+
+    def h2d(self, dptr, host, stream=STREAM_COMPUTE, nbytes=None):
+        host = np.ascontiguousarray(host)
+        check(lib().bricks_h2d(self._h, C.c_void_p(dptr), _np_ptr(host), host.nbytes if nbytes is None else nbytes, stream))
+        return host
+
+    def d2h(self, host, dptr, stream=STREAM_COMPUTE, nbytes=None):
+        assert host.flags["C_CONTIGUOUS"]
+        check(lib().bricks_d2h(self._h, _np_ptr(host), C.c_void_p(dptr), host.nbytes if nbytes is None else nbytes, stream))
+        return host
+
+    def d2d(self, dst, src, nbytes, stream=STREAM_COMPUTE):
+        check(lib().bricks_d2d(self._h, C.c_void_p(dst), C.c_void_p(src), nbytes, stream))
+
+    def upload(self, host):
+        """movBrickStorage / copyToDevice: allocate + copy, synchronous."""
+        host = np.ascontiguousarray(host)
+        d = self.malloc(host.nbytes)
+        self.h2d(d, host)
+        self.sync()
+        return d
+
+    def download(self, dptr, shape, dtype=np.float64):
+        out = np.empty(shape, dtype)
+        self.d2h(out, dptr)
+        self.sync()
+        return out
+
+    def sync(self, stream=-1):
+        check(lib().bricks_sync(self._h, stream))
+
+    def stream_wait(self, stream, other):
+        check(lib().bricks_stream_wait(self._h, stream, other))
+
+    def stream_handle(self, stream):
+        p = C.c_void_p()
+        check(lib().bricks_stream_handle(self._h, stream, C.byref(p)))
+        return p.value
+
+    # timers -----------------------------------------------------------------
+    def timer_start(self, slot=0, stream=STREAM_COMPUTE):
+        check(lib().bricks_timer_start(self._h, stream, slot))
+
+    def timer_stop(self, slot=0, stream=STREAM_COMPUTE):
+        check(lib().bricks_timer_stop(self._h, stream, slot))
+
+    def timer_ms(self, slot=0):
+        ms = C.c_float()
+        check(lib().bricks_timer_elapsed_ms(self._h, slot, C.byref(ms)))
+        return ms.value
+
+    # NCCL -------------------------------------------------------------------
+    def comm_init(self, rank, nranks, unique_id):
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        check(lib().bricks_comm_init(self._h, rank, nranks, buf))
+
+
+def unique_id():
+    buf = C.create_string_buffer(128)
+    check(lib().bricks_comm_unique_id(buf))
+    return buf.raw
+
+
+def launch_count():
+    n = C.c_ulonglong()
+    check(lib().bricks_launch_count(C.byref(n)))
+    return n.value
+
+
+class Plan(object):
+    """Launch plan over boxes of the brick grid (bricks_plan_create)."""
+
+    def __init__(self, ctx, grid, adj, boxes=None):
+        grid = np.ascontiguousarray(grid, np.uint32)
+        adj = np.ascontiguousarray(adj, np.uint32)
+        assert grid.ndim == 3 and adj.ndim == 2 and adj.shape[1] == 27
+        gd = np.array([grid.shape[2], grid.shape[1], grid.shape[0]], np.uint32)
+        if boxes is None:
+            boxes = [((0, 0, 0), tuple(int(x) for x in gd))]
+        bx = np.array([list(lo) + list(hi) for lo, hi in boxes], np.uint32)
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        check(lib().bricks_plan_create(ctx._h, _np_ptr(grid), _np_ptr(gd), _np_ptr(adj), adj.shape[0],
+                                       len(boxes), _np_ptr(bx), C.byref(self._h)))
+        self.nbricks = adj.shape[0]
+        self.ncells = int(sum(np.prod(np.array(hi) - np.array(lo)) for lo, hi in boxes))
+
+    def close(self):
+        if self._h:
+            lib().bricks_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def _run(self, fn, stencil, ins, outs, in_step, out_step, coeff, stream):
+        if not isinstance(ins, (list, tuple)):
+            ins, outs = [ins], [outs]
+        n = len(ins)
+        ia = (C.c_void_p * n)(*ins)
+        oa = (C.c_void_p * n)(*outs)
+        cp = None
+        if coeff is not None:
+            coeff = np.ascontiguousarray(coeff, np.float64)
+            cp = _np_ptr(coeff)
+        check(fn(self._h, stencil, n, ia, oa, in_step, out_step, cp, stream))
+
+    def stencil(self, stencil, ins, outs, in_step=512, out_step=512, coeff=None, stream=STREAM_COMPUTE):
+        self._run(lib().bricks_stencil, stencil, ins, outs, in_step, out_step, coeff, stream)
+
+    def stencil_naive(self, stencil, ins, outs, in_step=512, out_step=512, coeff=None, stream=STREAM_COMPUTE):
+        self._run(lib().bricks_stencil_naive, stencil, ins, outs, in_step, out_step, coeff, stream)
+
+
+class Exchange(object):
+    """Halo exchange plan (bricks_exchange_create).  Offsets and sizes in bytes."""
+
+    def __init__(self, ctx, rank, recv_off, send_off, nbytes, recv_peer, send_peer):
+        a = [np.ascontiguousarray(x, np.uint64) for x in (recv_off, send_off, nbytes)]
+        p = [np.ascontiguousarray(x, np.int32) for x in (recv_peer, send_peer)]
+        self._h = C.c_void_p()
+        self.ctx = ctx
+        check(lib().bricks_exchange_create(ctx._h, rank, len(a[0]), _np_ptr(a[0]), _np_ptr(a[1]), _np_ptr(a[2]),
+                                           _np_ptr(p[0]), _np_ptr(p[1]), C.byref(self._h)))
+
+    def run(self, storage_dev, stream=STREAM_COMM):
+        check(lib().bricks_exchange_run(self._h, C.c_void_p(storage_dev), stream))
+
+    def close(self):
+        if self._h:
+            lib().bricks_exchange_destroy(self._h)
+            self._h = C.c_void_p()
+
+
+def copy_regions(ctx, links, stream=STREAM_COMPUTE):
+    """links: list of (src_dev, dst_dev, nbytes).  Uploads the table then runs the copy kernel."""
+    arr = (RegionLink * len(links))(*[RegionLink(s, d, n) for s, d, n in links])
+    dev = C.c_void_p()
+    check(lib().bricks_links_upload(ctx._h, arr, len(links), C.byref(dev)))
+    check(lib().bricks_copy_regions(ctx._h, dev, len(links), stream))
+    return dev.value
+
+
+# probes ---------------------------------------------------------------------
+def probe_dfma(ctx, iters=20000):
+    t, ms = C.c_double(), C.c_float()
+    check(lib().bricks_probe_dfma(ctx._h, iters, C.byref(t), C.byref(ms)))
+    return t.value
+
+
+def probe_copy(ctx, nbytes, reps=10):
+    g = C.c_double()
+    check(lib().bricks_probe_copy(ctx._h, nbytes, reps, C.byref(g)))
+    return g.value
+
+
+def probe_read(ctx, nbytes, reps=10):
+    g = C.c_double()
+    check(lib().bricks_probe_read(ctx._h, nbytes, reps, C.byref(g)))
+    return g.value
+
+
+def probe_mio(ctx, mode):
+    a, b = C.c_double(), C.c_double()
+    check(lib().bricks_probe_mio(ctx._h, mode, C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
+def probe_tma_image(ctx, field_dev, nbricks, step, b):
+    out = np.zeros(512, np.float64)
+    check(lib().bricks_probe_tma_image(ctx._h, C.c_void_p(field_dev), nbricks, step, b, _np_ptr(out)))
+    return out

@@ -1,0 +1,124 @@
+// Shared internals of libbricks_b200.so (sm_100a only).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/bricks_b200.h"
+
+namespace bricks {
+
+void set_error(const char *fmt, ...);
+extern unsigned long long g_launches;
+
+#define BRK_CUDA(expr)                                                                  \
+  do {                                                                                  \
+    cudaError_t e_ = (expr);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      bricks::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_)); \
+      return (int)e_;                                                                   \
+    }                                                                                   \
+  } while (0)
+
+#define BRK_NCCL(expr)                                                                  \
+  do {                                                                                  \
+    ncclResult_t r_ = (expr);                                                           \
+    if (r_ != ncclSuccess) {                                                            \
+      bricks::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, ncclGetErrorString(r_)); \
+      return 1000 + (int)r_;                                                            \
+    }                                                                                   \
+  } while (0)
+
+#define BRK_ARG(cond)                                                                   \
+  do {                                                                                  \
+    if (!(cond)) {                                                                      \
+      bricks::set_error("%s:%d: bad argument: %s", __FILE__, __LINE__, #cond);          \
+      return -1;                                                                        \
+    }                                                                                   \
+  } while (0)
+
+constexpr int kNumStreams = 2;
+constexpr int kNumTimers = 16;
+
+}  // namespace bricks
+
+struct bricks_ctx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t streams[bricks::kNumStreams] = {nullptr, nullptr};
+  cudaEvent_t xev = nullptr; /* cross-stream dependency */
+  cudaEvent_t t0[bricks::kNumTimers] = {}, t1[bricks::kNumTimers] = {};
+  ncclComm_t comm = nullptr;
+  int rank = 0, nranks = 1;
+};
+
+/* One work item of the marching kernels: a column of nk brick layers at grid (gi..gi+1, gj). */
+struct MarchItem {
+  unsigned short gi, gj, gk0, nk;
+  unsigned valid1; /* second brick of the pair is inside the box */
+  unsigned pad;
+};
+
+/* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane
+ * pieces used for the pre-/post-roll of a column.  [0]=centre 8x8, [1]=i-face HWx8,
+ * [2]=j-face 8xR, [3]=corner HWxR. */
+struct alignas(64) MapSet {
+  CUtensorMap main[4];
+  CUtensorMap roll[4];
+};
+
+struct alignas(64) FieldDev {
+  MapSet maps;
+  double *out;
+  unsigned long long out_step;
+  unsigned long long pad[6];
+};
+
+struct FieldKey {
+  int variant;
+  std::vector<const void *> ptrs; /* in0,out0,in1,out1,... */
+  size_t in_step, out_step;
+  bool operator<(const FieldKey &o) const {
+    if (variant != o.variant) return variant < o.variant;
+    if (in_step != o.in_step) return in_step < o.in_step;
+    if (out_step != o.out_step) return out_step < o.out_step;
+    return ptrs < o.ptrs;
+  }
+};
+
+struct bricks_plan {
+  bricks_ctx *ctx = nullptr;
+  unsigned gdims[3] = {0, 0, 0};
+  unsigned nbricks = 0;
+  unsigned *grid_dev = nullptr;
+  unsigned *adj_dev = nullptr;
+  MarchItem *items_dev = nullptr; /* items for a given max column length */
+  int nitems = 0;
+  unsigned *blist_dev = nullptr; /* flat list of every brick in the boxes (naive kernel) */
+  long nlist = 0;
+  std::map<FieldKey, FieldDev *> fields; /* device arrays, one FieldDev per field */
+};
+
+struct bricks_exchange {
+  bricks_ctx *ctx = nullptr;
+  int rank = 0;
+  struct Msg {
+    size_t recv_off, send_off, nbytes;
+    int recv_peer, send_peer;
+  };
+  std::vector<Msg> msgs;
+  bricks_region_link *self_links_dev = nullptr; /* offsets relative to the storage base */
+  int nself = 0;
+};
+
+namespace bricks {
+int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
+               unsigned bj, unsigned bk, bool swizzle64);
+}

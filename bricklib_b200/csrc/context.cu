@@ -1,0 +1,183 @@
+// Context, memory, copies, streams, timers of libbricks_b200.so.
+// Replaces the gpu* macro layer of the reference (include/brick-cuda.h:12-24,
+// include/brick-gpu.h:23-99, stencils/cudaarray.h:11-31).
+#include "common.cuh"
+
+namespace bricks {
+static thread_local char g_err[1024] = "";
+unsigned long long g_launches = 0;
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+}  // namespace bricks
+
+using namespace bricks;
+
+extern "C" {
+
+const char *bricks_last_error(void) { return g_err; }
+
+int bricks_device_count(int *count) {
+  BRK_ARG(count);
+  BRK_CUDA(cudaGetDeviceCount(count));
+  return 0;
+}
+
+int bricks_ctx_create(int device, bricks_ctx **out) {
+  BRK_ARG(out);
+  BRK_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  BRK_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("bricks_b200 is built for sm_100a only; device %d is sm_%d%d", device, prop.major,
+              prop.minor);
+    return -2;
+  }
+  bricks_ctx *c = new bricks_ctx;
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  for (int s = 0; s < kNumStreams; ++s)
+    BRK_CUDA(cudaStreamCreateWithFlags(&c->streams[s], cudaStreamNonBlocking));
+  BRK_CUDA(cudaEventCreateWithFlags(&c->xev, cudaEventDisableTiming));
+  for (int t = 0; t < kNumTimers; ++t) {
+    BRK_CUDA(cudaEventCreate(&c->t0[t]));
+    BRK_CUDA(cudaEventCreate(&c->t1[t]));
+  }
+  *out = c;
+  return 0;
+}
+
+int bricks_ctx_destroy(bricks_ctx *c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  if (c->comm) ncclCommDestroy(c->comm);
+  for (int s = 0; s < kNumStreams; ++s)
+    if (c->streams[s]) cudaStreamDestroy(c->streams[s]);
+  if (c->xev) cudaEventDestroy(c->xev);
+  for (int t = 0; t < kNumTimers; ++t) {
+    if (c->t0[t]) cudaEventDestroy(c->t0[t]);
+    if (c->t1[t]) cudaEventDestroy(c->t1[t]);
+  }
+  delete c;
+  return 0;
+}
+
+int bricks_ctx_device(const bricks_ctx *c, int *device) {
+  BRK_ARG(c && device);
+  *device = c->device;
+  return 0;
+}
+
+static inline int pick_stream(bricks_ctx *c, int stream, cudaStream_t *s) {
+  BRK_ARG(c && stream >= 0 && stream < kNumStreams);
+  *s = c->streams[stream];
+  return 0;
+}
+
+int bricks_malloc(bricks_ctx *c, void **dptr, size_t bytes) {
+  BRK_ARG(c && dptr);
+  BRK_CUDA(cudaSetDevice(c->device));
+  BRK_CUDA(cudaMalloc(dptr, bytes ? bytes : 16));
+  return 0;
+}
+
+int bricks_free(bricks_ctx *c, void *dptr) {
+  BRK_ARG(c);
+  BRK_CUDA(cudaSetDevice(c->device));
+  BRK_CUDA(cudaFree(dptr));
+  return 0;
+}
+
+int bricks_memset(bricks_ctx *c, void *dptr, int value, size_t bytes) {
+  BRK_ARG(c && dptr);
+  BRK_CUDA(cudaSetDevice(c->device));
+  BRK_CUDA(cudaMemsetAsync(dptr, value, bytes, c->streams[BRICKS_STREAM_COMPUTE]));
+  return 0;
+}
+
+int bricks_host_alloc(void **hptr, size_t bytes) {
+  BRK_ARG(hptr);
+  BRK_CUDA(cudaMallocHost(hptr, bytes ? bytes : 16));
+  return 0;
+}
+
+int bricks_host_free(void *hptr) {
+  BRK_CUDA(cudaFreeHost(hptr));
+  return 0;
+}
+
+static int copy_async(bricks_ctx *c, void *dst, const void *src, size_t bytes, int stream,
+                      cudaMemcpyKind kind) {
+  cudaStream_t s;
+  int rc = pick_stream(c, stream, &s);
+  if (rc) return rc;
+  BRK_ARG(dst && src);
+  BRK_CUDA(cudaSetDevice(c->device));
+  BRK_CUDA(cudaMemcpyAsync(dst, src, bytes, kind, s));
+  return 0;
+}
+
+int bricks_h2d(bricks_ctx *c, void *dst, const void *src, size_t bytes, int stream) {
+  return copy_async(c, dst, src, bytes, stream, cudaMemcpyHostToDevice);
+}
+int bricks_d2h(bricks_ctx *c, void *dst, const void *src, size_t bytes, int stream) {
+  return copy_async(c, dst, src, bytes, stream, cudaMemcpyDeviceToHost);
+}
+int bricks_d2d(bricks_ctx *c, void *dst, const void *src, size_t bytes, int stream) {
+  return copy_async(c, dst, src, bytes, stream, cudaMemcpyDeviceToDevice);
+}
+
+int bricks_sync(bricks_ctx *c, int stream) {
+  BRK_ARG(c && stream < kNumStreams);
+  BRK_CUDA(cudaSetDevice(c->device));
+  if (stream < 0)
+    BRK_CUDA(cudaDeviceSynchronize());
+  else
+    BRK_CUDA(cudaStreamSynchronize(c->streams[stream]));
+  return 0;
+}
+
+int bricks_stream_wait(bricks_ctx *c, int stream, int other) {
+  BRK_ARG(c && stream >= 0 && stream < kNumStreams && other >= 0 && other < kNumStreams);
+  BRK_CUDA(cudaSetDevice(c->device));
+  BRK_CUDA(cudaEventRecord(c->xev, c->streams[other]));
+  BRK_CUDA(cudaStreamWaitEvent(c->streams[stream], c->xev, 0));
+  return 0;
+}
+
+int bricks_stream_handle(bricks_ctx *c, int stream, void **cuda_stream) {
+  BRK_ARG(c && cuda_stream && stream >= 0 && stream < kNumStreams);
+  *cuda_stream = (void *)c->streams[stream];
+  return 0;
+}
+
+int bricks_timer_start(bricks_ctx *c, int stream, int slot) {
+  BRK_ARG(c && slot >= 0 && slot < kNumTimers && stream >= 0 && stream < kNumStreams);
+  BRK_CUDA(cudaEventRecord(c->t0[slot], c->streams[stream]));
+  return 0;
+}
+
+int bricks_timer_stop(bricks_ctx *c, int stream, int slot) {
+  BRK_ARG(c && slot >= 0 && slot < kNumTimers && stream >= 0 && stream < kNumStreams);
+  BRK_CUDA(cudaEventRecord(c->t1[slot], c->streams[stream]));
+  return 0;
+}
+
+int bricks_timer_elapsed_ms(bricks_ctx *c, int slot, float *ms) {
+  BRK_ARG(c && ms && slot >= 0 && slot < kNumTimers);
+  BRK_CUDA(cudaEventSynchronize(c->t1[slot]));
+  BRK_CUDA(cudaEventElapsedTime(ms, c->t0[slot], c->t1[slot]));
+  return 0;
+}
+
+int bricks_launch_count(unsigned long long *count) {
+  BRK_ARG(count);
+  *count = g_launches;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,233 @@
+// Region copies and the halo exchange.
+//   bricks_copy_regions  replaces cudaCopy<<<nlinks,64>>> (strong/main.cu:62-83): the reference
+//                        gives each region ONE block of 64 threads moving 8-byte words; here a
+//                        region is split over as many CTAs as its size warrants, 16 bytes/lane.
+//   bricks_exchange_*    replaces BrickDecomp::exchange (include/brick-mpi.h:466-495) and the
+//                        D2H -> MPI -> H2D staging of weak/main.cu:251-275 with device-resident
+//                        ncclSend/ncclRecv straight from/to brick storage (regions are contiguous
+//                        by construction of the layout, so nothing is packed); regions whose
+//                        peer is this rank become on-device copies.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kCopyThreads = 256;
+constexpr size_t kChunk = 64 * 1024; /* bytes per CTA */
+
+struct CopyJob {
+  unsigned link;
+  unsigned chunk;
+};
+
+/* links[] in device memory; grid.x = total chunks; base_off shifts both ends (self links are
+ * stored relative to the storage base) */
+__global__ void __launch_bounds__(kCopyThreads) copy_regions_kernel(const bricks_region_link *links,
+                                                                   const unsigned *chunk_first, int nlinks,
+                                                                   char *base) {
+  /* binary search: which link does this CTA's chunk belong to */
+  int lo = 0, hi = nlinks - 1;
+  const unsigned c = blockIdx.x;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (chunk_first[mid] <= c) lo = mid; else hi = mid - 1;
+  }
+  const bricks_region_link l = links[lo];
+  const size_t start = (size_t)(c - chunk_first[lo]) * kChunk;
+  const size_t end = start + kChunk < l.len ? start + kChunk : l.len;
+  const char *src = (base ? base + (size_t)l.from : (const char *)l.from) + start;
+  char *dst = (base ? base + (size_t)l.to : (char *)l.to) + start;
+  const size_t n16 = (end - start) >> 4;
+  const int4 *s4 = reinterpret_cast<const int4 *>(src);
+  int4 *d4 = reinterpret_cast<int4 *>(dst);
+  for (size_t i = threadIdx.x; i < n16; i += 4 * kCopyThreads) {
+    int4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * kCopyThreads < n16) v[u] = __ldcs(s4 + i + u * kCopyThreads);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * kCopyThreads < n16) __stcs(d4 + i + u * kCopyThreads, v[u]);
+  }
+}
+
+struct LinkTable {
+  bricks_region_link *links;
+  unsigned *chunk_first;
+  unsigned nchunks;
+};
+
+int upload_links(bricks_ctx *ctx, const bricks_region_link *host, int n, void **blob, unsigned *nchunks) {
+  /* device blob = links[n] followed by chunk_first[n] */
+  std::vector<unsigned> first(n);
+  unsigned tot = 0;
+  for (int i = 0; i < n; ++i) {
+    first[i] = tot;
+    tot += (unsigned)((host[i].len + kChunk - 1) / kChunk);
+  }
+  const size_t lb = sizeof(bricks_region_link) * n, fb = sizeof(unsigned) * n;
+  char *d = nullptr;
+  BRK_CUDA(cudaMalloc(&d, lb + fb + 16));
+  cudaStream_t s = ctx->streams[BRICKS_STREAM_COMPUTE];
+  BRK_CUDA(cudaMemcpyAsync(d, host, lb, cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaMemcpyAsync(d + lb, first.data(), fb, cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaStreamSynchronize(s));
+  *blob = d;
+  *nchunks = tot;
+  return 0;
+}
+
+}  // namespace
+
+/* The device blob returned by bricks_links_upload carries its own chunk table after the links;
+ * the count of chunks is kept host side, keyed by the blob pointer. */
+static std::map<const void *, std::pair<int, unsigned>> g_link_meta;
+
+extern "C" {
+
+int bricks_links_upload(bricks_ctx *ctx, const bricks_region_link *links_host, int n,
+                        bricks_region_link **links_dev) {
+  BRK_ARG(ctx && links_host && links_dev && n > 0);
+  for (int i = 0; i < n; ++i)
+    BRK_ARG((links_host[i].len & 15) == 0 && ((uintptr_t)links_host[i].from & 15) == 0 &&
+            ((uintptr_t)links_host[i].to & 15) == 0);
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  void *blob = nullptr;
+  unsigned nchunks = 0;
+  int rc = upload_links(ctx, links_host, n, &blob, &nchunks);
+  if (rc) return rc;
+  g_link_meta[blob] = std::make_pair(n, nchunks);
+  *links_dev = (bricks_region_link *)blob;
+  return 0;
+}
+
+int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, int n, int stream) {
+  BRK_ARG(ctx && links_dev && stream >= 0 && stream < bricks::kNumStreams);
+  auto it = g_link_meta.find(links_dev);
+  BRK_ARG(it != g_link_meta.end() && it->second.first == n);
+  if (it->second.second == 0) return 0;
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  const unsigned *first = (const unsigned *)((const char *)links_dev + sizeof(bricks_region_link) * n);
+  copy_regions_kernel<<<it->second.second, kCopyThreads, 0, ctx->streams[stream]>>>(links_dev, first, n,
+                                                                                  nullptr);
+  BRK_CUDA(cudaGetLastError());
+  ++bricks::g_launches;
+  return 0;
+}
+
+int bricks_comm_unique_id(void *id128) {
+  BRK_ARG(id128);
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  BRK_NCCL(ncclGetUniqueId((ncclUniqueId *)id128));
+  return 0;
+}
+
+int bricks_comm_init(bricks_ctx *ctx, int rank, int nranks, const void *id128) {
+  BRK_ARG(ctx && id128 && nranks > 0 && rank >= 0 && rank < nranks);
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  ncclUniqueId id;
+  memcpy(&id, id128, sizeof id);
+  BRK_NCCL(ncclCommInitRank(&ctx->comm, nranks, id, rank));
+  ctx->rank = rank;
+  ctx->nranks = nranks;
+  return 0;
+}
+
+int bricks_comm_destroy(bricks_ctx *ctx) {
+  BRK_ARG(ctx);
+  if (ctx->comm) {
+    BRK_NCCL(ncclCommDestroy(ctx->comm));
+    ctx->comm = nullptr;
+  }
+  return 0;
+}
+
+int bricks_exchange_create(bricks_ctx *ctx, int rank, int nregions, const size_t *recv_off,
+                           const size_t *send_off, const size_t *nbytes, const int *recv_peer,
+                           const int *send_peer, bricks_exchange **out) {
+  BRK_ARG(ctx && out && nregions > 0 && recv_off && send_off && nbytes && recv_peer && send_peer);
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  bricks_exchange *ex = new bricks_exchange;
+  ex->ctx = ctx;
+  ex->rank = rank;
+  std::vector<bricks_region_link> self;
+  for (int i = 0; i < nregions; ++i) {
+    BRK_ARG((recv_off[i] & 15) == 0 && (send_off[i] & 15) == 0 && (nbytes[i] & 15) == 0);
+    BRK_ARG((recv_peer[i] == rank) == (send_peer[i] == rank));
+    if (nbytes[i] == 0) continue;
+    bricks_exchange::Msg m = {recv_off[i], send_off[i], nbytes[i], recv_peer[i], send_peer[i]};
+    ex->msgs.push_back(m);
+  }
+  /* Region i is received from recv_peer[i] and sent to send_peer[i].  When recv_peer[i] is this
+   * rank, the matching send is this rank's own region i (periodic process grid of extent 1 or
+   * 2 in that direction), i.e. ghost[i] <- skin[i] on the device. */
+  for (auto &m : ex->msgs)
+    if (m.recv_peer == rank) {
+      bricks_region_link l;
+      l.from = (double *)m.send_off; /* relative to the storage base */
+      l.to = (double *)m.recv_off;
+      l.len = m.nbytes;
+      self.push_back(l);
+    }
+  ex->nself = (int)self.size();
+  if (ex->nself) {
+    void *blob = nullptr;
+    unsigned nchunks = 0;
+    int rc = upload_links(ctx, self.data(), ex->nself, &blob, &nchunks);
+    if (rc) return rc;
+    g_link_meta[blob] = std::make_pair(ex->nself, nchunks);
+    ex->self_links_dev = (bricks_region_link *)blob;
+  }
+  *out = ex;
+  return 0;
+}
+
+int bricks_exchange_destroy(bricks_exchange *ex) {
+  if (!ex) return 0;
+  cudaSetDevice(ex->ctx->device);
+  if (ex->self_links_dev) {
+    g_link_meta.erase(ex->self_links_dev);
+    cudaFree(ex->self_links_dev);
+  }
+  delete ex;
+  return 0;
+}
+
+int bricks_exchange_run(bricks_exchange *ex, double *storage, int stream) {
+  BRK_ARG(ex && storage && stream >= 0 && stream < bricks::kNumStreams);
+  bricks_ctx *ctx = ex->ctx;
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->streams[stream];
+  char *base = (char *)storage;
+  bool remote = false;
+  for (auto &m : ex->msgs) remote = remote || m.recv_peer != ex->rank || m.send_peer != ex->rank;
+  if (remote) {
+    if (!ctx->comm) {
+      bricks::set_error("exchange has remote peers but bricks_comm_init was not called");
+      return -4;
+    }
+    /* both sides enumerate regions in the same order i (the reference's MPI tag, brick-mpi.h:478-484);
+     * NCCL matches send/recv pairs per peer in issue order */
+    BRK_NCCL(ncclGroupStart());
+    for (auto &m : ex->msgs) {
+      if (m.recv_peer != ex->rank)
+        BRK_NCCL(ncclRecv(base + m.recv_off, m.nbytes, ncclChar, m.recv_peer, ctx->comm, s));
+      if (m.send_peer != ex->rank)
+        BRK_NCCL(ncclSend(base + m.send_off, m.nbytes, ncclChar, m.send_peer, ctx->comm, s));
+    }
+    BRK_NCCL(ncclGroupEnd());
+  }
+  if (ex->nself) {
+    auto it = g_link_meta.find(ex->self_links_dev);
+    const unsigned *first =
+        (const unsigned *)((const char *)ex->self_links_dev + sizeof(bricks_region_link) * ex->nself);
+    copy_regions_kernel<<<it->second.second, kCopyThreads, 0, s>>>(ex->self_links_dev, first, ex->nself,
+                                                                  base);
+    BRK_CUDA(cudaGetLastError());
+    ++bricks::g_launches;
+  }
+  return 0;
+}
+
+}  // extern "C"

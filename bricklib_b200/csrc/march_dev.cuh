@@ -1,0 +1,159 @@
+// Device-side building blocks of the marching stencil kernels (sm_100a): mbarrier + TMA
+// (cp.async.bulk.tensor, SASS UTMALDG) wrappers, the per-stage shared-memory layout and the
+// per-lane addressing constants.
+//
+// Work decomposition (see DESIGN.md "Kernels"): ONE WARP marches a column of brick layers
+// along k for a footprint of two bricks adjacent in i (16 x 8 points per plane).  Lane
+// (bb, j, ih) owns the four consecutive points i = 4*ih .. 4*ih+3 of row j of brick bb, so a
+// plane of one brick is read by 16 lanes as 32-byte quads (two LDS.128), k-neighbours live in
+// registers of the marching lane, i-neighbours come from the adjacent lane by warp shuffle
+// (the `dev_shl` idea of the reference, include/dev_shl.h:51-63) and j-neighbours from shared
+// memory.  Each stage of the 2-deep TMA pipeline holds P planes of: the two centre bricks, the
+// i-face columns of the -i/+i neighbours, the j-face rows of the -j/+j neighbours and (cube
+// stencil) the four ij-corner pieces; every piece is one TMA box copy out of the neighbour
+// brick that BrickInfo::adj names (include/brick.h:96-127).
+#pragma once
+#include "common.cuh"
+
+namespace dev {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+/* one box of the [brick][k][j][i] field tensor -> dense box in shared memory */
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, int ci, int cj,
+                                            int ck, int cb, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(dst),
+      "l"(map), "r"(ci), "r"(cj), "r"(ck), "r"(cb), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void st_quad(double *p, const double (&v)[4]) {
+  /* 32 contiguous bytes per lane = one full L2 sector, streaming (written once per sweep) */
+  __stcs(reinterpret_cast<double2 *>(p), make_double2(v[0], v[1]));
+  __stcs(reinterpret_cast<double2 *>(p) + 1, make_double2(v[2], v[3]));
+}
+
+/* Byte layout of one pipeline stage.  P = planes per main stage (4 or 8). */
+template <int R, bool CUBE, int P>
+struct StageLayout {
+  static constexpr int HW = R > 2 ? 4 : 2;      /* i-face width in elements (16-byte multiple) */
+  static constexpr int C_PL = 512, I_PL = 64 * HW, J_PL = 64 * R, X_PL = 8 * R * HW; /* B/plane */
+  static constexpr int C0 = 0, C1 = P * C_PL;
+  static constexpr int IL = 2 * P * C_PL, IR = IL + P * I_PL;
+  static constexpr int JL0 = IR + P * I_PL, JL1 = JL0 + P * J_PL, JH0 = JL1 + P * J_PL,
+                       JH1 = JH0 + P * J_PL;
+  static constexpr int XLL = JH1 + P * J_PL, XRL = XLL + P * X_PL, XLH = XRL + P * X_PL,
+                       XRH = XLH + P * X_PL;
+  static constexpr int RAW = CUBE ? XRH + P * X_PL : XLL;
+  static constexpr int BYTES = (RAW + 511) / 512 * 512;
+  static constexpr int NPIECE_MAIN = CUBE ? 12 : 8;
+  static constexpr int NPIECE_ROLL = CUBE ? 12 : 2;
+};
+
+/* what lane p (< 12) copies: piece p of the stage */
+struct PieceK {
+  int useb1, di, dj, map, ci, cj, off, plane_bytes;
+};
+
+template <int R, bool CUBE, int P>
+__device__ __forceinline__ PieceK piece_of(int p) {
+  using L = StageLayout<R, CUBE, P>;
+  PieceK k;
+  k.useb1 = p & 1;
+  const int grp = p >> 1; /* 0 C, 1 I, 2 JL, 3 JH, 4 X-low (LL,RL), 5 X-high (LH,RH) */
+  const int side = k.useb1 ? +1 : -1;
+  k.di = (grp == 1 || grp >= 4) ? side : 0;
+  k.dj = (grp == 2 || grp == 4) ? -1 : ((grp == 3 || grp == 5) ? +1 : 0);
+  k.map = grp == 0 ? 0 : (grp == 1 ? 1 : (grp <= 3 ? 2 : 3));
+  k.ci = (k.di < 0) ? 8 - L::HW : 0;
+  k.cj = (k.dj < 0) ? 8 - R : 0;
+  k.plane_bytes = grp == 0 ? L::C_PL : (grp == 1 ? L::I_PL : (grp <= 3 ? L::J_PL : L::X_PL));
+  const int offs[12] = {L::C0,  L::C1,  L::IL,  L::IR,  L::JL0, L::JL1,
+                        L::JH0, L::JH1, L::XLL, L::XRL, L::XLH, L::XRH};
+  k.off = offs[p < 12 ? p : 0];
+  return k;
+}
+
+/* Per-lane addressing constants.  Row j+d of the lane's own brick lives either in the centre
+ * piece (64B-swizzled by TMA: 16-byte chunk index ^= (row >> 1) & 3) or in a j-face piece. */
+template <int R, bool CUBE, int P>
+struct LaneK {
+  using L = StageLayout<R, CUBE, P>;
+  int bb, j, ih;
+  int srcL, srcR;        /* shuffle sources for the left / right i-neighbour quads */
+  bool halo;             /* this lane loads the i-face (left if bb==0, right if bb==1) */
+  int row0[2 * R + 1];   /* byte offset of quad chunk 0 of row j+d, plane 0 */
+  int row1[2 * R + 1];   /* ... chunk 1 */
+  int rpitch[2 * R + 1]; /* bytes per plane for that row */
+  int hrow[2 * R + 1];   /* halo: byte offset of the HW-wide row j+d, plane 0 */
+  int hpitch[2 * R + 1];
+
+  __device__ __forceinline__ void init(int lane) {
+    bb = lane >> 4;
+    j = (lane >> 1) & 7;
+    ih = lane & 1;
+    halo = (ih == bb);
+    srcL = ih ? lane - 1 : (bb ? lane - 15 : lane);
+    srcR = ih ? (bb ? lane : lane + 15) : lane + 1;
+#pragma unroll
+    for (int d = -R; d <= R; ++d) {
+      const int jj = j + d, a = d + R;
+      if (jj >= 0 && jj < 8) {
+        const int base = (bb ? L::C1 : L::C0) + jj * 64, sw = (jj >> 1) & 3;
+        row0[a] = base + (((2 * ih) ^ sw) << 4);
+        row1[a] = base + (((2 * ih + 1) ^ sw) << 4);
+        rpitch[a] = L::C_PL;
+        hrow[a] = (bb ? L::IR : L::IL) + jj * L::HW * 8;
+        hpitch[a] = L::I_PL;
+      } else {
+        const bool low = jj < 0;
+        const int rr = low ? jj + R : jj - 8;
+        const int base = (low ? (bb ? L::JL1 : L::JL0) : (bb ? L::JH1 : L::JH0)) + rr * 64;
+        row0[a] = base + ih * 32;
+        row1[a] = base + ih * 32 + 16;
+        rpitch[a] = L::J_PL;
+        hrow[a] = (low ? (bb ? L::XRL : L::XLL) : (bb ? L::XRH : L::XLH)) + rr * L::HW * 8;
+        hpitch[a] = L::X_PL;
+      }
+    }
+  }
+};
+
+__device__ __forceinline__ void ld_quad(const char *st, int off0, int off1, double (&v)[4]) {
+  const double2 a = *reinterpret_cast<const double2 *>(st + off0);
+  const double2 b = *reinterpret_cast<const double2 *>(st + off1);
+  v[0] = a.x;
+  v[1] = a.y;
+  v[2] = b.x;
+  v[3] = b.y;
+}
+
+}  // namespace dev

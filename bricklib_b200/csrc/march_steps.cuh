@@ -1,0 +1,207 @@
+// Per-stage arithmetic of the marching kernels.  MODE: 0 = pre-roll (R planes below the
+// column: only their contribution to later output planes), 1 = main stage (NZ planes of a
+// brick layer), 2 = post-roll (R planes above the column: only their contribution to earlier
+// planes).  `carry` holds the 2R partially summed output planes that straddle stages:
+// carry[a] <-> output plane (a - R) relative to the first input plane of the next stage.
+//
+// Stencil definitions followed: stencils/7pt.py:19-26 (VAR=1: coeff[0..6] = centre, i+1, i-1,
+// j+1, j-1, k+1, k-1), stencils/mpi7pt.py:17-24, mpi13pt.py:18-31, mpi25pt.py:20-45 (VAR=0:
+// c[r] for |offset| = r along one axis), stencils/mpi125pt.py:12-161 (10 coefficients indexed by
+// the sorted |offset| triple).  Summation order differs from the generated reference code, so
+// results agree to rounding (<= 1e-12 relative is the bar), not bit for bit.
+#pragma once
+#include "march_dev.cuh"
+
+namespace dev {
+
+struct OutPtrs {
+  double *cur, *prev; /* lane's quad in plane 0 of the current / previous layer's brick */
+  bool curv, prevv;
+};
+
+template <int R, int MODE>
+__device__ __forceinline__ void store_done(const OutPtrs &o, int zbase, int z, const double (&v)[4]) {
+  if (MODE == 0) return;
+  const int op = zbase + z - R; /* output plane relative to the current layer */
+  if (op >= 0) {
+    if (o.curv) st_quad(o.cur + op * 64, v);
+  } else {
+    if (o.prevv) st_quad(o.prev + (op + 8) * 64, v);
+  }
+}
+
+/* i-neighbours of the lane's quad: R values on each side, by shuffle from the adjacent lane or,
+ * on the footprint edge, from the i-face piece. */
+template <int R, int HW>
+__device__ __forceinline__ void gather_i(const double (&x)[4], const double (&h)[HW], bool halo, int bb,
+                                         int srcL, int srcR, double (&e)[4 + 2 * R]) {
+#pragma unroll
+  for (int m = 0; m < 4; ++m) e[R + m] = x[m];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const double l = __shfl_sync(0xffffffffu, x[4 - R + r], srcL);
+    const double g = __shfl_sync(0xffffffffu, x[r], srcR);
+    e[r] = (halo && bb == 0) ? h[HW - R + r] : l;
+    e[R + 4 + r] = (halo && bb == 1) ? h[r] : g;
+  }
+}
+
+template <int HW>
+__device__ __forceinline__ void ld_halo(const char *st, int off, bool halo, double (&h)[HW]) {
+#pragma unroll
+  for (int q = 0; q < HW; ++q) h[q] = 0.0;
+  if (halo) {
+#pragma unroll
+    for (int q = 0; q < HW / 2; ++q) {
+      const double2 v = *reinterpret_cast<const double2 *>(st + off + 16 * q);
+      h[2 * q] = v.x;
+      h[2 * q + 1] = v.y;
+    }
+  }
+}
+
+/* ------------------------------------------------------------------ star stencils */
+template <int R, int VAR, int P, int NZ, int MODE>
+__device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, P> &lk,
+                                          const double *__restrict__ c, double (&carry)[2 * R][4],
+                                          const OutPtrs &o, int zbase) {
+  constexpr int HW = StageLayout<R, false, P>::HW;
+  double acc[NZ + 2 * R][4];
+#pragma unroll
+  for (int a = 0; a < NZ + 2 * R; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) acc[a][m] = a < 2 * R ? carry[a][m] : 0.0;
+
+#pragma unroll
+  for (int z = 0; z < NZ; ++z) {
+    double x[4];
+    ld_quad(st, lk.row0[R] + z * lk.rpitch[R], lk.row1[R] + z * lk.rpitch[R], x);
+    if (MODE == 1) {
+      double h[HW], e[4 + 2 * R];
+      ld_halo<HW>(st, lk.hrow[R] + z * lk.hpitch[R], lk.halo, h);
+      gather_i<R, HW>(x, h, lk.halo, lk.bb, lk.srcL, lk.srcR, e);
+      double s[4];
+#pragma unroll
+      for (int m = 0; m < 4; ++m) s[m] = c[0] * x[m];
+#pragma unroll
+      for (int r = 1; r <= R; ++r) {
+        double up[4], dn[4];
+        ld_quad(st, lk.row0[R + r] + z * lk.rpitch[R + r], lk.row1[R + r] + z * lk.rpitch[R + r], up);
+        ld_quad(st, lk.row0[R - r] + z * lk.rpitch[R - r], lk.row1[R - r] + z * lk.rpitch[R - r], dn);
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          if (VAR) {
+            s[m] += c[1] * e[R + m + 1];
+            s[m] += c[2] * e[R + m - 1];
+            s[m] += c[3] * up[m];
+            s[m] += c[4] * dn[m];
+          } else {
+            s[m] += c[r] * ((e[R + m + r] + e[R + m - r]) + (up[m] + dn[m]));
+          }
+        }
+      }
+#pragma unroll
+      for (int m = 0; m < 4; ++m) acc[z + R][m] += s[m];
+    }
+#pragma unroll
+    for (int r = 1; r <= R; ++r)
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        /* input plane z feeds output planes z-r (needs x(k+r)) and z+r (needs x(k-r)) */
+        if (MODE != 0) acc[z + R - r][m] += (VAR ? c[5] : c[r]) * x[m];
+        if (MODE != 2) {
+          if (r == R)
+            acc[z + R + r][m] = (VAR ? c[6] : c[r]) * x[m];
+          else
+            acc[z + R + r][m] += (VAR ? c[6] : c[r]) * x[m];
+        }
+      }
+    store_done<R, MODE>(o, zbase, z, acc[z]);
+  }
+#pragma unroll
+  for (int a = 0; a < 2 * R; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) carry[a][m] = acc[NZ + a][m];
+}
+
+/* ------------------------------------------------------------------ 125-point cube
+ * Factorisation: per input plane, with v_b = x(j+b)+x(j-b) (v_0 = x),
+ * t_ab = v_b(i+a)+v_b(i-a), Q_ab = t_ab + t_ba (a<b), the plane's contribution to output plane
+ * z+-c is G_c = sum_{a<=b} C[class(a,b,c)] * Q_ab.  ~35 fp64 ops per point instead of 125. */
+template <int P, int NZ, int MODE>
+__device__ __forceinline__ void cube_step(const char *st, const LaneK<2, true, P> &lk,
+                                          const double *__restrict__ c, double (&carry)[4][4],
+                                          const OutPtrs &o, int zbase) {
+  constexpr int R = 2, HW = 2;
+  double acc[NZ + 4][4];
+#pragma unroll
+  for (int a = 0; a < NZ + 4; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) acc[a][m] = a < 4 ? carry[a][m] : 0.0;
+
+#pragma unroll
+  for (int z = 0; z < NZ; ++z) {
+    /* v_b on the lane's quad and on its i-face pair */
+    double v[3][4], hv[3][HW];
+    {
+      double xr[5][4], hr[5][HW];
+#pragma unroll
+      for (int a = 0; a < 5; ++a) {
+        ld_quad(st, lk.row0[a] + z * lk.rpitch[a], lk.row1[a] + z * lk.rpitch[a], xr[a]);
+        ld_halo<HW>(st, lk.hrow[a] + z * lk.hpitch[a], lk.halo, hr[a]);
+      }
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        v[0][m] = xr[2][m];
+        v[1][m] = xr[1][m] + xr[3][m];
+        v[2][m] = xr[0][m] + xr[4][m];
+      }
+#pragma unroll
+      for (int q = 0; q < HW; ++q) {
+        hv[0][q] = hr[2][q];
+        hv[1][q] = hr[1][q] + hr[3][q];
+        hv[2][q] = hr[0][q] + hr[4][q];
+      }
+    }
+    double e[3][8];
+#pragma unroll
+    for (int b = 0; b < 3; ++b) gather_i<R, HW>(v[b], hv[b], lk.halo, lk.bb, lk.srcL, lk.srcR, e[b]);
+
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      double t[3][3]; /* t[a][b]: i-offset a, j-offset b */
+#pragma unroll
+      for (int b = 0; b < 3; ++b) {
+        t[0][b] = e[b][2 + m];
+        t[1][b] = e[b][3 + m] + e[b][1 + m];
+        t[2][b] = e[b][4 + m] + e[b][m];
+      }
+      const double q00 = t[0][0], q11 = t[1][1], q22 = t[2][2];
+      const double q01 = t[0][1] + t[1][0], q02 = t[0][2] + t[2][0], q12 = t[1][2] + t[2][1];
+      /* coefficient classes of stencils/mpi125pt.py:12-33: c[0]=(0,0,0) c[1]=(0,0,1) c[2]=(0,0,2)
+       * c[3]=(0,1,1) c[4]=(0,1,2) c[5]=(0,2,2) c[6]=(1,1,1) c[7]=(1,1,2) c[8]=(1,2,2) c[9]=(2,2,2) */
+      double g[3];
+      g[0] = 0.0;
+      if (MODE == 1)
+        g[0] = c[0] * q00 + c[1] * q01 + c[2] * q02 + c[3] * q11 + c[4] * q12 + c[5] * q22;
+      g[1] = c[1] * q00 + c[3] * q01 + c[4] * q02 + c[6] * q11 + c[7] * q12 + c[8] * q22;
+      g[2] = c[2] * q00 + c[4] * q01 + c[5] * q02 + c[7] * q11 + c[8] * q12 + c[9] * q22;
+      if (MODE == 1) acc[z + 2][m] += g[0];
+      if (MODE != 0) {
+        acc[z + 1][m] += g[1];
+        acc[z][m] += g[2];
+      }
+      if (MODE != 2) {
+        acc[z + 3][m] += g[1];
+        acc[z + 4][m] = g[2];
+      }
+    }
+    store_done<R, MODE>(o, zbase, z, acc[z]);
+  }
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) carry[a][m] = acc[NZ + a][m];
+}
+
+}  // namespace dev

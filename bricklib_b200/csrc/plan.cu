@@ -1,0 +1,156 @@
+// Launch plans: the host side of the reference's `<<<dim3(strideb0,strideb1,strideb2),32>>>`
+// launch shape (weak/main.cu:277-281, stencils/3axis.cu:163-169, strong/main.cu:464-475),
+// re-expressed as marching work items, plus TMA tensor-map construction over a brick field.
+#include <algorithm>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace bricks {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+/* A field is viewed as the 4-D tensor [brick][k][j][i] of fp64 with strides
+ * (step*8, 512, 64, 8) bytes: the layout contract of include/brick.h:229-246 for fold <4,8>. */
+int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
+               unsigned bj, unsigned bk, bool swizzle64) {
+  EncodeTiledFn fn = get_encode();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return -3;
+  }
+  cuuint64_t dims[4] = {8, 8, 8, nbricks};
+  cuuint64_t strides[3] = {64, 512, (cuuint64_t)step_elems * 8};
+  cuuint32_t box[4] = {bi, bj, bk, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<void *>(base), dims, strides, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(box %ux%ux%u, step %zu) failed with CUresult %d", bi, bj, bk,
+              step_elems, (int)r);
+    return 2000 + (int)r;
+  }
+  return 0;
+}
+
+/* longest column a single warp marches; chosen so a 66-layer column splits evenly and the
+ * pre/post-roll overhead stays below ~5 % */
+static const unsigned kMaxColumn = 11;
+
+static void build_items(const unsigned gdims[3], int nboxes, const unsigned *boxes,
+                        std::vector<MarchItem> &items, std::vector<unsigned> &cells) {
+  for (int b = 0; b < nboxes; ++b) {
+    const unsigned *lo = boxes + 6 * b, *hi = lo + 3;
+    if (hi[0] <= lo[0] || hi[1] <= lo[1] || hi[2] <= lo[2]) continue;
+    unsigned nk = hi[2] - lo[2];
+    unsigned nseg = (nk + kMaxColumn - 1) / kMaxColumn;
+    unsigned seglen = (nk + nseg - 1) / nseg;
+    for (unsigned s = 0; s < nseg; ++s) {
+      unsigned k0 = lo[2] + s * seglen;
+      unsigned k1 = std::min(hi[2], k0 + seglen);
+      if (k0 >= k1) continue;
+      for (unsigned j = lo[1]; j < hi[1]; ++j)
+        for (unsigned i = lo[0]; i < hi[0]; i += 2) {
+          MarchItem it;
+          it.gi = (unsigned short)i;
+          it.gj = (unsigned short)j;
+          it.gk0 = (unsigned short)k0;
+          it.nk = (unsigned short)(k1 - k0);
+          it.valid1 = (i + 1 < hi[0]) ? 1u : 0u;
+          it.pad = 0;
+          items.push_back(it);
+        }
+    }
+    for (unsigned k = lo[2]; k < hi[2]; ++k)
+      for (unsigned j = lo[1]; j < hi[1]; ++j)
+        for (unsigned i = lo[0]; i < hi[0]; ++i)
+          cells.push_back((k * gdims[1] + j) * gdims[0] + i);
+  }
+}
+
+}  // namespace bricks
+
+using namespace bricks;
+
+extern "C" {
+
+int bricks_plan_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigned gdims[3],
+                       const unsigned *adj_host, unsigned nbricks, int nboxes, const unsigned *boxes,
+                       bricks_plan **out) {
+  BRK_ARG(ctx && grid_host && gdims && adj_host && boxes && out && nboxes > 0 && nbricks > 0);
+  for (int b = 0; b < nboxes; ++b)
+    for (int d = 0; d < 3; ++d) BRK_ARG(boxes[6 * b + 3 + d] <= gdims[d]);
+  BRK_ARG(gdims[0] < 65536 && gdims[1] < 65536 && gdims[2] < 65536);
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  bricks_plan *p = new bricks_plan;
+  p->ctx = ctx;
+  p->nbricks = nbricks;
+  size_t ncell = 1;
+  for (int d = 0; d < 3; ++d) {
+    p->gdims[d] = gdims[d];
+    ncell *= gdims[d];
+  }
+  for (size_t c = 0; c < ncell; ++c) BRK_ARG(grid_host[c] < nbricks);
+  std::vector<MarchItem> items;
+  std::vector<unsigned> cells;
+  build_items(gdims, nboxes, boxes, items, cells);
+  BRK_ARG(!items.empty());
+  std::vector<unsigned> blist(cells.size());
+  for (size_t n = 0; n < cells.size(); ++n) blist[n] = grid_host[cells[n]];
+
+  cudaStream_t s = ctx->streams[BRICKS_STREAM_COMPUTE];
+  BRK_CUDA(cudaMalloc(&p->grid_dev, ncell * sizeof(unsigned)));
+  BRK_CUDA(cudaMalloc(&p->adj_dev, (size_t)nbricks * 27 * sizeof(unsigned)));
+  BRK_CUDA(cudaMalloc(&p->items_dev, items.size() * sizeof(MarchItem)));
+  BRK_CUDA(cudaMalloc(&p->blist_dev, blist.size() * sizeof(unsigned)));
+  BRK_CUDA(cudaMemcpyAsync(p->grid_dev, grid_host, ncell * sizeof(unsigned), cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaMemcpyAsync(p->adj_dev, adj_host, (size_t)nbricks * 27 * sizeof(unsigned),
+                           cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaMemcpyAsync(p->items_dev, items.data(), items.size() * sizeof(MarchItem),
+                           cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaMemcpyAsync(p->blist_dev, blist.data(), blist.size() * sizeof(unsigned),
+                           cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaStreamSynchronize(s)); /* host vectors die here */
+  p->nitems = (int)items.size();
+  p->nlist = (long)blist.size();
+  *out = p;
+  return 0;
+}
+
+int bricks_plan_destroy(bricks_plan *p) {
+  if (!p) return 0;
+  cudaSetDevice(p->ctx->device);
+  cudaFree(p->grid_dev);
+  cudaFree(p->adj_dev);
+  cudaFree(p->items_dev);
+  cudaFree(p->blist_dev);
+  for (auto &kv : p->fields) cudaFree(kv.second);
+  delete p;
+  return 0;
+}
+
+int bricks_plan_device_tables(const bricks_plan *p, const unsigned **adj_dev, const unsigned **grid_dev) {
+  BRK_ARG(p);
+  if (adj_dev) *adj_dev = p->adj_dev;
+  if (grid_dev) *grid_dev = p->grid_dev;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,273 @@
+// The marching stencil kernels and their launcher (bricks_stencil).
+// Replaces the generated bodies of `brick(ST_SCRTPT, "CUDA", (8,8,8), (4,8), b)` inside
+// brick_kernel (weak/main.cu:35-43, strong/main.cu:85-111) and d3pt7_brick_trans
+// (stencils/3axis.cu:28-37).  See march_dev.cuh for the work decomposition.
+#include <cstdlib>
+#include <cstring>
+
+#include "march_steps.cuh"
+
+namespace {
+
+struct MarchParams {
+  const MarchItem *items;
+  const unsigned *grid;
+  const unsigned *adj;
+  const FieldDev *fields;
+  unsigned gd0, gd1;
+  double c[10];
+};
+
+template <int R, bool CUBE, int VAR, int P>
+__global__ void __launch_bounds__(32) march_kernel(const __grid_constant__ MarchParams prm) {
+  using L = dev::StageLayout<R, CUBE, P>;
+  constexpr int H = 8 / P;
+  extern __shared__ __align__(1024) char smem[];
+  const int lane = threadIdx.x;
+  const MarchItem it = prm.items[blockIdx.x];
+  const FieldDev &fd = prm.fields[blockIdx.y];
+  const int nk = it.nk, nsteps = nk * H + 2;
+
+  const uint32_t smem0 = dev::smem_u32(smem);
+  if ((smem0 & 511u) != 0) __trap(); /* swizzled centre pieces need 512-byte alignment */
+  const uint32_t bar0 = smem0 + 2 * L::BYTES;
+  if (lane == 0) {
+    dev::mbar_init(bar0, 1);
+    dev::mbar_init(bar0 + 8, 1);
+    dev::fence_barrier_init();
+    dev::fence_proxy_async();
+  }
+  __syncwarp();
+
+  /* brick ids of the column: lane t holds layer t */
+  unsigned col0 = 0, col1 = 0;
+  if (lane < nk) {
+    const size_t cell = ((size_t)(it.gk0 + lane) * prm.gd1 + it.gj) * prm.gd0 + it.gi;
+    col0 = prm.grid[cell];
+    col1 = it.valid1 ? prm.grid[cell + 1] : prm.adj[(size_t)col0 * 27 + 14];
+  }
+
+  dev::LaneK<R, CUBE, P> lk;
+  lk.init(lane);
+  const dev::PieceK pk = dev::piece_of<R, CUBE, P>(lane < 12 ? lane : 0);
+  constexpr int MAIN_PLANE_BYTES =
+      2 * L::C_PL + 2 * L::I_PL + 4 * L::J_PL + (CUBE ? 4 * L::X_PL : 0);
+  constexpr int ROLL_PLANE_BYTES = CUBE ? MAIN_PLANE_BYTES : 2 * L::C_PL;
+
+  auto step_layer = [&](int s, int &dk) -> int {
+    if (s == 0) { dk = -1; return 0; }
+    if (s == nsteps - 1) { dk = +1; return nk - 1; }
+    dk = 0;
+    return (s - 1) / H;
+  };
+  /* neighbour brick that lane's piece of stage s is cut from */
+  auto load_nb = [&](int s) -> unsigned {
+    int dk;
+    const int layer = step_layer(s, dk);
+    const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
+    const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
+    const unsigned rowb = pk.useb1 ? b1 : b0;
+    unsigned nb = 0;
+    if (lane < 12) nb = prm.adj[(size_t)rowb * 27 + (dk + 1) * 9 + (pk.dj + 1) * 3 + (pk.di + 1)];
+    return nb;
+  };
+  auto issue = [&](int s, unsigned nb) {
+    const bool roll = (s == 0) || (s == nsteps - 1);
+    const uint32_t bar = bar0 + 8 * (s & 1);
+    const uint32_t dst = smem0 + (s & 1) * L::BYTES + pk.off;
+    const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
+    if (lane == 0) dev::mbar_expect_tx(bar, roll ? R * ROLL_PLANE_BYTES : P * MAIN_PLANE_BYTES);
+    const int np = roll ? L::NPIECE_ROLL : L::NPIECE_MAIN;
+    if (lane < np)
+      dev::tma_load_4d(dst, roll ? &fd.maps.roll[pk.map] : &fd.maps.main[pk.map], pk.ci, pk.cj, ck,
+                       (int)nb, bar);
+  };
+
+  double carry[2 * R][4];
+#pragma unroll
+  for (int a = 0; a < 2 * R; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) carry[a][m] = 0.0;
+
+  dev::OutPtrs o;
+  o.cur = o.prev = nullptr;
+  o.curv = o.prevv = false;
+  const int lane_off = lk.j * 8 + lk.ih * 4;
+
+  unsigned nbn = load_nb(0);
+  issue(0, nbn);
+  nbn = load_nb(1);
+
+  for (int s = 0; s < nsteps; ++s) {
+    if (s + 1 < nsteps) {
+      dev::fence_proxy_async();
+      issue(s + 1, nbn);
+      if (s + 2 < nsteps) nbn = load_nb(s + 2);
+    }
+    dev::mbar_wait(bar0 + 8 * (s & 1), (s >> 1) & 1);
+    const char *st = smem + (s & 1) * L::BYTES;
+    int mode = 1, zbase = 0;
+    if (s == 0) {
+      mode = 0;
+    } else if (s == nsteps - 1) {
+      mode = 2;
+      zbase = 8;
+    } else {
+      const int layer = (s - 1) / H, half = (s - 1) % H;
+      zbase = half * P;
+      if (half == 0) {
+        const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
+        const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
+        o.prev = o.cur;
+        o.prevv = o.curv && layer > 0;
+        o.cur = fd.out + (size_t)(lk.bb ? b1 : b0) * fd.out_step + lane_off;
+        o.curv = (lk.bb == 0) || (it.valid1 != 0);
+      }
+    }
+    if constexpr (CUBE) {
+      if (mode == 1)
+        dev::cube_step<P, P, 1>(st, lk, prm.c, carry, o, zbase);
+      else if (mode == 0)
+        dev::cube_step<P, R, 0>(st, lk, prm.c, carry, o, zbase);
+      else
+        dev::cube_step<P, R, 2>(st, lk, prm.c, carry, o, zbase);
+    } else {
+      if (mode == 1)
+        dev::star_step<R, VAR, P, P, 1>(st, lk, prm.c, carry, o, zbase);
+      else if (mode == 0)
+        dev::star_step<R, VAR, P, R, 0>(st, lk, prm.c, carry, o, zbase);
+      else
+        dev::star_step<R, VAR, P, R, 2>(st, lk, prm.c, carry, o, zbase);
+    }
+    __syncwarp();
+  }
+}
+
+template <int R, bool CUBE, int VAR, int P>
+int launch(bricks_plan *plan, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
+  using L = dev::StageLayout<R, CUBE, P>;
+  const int smem = 2 * L::BYTES + 64;
+  auto kern = march_kernel<R, CUBE, VAR, P>;
+  static bool configured[64] = {false};
+  bool &done = configured[plan->ctx->device & 63];
+  if (!done) {
+    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    done = true;
+  }
+  MarchParams prm;
+  prm.items = plan->items_dev;
+  prm.grid = plan->grid_dev;
+  prm.adj = plan->adj_dev;
+  prm.fields = fields;
+  prm.gd0 = plan->gdims[0];
+  prm.gd1 = plan->gdims[1];
+  for (int i = 0; i < 10; ++i) prm.c[i] = c[i];
+  kern<<<dim3(plan->nitems, nfields), 32, smem, s>>>(prm);
+  BRK_CUDA(cudaGetLastError());
+  ++bricks::g_launches;
+  return 0;
+}
+
+int planes_per_stage() {
+  static int p = 0;
+  if (!p) {
+    const char *e = getenv("BRICKS_PLANES");
+    p = (e && atoi(e) == 8) ? 8 : 4;
+  }
+  return p;
+}
+
+/* build (or find) the device FieldDev array for these storages and this kernel variant */
+int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const double *const *in,
+               double *const *out, size_t in_step, size_t out_step, cudaStream_t s,
+               const FieldDev **dev_out) {
+  FieldKey key;
+  key.variant = stencil_id * 16 + P;
+  key.in_step = in_step;
+  key.out_step = out_step;
+  for (int f = 0; f < nfields; ++f) {
+    key.ptrs.push_back(in[f]);
+    key.ptrs.push_back(out[f]);
+  }
+  auto itf = plan->fields.find(key);
+  if (itf != plan->fields.end()) {
+    *dev_out = itf->second;
+    return 0;
+  }
+  const int R = stencil_id == 13 || stencil_id == 125 ? 2 : (stencil_id == 25 ? 4 : 1);
+  const bool cube = stencil_id == 125;
+  const int HW = R > 2 ? 4 : 2;
+  std::vector<FieldDev> host(nfields);
+  for (int f = 0; f < nfields; ++f) {
+    FieldDev &fd = host[f];
+    memset(&fd, 0, sizeof fd);
+    fd.out = out[f];
+    fd.out_step = out_step;
+    for (int roll = 0; roll < 2; ++roll) {
+      CUtensorMap *m = roll ? fd.maps.roll : fd.maps.main;
+      const unsigned pk = roll ? R : P;
+      int rc = bricks::encode_map(&m[0], in[f], plan->nbricks, in_step, 8, 8, pk, true);
+      if (!rc) rc = bricks::encode_map(&m[1], in[f], plan->nbricks, in_step, HW, 8, pk, false);
+      if (!rc) rc = bricks::encode_map(&m[2], in[f], plan->nbricks, in_step, 8, R, pk, false);
+      if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false);
+      if (rc) return rc;
+    }
+  }
+  FieldDev *d = nullptr;
+  BRK_CUDA(cudaMalloc(&d, sizeof(FieldDev) * nfields));
+  BRK_CUDA(cudaMemcpyAsync(d, host.data(), sizeof(FieldDev) * nfields, cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaStreamSynchronize(s)); /* `host` dies at return; first use only */
+  plan->fields[key] = d;
+  *dev_out = d;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, const double *const *in,
+                              double *const *out, size_t in_step, size_t out_step,
+                              const double *coeff_host, int stream) {
+  BRK_ARG(plan && in && out && nfields > 0 && nfields < 65536);
+  BRK_ARG(stream >= 0 && stream < bricks::kNumStreams);
+  BRK_ARG(in_step >= 512 && in_step % 2 == 0 && out_step >= 512 && out_step % 4 == 0);
+  for (int f = 0; f < nfields; ++f) {
+    BRK_ARG(in[f] && out[f] && in[f] != out[f]);
+    BRK_ARG(((uintptr_t)in[f] & 15) == 0 && ((uintptr_t)out[f] & 31) == 0);
+  }
+  BRK_CUDA(cudaSetDevice(plan->ctx->device));
+  cudaStream_t s = plan->ctx->streams[stream];
+  const int P = planes_per_stage();
+  const FieldDev *fields = nullptr;
+  int rc = get_fields(plan, stencil_id, P, nfields, in, out, in_step, out_step, s, &fields);
+  if (rc) return rc;
+  double c[10] = {0};
+  switch (stencil_id) {
+    case BRICKS_ST_7PT_COEFF:
+      BRK_ARG(coeff_host);
+      for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
+      return P == 8 ? launch<1, false, 1, 8>(plan, fields, nfields, c, s)
+                    : launch<1, false, 1, 4>(plan, fields, nfields, c, s);
+    case BRICKS_ST_7PT: /* MPI_ALPHA, MPI_BETA (stencils/fake.h:11-12) */
+      c[0] = 0.4, c[1] = 0.1;
+      return P == 8 ? launch<1, false, 0, 8>(plan, fields, nfields, c, s)
+                    : launch<1, false, 0, 4>(plan, fields, nfields, c, s);
+    case BRICKS_ST_13PT: /* MPI_B0..B2 (fake.h:20-22) */
+      c[0] = 0.4, c[1] = 0.07, c[2] = 0.03;
+      return P == 8 ? launch<2, false, 0, 8>(plan, fields, nfields, c, s)
+                    : launch<2, false, 0, 4>(plan, fields, nfields, c, s);
+    case BRICKS_ST_25PT: /* MPI_A0..A4 (fake.h:14-18) */
+      c[0] = 0.1, c[1] = 0.06, c[2] = 0.045, c[3] = 0.03, c[4] = 0.015;
+      return P == 8 ? launch<4, false, 0, 8>(plan, fields, nfields, c, s)
+                    : launch<4, false, 0, 4>(plan, fields, nfields, c, s);
+    case BRICKS_ST_125PT: { /* MPI_C0..C9 (fake.h:24-33) */
+      const double cc[10] = {0.1, 0.04, 0.03, 0.01, 0.006, 0.004, 0.005, 0.002, 0.003, 0.001};
+      for (int i = 0; i < 10; ++i) c[i] = cc[i];
+      return P == 8 ? launch<2, true, 0, 8>(plan, fields, nfields, c, s)
+                    : launch<2, true, 0, 4>(plan, fields, nfields, c, s);
+    }
+    default:
+      bricks::set_error("unknown stencil id %d", stencil_id);
+      return -1;
+  }
+}
