@@ -10,11 +10,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libbricks_b200.so")
-SOURCES = ["context.cu", "plan.cu", "stencil_march.cu", "stencil_naive.cu", "exchange.cu", "probe.cu"]
+SOURCES = ["context.cu", "plan.cu", "stencil_march.cu", "stencil_naive.cu", "exchange.cu", "probe.cu",
+           "host_capi.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "-Xcompiler", "-Wno-unused-function",
-         "--expt-relaxed-constexpr", "-ccbin", "/usr/bin/g++"]
+         "--expt-relaxed-constexpr", "-ccbin", "/usr/bin/g++", "-Xcompiler", "-fopenmp"]
 
 
 def _stale(target, deps):
@@ -29,12 +30,13 @@ def build(verbose=False, force=False, ptxas_v=False):
     objdir = os.path.join(LIBDIR, "obj")
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
-    headers += [os.path.join(HERE, "..", "include", f) for f in os.listdir(os.path.join(HERE, "..", "include"))]
+    for root, _, files in os.walk(os.path.join(HERE, "..", "include")):
+        headers += [os.path.join(root, f) for f in files]
     objs = []
     procs = []
     for src in SOURCES:
         s = os.path.join(CSRC, src)
-        o = os.path.join(objdir, src.replace(".cu", ".o"))
+        o = os.path.join(objdir, os.path.splitext(src)[0] + ".o")
         objs.append(o)
         if force or _stale(o, [s] + headers):
             cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if ptxas_v else []) + ["-c", s, "-o", o]
@@ -51,10 +53,10 @@ def build(verbose=False, force=False, ptxas_v=False):
             print("nvcc failed on %s" % src)
     if failed:
         raise RuntimeError("libbricks_b200 build failed")
-    if force or _stale(LIB, objs):
+    if force or _stale(LIB, objs + [os.path.join(CSRC, "exports.map")]):
         # cudart static; NCCL resolved at load time (torch's bundled libnccl.so.2 when torch is
         # imported first, else the system one)
-        cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lnccl", "-ccbin", "/usr/bin/g++",
+        cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lnccl", "-lgomp", "-Xlinker", "--version-script=" + os.path.join(CSRC, "exports.map"), "-ccbin", "/usr/bin/g++",
                                                      "-gencode", "arch=compute_100a,code=sm_100a"]
         if verbose:
             print(" ".join(cmd))

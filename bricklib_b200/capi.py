@@ -78,7 +78,7 @@ def lib():
         if not os.path.exists(LIBPATH):
             raise BricksError("libbricks_b200.so is not built (run __graft_entry__.build()); "
                               "there is no CPU fallback")
-        L = C.CDLL(LIBPATH, mode=C.RTLD_GLOBAL)
+        L = C.CDLL(LIBPATH)
         for name, (res, args) in _SIGS.items():
             fn = getattr(L, name)
             fn.restype = res
@@ -288,4 +288,144 @@ def probe_mio(ctx, mode):
 def probe_tma_image(ctx, field_dev, nbricks, step, b):
     out = np.zeros(512, np.float64)
     check(lib().bricks_probe_tma_image(ctx._h, C.c_void_p(field_dev), nbricks, step, b, _np_ptr(out)))
+    return out
+
+
+# ---------------------------------------------------------------------------
+# host templates through include/bricks_b200_host.h (no device involved)
+REGION_DT = np.dtype([("neighbor", np.uint64), ("skin_st", np.uint32), ("skin_ed", np.uint32),
+                      ("pos", np.uint32), ("len", np.uint32), ("first_pad", np.uint32),
+                      ("last_pad", np.uint32)], align=True)
+SKIN_GOOD, SKIN_NORMAL, SKIN_BAD = 0, 1, 2
+
+_SIGS.update({
+    "bricks_decomp_create": (C.c_int, [_vp, C.c_uint, C.c_int, _vpp]),
+    "bricks_decomp_destroy": (C.c_int, [_vp]),
+    "bricks_decomp_sizes": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "bricks_decomp_tables": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "bricks_decomp_rank_map": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "bricks_decomp_exchange_plan": (C.c_int, [_vp, C.c_size_t, _vp, _vp, _vp, _vp, _vp]),
+    "bricks_init_grid3": (C.c_int, [_vp, _vp, _vp]),
+    "bricks_copy_brick3": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp, C.c_uint]),
+    "bricks_compare_brick3": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp, C.c_uint, _vp, _vp]),
+    "bricks_cart_dims": (C.c_int, [C.c_int, C.c_int, _vp]),
+    "bricks_cart_rank": (C.c_int, [C.c_int, _vp, _vp, _vp]),
+    "bricks_cart_coords": (C.c_int, [C.c_int, _vp, C.c_int, _vp]),
+    "bricks_zmort3": (C.c_ulong, [C.c_ulong, C.c_ulong, C.c_ulong]),
+    "bricks_zmort3_coord": (C.c_ulong, [C.c_ulong, C.c_ulong]),
+    "bricks_zmort3_set": (C.c_ulong, [C.c_ulong, C.c_ulong, C.c_ulong]),
+    "bricks_uniform_fill": (C.c_int, [_vp, C.c_size_t, C.c_uint64, C.c_uint64]),
+})
+
+
+class Decomp(object):
+    """BrickDecomp<3,8,8,8>(dims, depth).initialize(skin3d_*) -- the product's own C++
+    template (include/bricks/brick-decomp.h), reached through bricks_decomp_*."""
+
+    def __init__(self, dims, depth=8, skin=SKIN_GOOD):
+        L = lib()
+        d = np.asarray(dims, np.uint32)
+        self._h = C.c_void_p()
+        check(L.bricks_decomp_create(_np_ptr(d), depth, skin, C.byref(self._h)))
+        self.dims = tuple(int(x) for x in dims)
+        self.depth = depth
+        nb, nr, ns = C.c_uint(), C.c_int(), C.c_int()
+        self.sep_pos = np.zeros(3, np.uint32)
+        gd = np.zeros(3, np.uint32)
+        check(L.bricks_decomp_sizes(self._h, C.byref(nb), _np_ptr(self.sep_pos), _np_ptr(gd), C.byref(nr), C.byref(ns)))
+        self.nbricks, self.nregions = nb.value, nr.value
+        self.gdims = tuple(int(x) for x in gd)  # contiguous axis first
+        grid = np.zeros(int(gd[0]) * int(gd[1]) * int(gd[2]), np.uint32)
+        self.adj = np.zeros((self.nbricks, 27), np.uint32)
+        self.ghost = np.zeros(nr.value, REGION_DT)
+        self.skin = np.zeros(nr.value, REGION_DT)
+        self.skin_size = np.zeros(ns.value, np.int64)
+        assert REGION_DT.itemsize == 32
+        check(L.bricks_decomp_tables(self._h, _np_ptr(grid), _np_ptr(self.adj), _np_ptr(self.ghost),
+                                     _np_ptr(self.skin), _np_ptr(self.skin_size)))
+        self.grid = grid.reshape(int(gd[2]), int(gd[1]), int(gd[0]))
+
+    def rank_map(self, procdims, coo):
+        """populate(): {direction set: rank} on the periodic process grid `procdims`."""
+        keys, ranks = np.zeros(27, np.uint64), np.zeros(27, np.int32)
+        pd, cc = np.asarray(procdims, np.int32), np.asarray(coo, np.int32)
+        check(lib().bricks_decomp_rank_map(self._h, _np_ptr(pd), _np_ptr(cc), _np_ptr(keys), _np_ptr(ranks)))
+        return {int(k): int(r) for k, r in zip(keys, ranks)}
+
+    def exchange_plan(self, step=512):
+        """(recv_off, send_off, nbytes, recv_peer, send_peer) of BrickDecomp::exchange for the
+        rank map set by the last rank_map() call."""
+        n = self.nregions
+        ro, so, nb = (np.zeros(n, np.uint64) for _ in range(3))
+        rp, sp = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        check(lib().bricks_decomp_exchange_plan(self._h, step, _np_ptr(ro), _np_ptr(so), _np_ptr(nb),
+                                                _np_ptr(rp), _np_ptr(sp)))
+        return ro, so, nb, rp, sp
+
+    def close(self):
+        if self._h:
+            lib().bricks_decomp_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def init_grid(dimlist):
+    """init_grid<3>: (grid[k][j][i], adj) with identity numbering (bricksetup.h:73-90)."""
+    d = np.asarray(dimlist, np.int64)
+    n = int(d[0] * d[1] * d[2])
+    grid, adj = np.zeros(n, np.uint32), np.zeros((n, 27), np.uint32)
+    check(lib().bricks_init_grid3(_np_ptr(d), _np_ptr(grid), _np_ptr(adj)))
+    return grid.reshape(int(d[2]), int(d[1]), int(d[0])), adj
+
+
+def copy_brick(to_brick, dimlist, padding, ghost, arr, grid, bdat, adj, step=512):
+    """copyToBrick<3> / copyFromBrick<3> between a padded array and row-major bricks."""
+    d, p, g = (np.asarray(x, np.int64) for x in (dimlist, padding, ghost))
+    grid = np.ascontiguousarray(grid, np.uint32)
+    adj = np.ascontiguousarray(adj, np.uint32)
+    assert arr.flags["C_CONTIGUOUS"] and bdat.flags["C_CONTIGUOUS"]
+    check(lib().bricks_copy_brick3(1 if to_brick else 0, _np_ptr(d), _np_ptr(p), _np_ptr(g), _np_ptr(arr),
+                                   _np_ptr(grid), _np_ptr(bdat), step, _np_ptr(adj), adj.shape[0]))
+
+
+def compare_brick(dimlist, padding, ghost, arr, grid, bdat, adj, step=512):
+    """(compareBrick verdict at BRICK_TOLERANCE, strict max relative error)."""
+    d, p, g = (np.asarray(x, np.int64) for x in (dimlist, padding, ghost))
+    grid = np.ascontiguousarray(grid, np.uint32)
+    adj = np.ascontiguousarray(adj, np.uint32)
+    m, r = C.c_int(), C.c_double()
+    check(lib().bricks_compare_brick3(_np_ptr(d), _np_ptr(p), _np_ptr(g), _np_ptr(arr), _np_ptr(grid),
+                                      _np_ptr(bdat), step, _np_ptr(adj), adj.shape[0], C.byref(m), C.byref(r)))
+    return bool(m.value), r.value
+
+
+def cart_dims(nranks, ndims=3):
+    out = np.zeros(ndims, np.int32)
+    check(lib().bricks_cart_dims(nranks, ndims, _np_ptr(out)))
+    return [int(x) for x in out]
+
+
+def cart_coords(rank, dims):
+    d = np.asarray(dims, np.int32)
+    out = np.zeros(len(dims), np.int32)
+    check(lib().bricks_cart_coords(len(dims), _np_ptr(d), rank, _np_ptr(out)))
+    return [int(x) for x in out]
+
+
+def cart_rank(coo, dims):
+    d, c = np.asarray(dims, np.int32), np.asarray(coo, np.int32)
+    r = C.c_int()
+    check(lib().bricks_cart_rank(len(dims), _np_ptr(d), _np_ptr(c), C.byref(r)))
+    return r.value
+
+
+def uniform(n, seed=0, start=0):
+    """randomArray(list, seed) of include/bricks/multiarray.h (== bricklib_b200.synth.uniform)."""
+    out = np.empty(n, np.float64)
+    check(lib().bricks_uniform_fill(_np_ptr(out), n, seed, start))
     return out

@@ -1,0 +1,76 @@
+/*
+ * bricks_b200_host.h -- flat C window onto the C++ host templates of include/bricks/.
+ *
+ * The drop-in host API is C++ (Brick / BrickInfo / BrickStorage, BrickDecomp, init_grid,
+ * copyToBrick ...: include/bricks/*.h, mirroring the reference's include/brick.h,
+ * bricksetup.h and brick-mpi.h).  Harnesses that are not C++ (bench.py, the pytest parity
+ * tests) reach the SAME code through these wrappers, instantiated for 3-D 8x8x8 fp64 bricks
+ * -- so the tables the GPU path runs on come from the product's own BrickDecomp, never from
+ * the oracle.  Host-only: nothing here touches a device.
+ */
+#ifndef BRICKS_B200_HOST_H
+#define BRICKS_B200_HOST_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bricks_decomp bricks_decomp;
+
+/* BrickDecomp<3,8,8,8>::g_region (include/brick-mpi.h:183-191) flattened */
+typedef struct {
+  uint64_t neighbor;
+  unsigned skin_st, skin_ed, pos, len, first_pad, last_pad;
+} bricks_region;
+
+enum { BRICKS_SKIN_GOOD = 0, BRICKS_SKIN_NORMAL = 1, BRICKS_SKIN_BAD = 2 };
+
+/* BrickDecomp<3,8,8,8>(dims, depth).initialize(skin3d_*)  -- brick-mpi.h:304-460.
+ * dims in elements, contiguous axis first. */
+int bricks_decomp_create(const unsigned dims[3], unsigned depth, int skin_kind, bricks_decomp **out);
+int bricks_decomp_destroy(bricks_decomp *d);
+/* gdims = brick-grid extent including ghost bricks, contiguous axis first */
+int bricks_decomp_sizes(const bricks_decomp *d, unsigned *nbricks, unsigned sep_pos[3], unsigned gdims[3],
+                        int *nregions, int *nskin);
+/* any output may be NULL.  grid: gdims[2]*gdims[1]*gdims[0] cells, i fastest; adj: nbricks*27 */
+int bricks_decomp_tables(const bricks_decomp *d, unsigned *grid, unsigned *adj, bricks_region *ghost,
+                         bricks_region *skin, long *skin_size);
+/* populate(cart, decomp, 0, 1, coo) on a periodic procdims grid (brick-mpi.h:730-753);
+ * keys/ranks in allneighbors() order, 27 entries */
+int bricks_decomp_rank_map(bricks_decomp *d, const int procdims[3], const int coo[3], uint64_t keys[27],
+                           int ranks[27]);
+/* byte offsets / sizes / peers of BrickDecomp::exchange (brick-mpi.h:466-495) for a storage of
+ * `step` elements per brick, using the rank map of the last bricks_decomp_rank_map call;
+ * arrays of nregions entries: the arguments of bricks_exchange_create */
+int bricks_decomp_exchange_plan(bricks_decomp *d, size_t step, size_t *recv_off, size_t *send_off,
+                                size_t *nbytes, int *recv_peer, int *send_peer);
+
+/* init_grid<3> (bricksetup.h:73-90): grid[n0*n1*n2], adj[n0*n1*n2][27] */
+int bricks_init_grid3(const long dimlist[3], unsigned *grid, unsigned *adj);
+/* copyToBrick<3> (to_brick != 0) / copyFromBrick<3> (bricksetup.h:172-221) on row-major bricks */
+int bricks_copy_brick3(int to_brick, const long dimlist[3], const long padding[3], const long ghost[3],
+                       double *arr, const unsigned *grid, double *brick_dat, size_t step, const unsigned *adj,
+                       unsigned nbricks);
+/* compareBrick<3> (brickcompare.h:30-57): *match = 1 when within BRICK_TOLERANCE; *max_rel = the
+ * strict measure max |brick-arr| / |arr| */
+int bricks_compare_brick3(const long dimlist[3], const long padding[3], const long ghost[3], double *arr,
+                          const unsigned *grid, double *brick_dat, size_t step, const unsigned *adj,
+                          unsigned nbricks, int *match, double *max_rel);
+/* MPI_Dims_create / MPI_Cart_rank / MPI_Cart_coords equivalents (weak/args.cpp:105-115) */
+int bricks_cart_dims(int nranks, int ndims, int *dims);
+int bricks_cart_rank(int ndims, const int *dims, const int *coo, int *rank);
+int bricks_cart_coords(int ndims, const int *dims, int rank, int *coo);
+/* ZMORT()[c0][c1][c2] and its inverse (include/zmort.h:18-105) */
+unsigned long bricks_zmort3(unsigned long c0, unsigned long c1, unsigned long c2);
+unsigned long bricks_zmort3_coord(unsigned long id, unsigned long d);
+unsigned long bricks_zmort3_set(unsigned long id, unsigned long d, unsigned long p);
+/* randomArray(list, seed) of include/bricks/multiarray.h: n doubles from element `start` */
+int bricks_uniform_fill(double *out, size_t n, uint64_t seed, uint64_t start);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BRICKS_B200_HOST_H */

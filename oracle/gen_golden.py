@@ -1,0 +1,106 @@
+"""oracle/gen_golden.py -- TEST INFRASTRUCTURE, not product code.
+
+Generates tests/golden/* from the UNMODIFIED reference compiled into oracle/_ref by
+oracle/Makefile (BrickDecomp::initialize / populate of include/brick-mpi.h, the codegen
+brick kernels of stencils/*.py and the ST_CPU array forms of stencils/fake.h).  Run it in
+the build container, where /root/reference exists:
+
+    make -C oracle all && python oracle/gen_golden.py
+
+The fixtures pin the oracle (tests/test_oracle_golden.py) and, through it, the CUDA path.
+Inputs are not stored: they are a pure function of the element index
+(bricklib_b200/synth.py), so every machine regenerates them bit for bit.
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, ".."))
+from bricklib_b200 import synth  # noqa: E402
+from oracle import refload as R  # noqa: E402
+
+GOLDEN = os.path.join(HERE, "..", "tests", "golden")
+STENCILS = (0, 7, 13, 25, 125)
+DECOMP_DIMS = [(16, 16, 16), (32, 16, 24), (64, 64, 64), (128, 128, 128), (512, 512, 512)]
+RANK_CASES = [((1, 1, 1), (0, 0, 0)), ((2, 1, 1), (1, 0, 0)), ((2, 2, 1), (0, 1, 0)),
+              ((2, 2, 2), (0, 1, 1)), ((2, 2, 2), (1, 0, 1)), ((3, 2, 1), (2, 1, 0))]
+STENCIL_DIMS = [(16, 16, 16), (16, 24, 32)]
+
+
+def fnv1a64(values):
+    """FNV-1a over a stream of integers, one value per step."""
+    h = 0xCBF29CE484222325
+    for v in np.asarray(values).reshape(-1).tolist():
+        h ^= int(v)
+        h = (h * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+    return "%016x" % h
+
+
+def decomp_record(dims):
+    ref = R.RefDecomp(dims, 8)
+    rec = {"dims": list(dims), "gz": 8, "nbricks": int(ref.nbricks),
+           "sep_pos": [int(x) for x in ref.sep_pos],
+           "skin_size": [int(x) for x in ref.skin_size],
+           "adj_fnv": fnv1a64(ref.adj), "grid_fnv": fnv1a64(ref.grid)}
+    for name in ("ghost", "skin"):
+        rec[name] = {k: [int(x) for x in v] for k, v in ref.regions[name].items()}
+    rec["rank_map"] = []
+    for procdims, coo in RANK_CASES:
+        rm = ref.rank_map(procdims, coo)
+        rec["rank_map"].append({"procdims": list(procdims), "coo": list(coo),
+                                "map": {"%x" % k: v for k, v in sorted(rm.items())}})
+    ref.close()
+    return rec
+
+
+def stencil_fixture(dims):
+    """Reference outputs on one decomposed subdomain: codegen brick kernel over every grid
+    brick (stored for the interior bricks only, the region the reference itself compares),
+    and the ST_CPU array form over the interior of the matching padded array."""
+    ref = R.RefDecomp(dims, 8)
+    nb = ref.nbricks
+    inp = synth.uniform(nb * 512, seed=11)
+    coeff = synth.coefficients()
+    blist = ref.grid.reshape(-1)
+    t = ref.grid.shape  # (tk, tj, ti) brick grid incl. ghost
+    interior = ref.grid[1:-1, 1:-1, 1:-1].reshape(-1)
+    out = {"dims": np.array(dims), "interior_bricks": interior.astype(np.uint32)}
+    # padded array twin of the same field: element (k,j,i) of the (dims+16)^3 region
+    arr = np.zeros((t[0] * 8, t[1] * 8, t[2] * 8))
+    field = inp.reshape(nb, 8, 8, 8)
+    for bk in range(t[0]):
+        for bj in range(t[1]):
+            for bi in range(t[2]):
+                arr[bk * 8:bk * 8 + 8, bj * 8:bj * 8 + 8, bi * 8:bi * 8 + 8] = field[ref.grid[bk, bj, bi]]
+    for w in STENCILS:
+        cf = coeff if w == 0 else None
+        res = np.zeros(nb * 512)
+        R.brick_sweep_rm(w, ref.adj, blist, inp, res, 512, cf)
+        out["brick_%d" % w] = res.reshape(nb, 512)[interior].copy()
+        aout = np.zeros_like(arr)
+        box = (8, arr.shape[0] - 8, 8, arr.shape[1] - 8, 8, arr.shape[2] - 8)
+        R.array_sweep(w, arr, aout, box, cf)
+        out["array_%d" % w] = aout[8:-8, 8:-8, 8:-8].copy()
+    ref.close()
+    return out
+
+
+def main():
+    os.makedirs(GOLDEN, exist_ok=True)
+    recs = [decomp_record(d) for d in DECOMP_DIMS]
+    meta = {"generator": "oracle/gen_golden.py", "source": "oracle/_ref/libref_%s.so" % R.host_isa(),
+            "vsvec": R.vsvec(), "decomp": recs}
+    with open(os.path.join(GOLDEN, "decomp.json"), "w") as f:
+        json.dump(meta, f, indent=0, separators=(",", ":"))
+    for d in STENCIL_DIMS:
+        fx = stencil_fixture(d)
+        np.savez(os.path.join(GOLDEN, "stencil_%dx%dx%d.npz" % d), **fx)
+    for fn in sorted(os.listdir(GOLDEN)):
+        print(fn, os.path.getsize(os.path.join(GOLDEN, fn)))
+
+
+if __name__ == "__main__":
+    main()

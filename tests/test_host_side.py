@@ -1,0 +1,166 @@
+"""CPU tests of the product's own host code (include/bricks/*.h through the flat wrappers of
+include/bricks_b200_host.h) against the golden tables of the compiled reference and against
+the oracle, plus the check that libbricks_b200.so exports every symbol the headers declare."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, fnv1a64, relerr
+
+
+def _declared_symbols():
+    names = set()
+    for hdr in ("bricks_b200.h", "bricks_b200_host.h", "bricks_b200_probe.h"):
+        text = open(os.path.join(ROOT, "include", hdr)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names |= set(re.findall(r"\b(bricks_[a-z0-9_]+)\s*\(", text))
+    return sorted(names)
+
+
+def test_library_loads_and_exports_every_declared_symbol(built):
+    L = ctypes.CDLL(built.LIBPATH)
+    declared = _declared_symbols()
+    assert len(declared) >= 50
+    missing = [n for n in declared if not hasattr(L, n)]
+    assert not missing, missing
+    # and the ctypes binding covers all of them
+    unbound = [n for n in declared if n not in built._SIGS]
+    assert not unbound, unbound
+
+
+def test_product_path_fails_loudly_without_the_library(built, monkeypatch):
+    monkeypatch.setattr(built, "_lib", None)
+    monkeypatch.setattr(built, "LIBPATH", "/nonexistent/libbricks_b200.so")
+    with pytest.raises(built.BricksError):
+        built.lib()
+
+
+def test_errors_are_reported_not_thrown(built):
+    h = ctypes.c_void_p()
+    rc = built.lib().bricks_decomp_create(None, 8, 0, ctypes.byref(h))
+    assert rc != 0 and built.lib().bricks_last_error()
+    with pytest.raises(built.BricksError):
+        built.Decomp((12, 16, 16), 8)  # not a multiple of the brick size
+    with pytest.raises(built.BricksError):
+        built.Decomp((8, 16, 16), 8)  # smaller than two ghost depths
+
+
+@pytest.mark.parametrize("idx", range(5))
+def test_brickdecomp_is_bit_exact_with_reference(built, golden_decomp, idx):
+    rec = golden_decomp["decomp"][idx]
+    d = built.Decomp(rec["dims"], 8)
+    assert d.nbricks == rec["nbricks"]
+    assert [int(x) for x in d.sep_pos] == rec["sep_pos"]
+    assert [int(x) for x in d.skin_size] == rec["skin_size"]
+    for name, tab in (("ghost", d.ghost), ("skin", d.skin)):
+        for k, v in rec[name].items():
+            assert np.array_equal(tab[k].astype(np.uint64), np.array(v, np.uint64)), (name, k)
+    for case in rec["rank_map"]:
+        assert d.rank_map(case["procdims"], case["coo"]) == {int(k, 16): v for k, v in case["map"].items()}
+    if rec["nbricks"] <= 6000:
+        assert fnv1a64(d.grid) == rec["grid_fnv"]
+        assert fnv1a64(d.adj) == rec["adj_fnv"]
+    d.close()
+
+
+def test_brickdecomp_512_tables_equal_oracle(built, oracle):
+    d = built.Decomp((512, 512, 512), 8)
+    o = oracle.Decomp((512, 512, 512), 8)
+    assert np.array_equal(d.grid, o.grid) and np.array_equal(d.adj, o.adj)
+    # the reference drivers' own sanity check (weak/main.cu:102-109): adjacency is symmetric
+    interior = d.grid[1:-1, 1:-1, 1:-1].reshape(-1)
+    for slot in (0, 4, 12, 14, 22, 26):
+        assert np.array_equal(d.adj[d.adj[interior, slot], 26 - slot], interior)
+    d.close()
+
+
+@pytest.mark.parametrize("skin", [0, 1, 2])
+def test_brickdecomp_other_skin_orders_equal_oracle(built, oracle, skin):
+    from oracle import oracle as O
+    lex = [tuple(a * s for a, s in ((1, i), (2, j), (3, k)) if s) for k in (-1, 0, 1) for j in (-1, 0, 1)
+           for i in (-1, 0, 1)]
+    lists = {0: O.SKIN3D_GOOD, 1: lex, 2: None}
+    bad = []
+    for s in lex:
+        if not s:
+            continue
+        if bad:
+            bad.append(())
+        bad.append(s)
+    lists[2] = bad
+    d = built.Decomp((32, 24, 16), 8, skin)
+    o = oracle.Decomp((32, 24, 16), 8, skinlist=lists[skin])
+    assert d.nbricks == o.nbricks and np.array_equal(d.grid, o.grid) and np.array_equal(d.adj, o.adj)
+    for k in o.ghost.dtype.names:
+        assert np.array_equal(d.ghost[k], o.ghost[k]) and np.array_equal(d.skin[k], o.skin[k])
+    d.close()
+
+
+def test_init_grid_and_copy_round_trip(built, oracle):
+    """copy() of the reference (stencils/copy.cpp:32-68): array -> brick -> array is the identity,
+    and init_grid numbering equals the oracle's restatement of bricksetup.h:73-90."""
+    from bricklib_b200 import synth
+    grid, adj = built.init_grid((5, 4, 3))
+    og, oa = oracle.init_grid((5, 4, 3))
+    assert np.array_equal(grid, og) and np.array_equal(adj, oa)
+    # N = 16 interior, GZ = 8 ghost, PADDING = 8: array 48^3, brick grid 4^3 (3axis.cpp:20-30)
+    n, gz, pad = 16, 8, 8
+    sg = n + 2 * gz
+    grid, adj = built.init_grid((sg // 8,) * 3)
+    arr = synth.uniform((sg + 2 * pad) ** 3, seed=9).reshape((sg + 2 * pad,) * 3)
+    bdat = np.zeros(adj.shape[0] * 512)
+    built.copy_brick(True, (sg,) * 3, (pad,) * 3, (0,) * 3, arr, grid, bdat, adj)
+    ob = np.zeros_like(bdat)
+    oracle.copy_brick(True, (sg,) * 3, (pad,) * 3, (0,) * 3, arr, grid, ob)
+    assert np.array_equal(bdat, ob)
+    back = np.zeros_like(arr)
+    built.copy_brick(False, (sg,) * 3, (pad,) * 3, (0,) * 3, back, grid, bdat, adj)
+    assert np.array_equal(back[pad:-pad, pad:-pad, pad:-pad], arr[pad:-pad, pad:-pad, pad:-pad])
+    ok, rel = built.compare_brick((n,) * 3, (pad,) * 3, (gz,) * 3, arr, grid, bdat, adj)
+    assert ok and rel == 0.0
+    bdat[int(grid[2, 1, 1]) * 512 + 7] += 1e-3  # an interior brick
+    ok, rel = built.compare_brick((n,) * 3, (pad,) * 3, (gz,) * 3, arr, grid, bdat, adj)
+    assert not ok and rel > 1e-4
+
+
+def test_cartesian_grid_helpers(built, oracle):
+    for n in (1, 2, 3, 4, 6, 8, 12, 16, 64):
+        assert built.cart_dims(n) == oracle.dims_create(n)
+    dims = [2, 2, 2]
+    for r in range(8):
+        coo = built.cart_coords(r, dims)
+        assert coo == oracle.cart_coords(r, dims)
+        assert built.cart_rank(coo, dims) == r
+    assert built.cart_rank([-1, 2, 5], [2, 2, 2]) == built.cart_rank([1, 0, 1], [2, 2, 2])
+
+
+def test_zmort_known_answers(built):
+    L = built.lib()
+    # last coordinate appended is the least significant bit of each 3-bit group
+    assert L.bricks_zmort3(0, 0, 1) == 1 and L.bricks_zmort3(0, 1, 0) == 2 and L.bricks_zmort3(1, 0, 0) == 4
+    assert L.bricks_zmort3(3, 5, 6) == int("".join(a + b + c for a, b, c in zip("011", "101", "110")), 2)
+    for c in [(0, 0, 0), (7, 2, 5), (13, 200, 31)]:
+        z = L.bricks_zmort3(*c)
+        assert (L.bricks_zmort3_coord(z, 2), L.bricks_zmort3_coord(z, 1), L.bricks_zmort3_coord(z, 0)) == c
+        assert L.bricks_zmort3_set(z, 1, 9) == L.bricks_zmort3(c[0], 9, c[2])
+
+
+def test_exchange_plan_matches_oracle_restatement(built, oracle):
+    """Offsets / sizes / peers handed to bricks_exchange_create equal the restated
+    BrickDecomp::exchange loop (brick-mpi.h:466-495) for every rank of a 2x2x2 grid."""
+    d = built.Decomp((32, 32, 32), 8)
+    o = oracle.Decomp((32, 32, 32), 8)
+    for r in range(8):
+        coo = built.cart_coords(r, [2, 2, 2])
+        d.rank_map([2, 2, 2], coo)
+        ro, so, nb, rp, sp = d.exchange_plan(512)
+        rm = oracle.rank_map([2, 2, 2], coo)
+        for i in range(len(o.ghost)):
+            g, s = o.ghost[i], o.skin[i]
+            assert ro[i] == int(g["pos"]) * 4096 and so[i] == int(s["pos"]) * 4096
+            assert nb[i] == int(g["len"]) * 4096
+            assert rp[i] == rm[int(g["neighbor"])] and sp[i] == rm[int(s["neighbor"])]
+    d.close()
