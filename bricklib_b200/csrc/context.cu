@@ -40,8 +40,13 @@ int bricks_ctx_create(int device, bricks_ctx **out) {
   bricks_ctx *c = new bricks_ctx;
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
+  /* the communication stream outranks the compute stream, so exchange kernels (NCCL, region
+   * copies) get the next free SM slots while a stencil sweep is in flight */
+  int prio_lo = 0, prio_hi = 0;
+  BRK_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
   for (int s = 0; s < kNumStreams; ++s)
-    BRK_CUDA(cudaStreamCreateWithFlags(&c->streams[s], cudaStreamNonBlocking));
+    BRK_CUDA(cudaStreamCreateWithPriority(&c->streams[s], cudaStreamNonBlocking,
+                                          s == BRICKS_STREAM_COMM ? prio_hi : prio_lo));
   BRK_CUDA(cudaEventCreateWithFlags(&c->xev, cudaEventDisableTiming));
   for (int t = 0; t < kNumTimers; ++t) {
     BRK_CUDA(cudaEventCreate(&c->t0[t]));

@@ -1,0 +1,123 @@
+"""Weak-scaling step: one subdomain per GPU, one halo exchange per ST_ITER stencil sweeps.
+
+Host-side mirror of the reference's weak driver hot loop (weak/main.cu:246-287 `brick_func`;
+CPU twin weak/main.cpp:172-213) above the C ABI:
+
+    reference                                   here
+    ---------                                   ----
+    cudaMemcpy D2H skin / MPI / H2D ghost       ExchangeView.start(): NCCL send/recv (or on-device
+    or CUDA-aware bDecomp.exchange()            copies for self neighbours) on the comm stream
+    brick_kernel<<<strideb^3,32>>> x ST_ITER    bricks_stencil over box plans on the compute stream
+
+and two things the reference does not do: (1) the first sweep of a step runs on the bricks that
+do not read ghost data ([2, n-2) cells of the brick grid = the inner-inner region
+[1, sep_pos[0]) of the numbering) WHILE the exchange is in flight, and only its outer shell
+waits for the exchange; (2) the last sweep skips the ghost bricks (the CPU driver's skip=1,
+weak/main.cpp:204-209): their output is never read because the next exchange overwrites it.
+"""
+import numpy as np
+
+from . import capi
+
+
+def shell_boxes(g, inner_lo, inner_hi):
+    """Six disjoint slabs covering [0,g)^3 minus [inner_lo, inner_hi)^3 (i fastest)."""
+    (g0, g1, g2), (a0, a1, a2), (b0, b1, b2) = g, inner_lo, inner_hi
+    return [((0, 0, 0), (g0, g1, a2)), ((0, 0, b2), (g0, g1, g2)),
+            ((0, 0, a2), (g0, a1, b2)), ((0, b1, a2), (g0, g1, b2)),
+            ((0, a1, a2), (a0, b1, b2)), ((b0, a1, a2), (g0, b1, b2))]
+
+
+class WeakSubdomain(object):
+    """One rank's subdomain: BrickDecomp tables, two ping-pong storages on the device, the box
+    plans of the sweep schedule and the exchange plan."""
+
+    def __init__(self, ctx, dims, stencil, rank=0, procdims=(1, 1, 1), depth=8, seed=20240601):
+        self.ctx, self.stencil, self.rank = ctx, stencil, rank
+        self.procdims = list(procdims)
+        self.nranks = int(np.prod(procdims))
+        self.dims = tuple(dims)
+        self.dec = capi.Decomp(dims, depth)
+        self.st_iter = capi.ST_ITER[stencil]
+        self.coo = capi.cart_coords(rank, self.procdims)
+        self.rank_map = self.dec.rank_map(self.procdims, self.coo)
+        g = self.dec.gdims
+        gb = depth // 8
+        self.gdims = g
+        nb = self.dec.nbricks
+        self.nbytes = nb * 512 * 8
+        self.d_a = ctx.malloc(self.nbytes)
+        self.d_b = ctx.malloc(self.nbytes)
+        ctx.memset(self.d_a, 0, self.nbytes)
+        ctx.memset(self.d_b, 0, self.nbytes)
+        full = ((0, 0, 0), tuple(g))
+        inner = (tuple(2 * gb for _ in g), tuple(x - 2 * gb for x in g))
+        owned = (tuple(gb for _ in g), tuple(x - gb for x in g))
+        self.plan_full = capi.Plan(ctx, self.dec.grid, self.dec.adj, [full])
+        self.plan_inner = capi.Plan(ctx, self.dec.grid, self.dec.adj, [inner])
+        self.plan_shell = capi.Plan(ctx, self.dec.grid, self.dec.adj, shell_boxes(g, inner[0], inner[1]))
+        self.plan_owned = capi.Plan(ctx, self.dec.grid, self.dec.adj, [owned])
+        ro, so, nbts, rp, sp = self.dec.exchange_plan(512)
+        self.exchange = capi.Exchange(ctx, rank, ro, so, nbts, rp, sp)
+        self.exchange_bytes = int(nbts.sum())
+        self.seed = seed + 1000 * rank
+        self.launches_per_step = None
+
+    # ------------------------------------------------------------------ data
+    def host_field(self):
+        """U[0,1) initial field over every brick of the storage (ghost bricks included; the
+        first exchange overwrites them).  Brick 0, the sentinel, is zero."""
+        f = capi.uniform(self.dec.nbricks * 512, seed=self.seed)
+        f[:512] = 0.0
+        return f
+
+    def upload(self, field):
+        self.ctx.h2d(self.d_a, field)
+        self.ctx.sync()
+
+    def download(self):
+        return self.ctx.download(self.d_a, self.dec.nbricks * 512)
+
+    # ------------------------------------------------------------------ one step
+    def step(self, overlap=True, coeff=None):
+        """exchange(d_a) + ST_ITER ping-pong sweeps; the result ends in d_a (ST_ITER is even).
+        Everything is enqueued asynchronously; returns the number of kernels launched."""
+        C, X = capi.STREAM_COMPUTE, capi.STREAM_COMM
+        n0 = capi.launch_count()
+        ctx, st = self.ctx, self.stencil
+        # the exchange reads the skin written by the previous step's last sweep
+        ctx.stream_wait(X, C)
+        self.exchange.run(self.d_a, X)
+        src, dst = self.d_a, self.d_b
+        for it in range(self.st_iter):
+            last = it == self.st_iter - 1
+            if it == 0:
+                if overlap:
+                    self.plan_inner.stencil(st, src, dst, 512, 512, coeff, C)
+                    ctx.stream_wait(C, X)
+                    self.plan_shell.stencil(st, src, dst, 512, 512, coeff, C)
+                else:
+                    ctx.stream_wait(C, X)
+                    self.plan_full.stencil(st, src, dst, 512, 512, coeff, C)
+            elif last:
+                self.plan_owned.stencil(st, src, dst, 512, 512, coeff, C)
+            else:
+                self.plan_full.stencil(st, src, dst, 512, 512, coeff, C)
+            src, dst = dst, src
+        assert src == self.d_a
+        # NCCL launches its own kernels; count ours plus one per remote exchange
+        self.launches_per_step = capi.launch_count() - n0
+        return self.launches_per_step
+
+    def close(self):
+        for p in (self.plan_full, self.plan_inner, self.plan_shell, self.plan_owned):
+            p.close()
+        self.exchange.close()
+        self.ctx.free(self.d_a)
+        self.ctx.free(self.d_b)
+        self.dec.close()
+
+
+def interior_points(dims, nranks=1):
+    """tot_elems of the reference (weak/args.cpp:107-130): global interior points per sweep."""
+    return int(np.prod(dims)) * nranks
