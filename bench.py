@@ -93,3 +93,275 @@ def cpu_reference_rate(which, budget_s=15.0, dims=(256, 256, 256)):
             "sample": "%d sweeps of the %d-point stencil over one %dx%dx%d subdomain (+ghost bricks), "
                       "reference codegen brick kernel (%s), %.1f ms/sweep" % (reps, which if which else 7, dims[0], dims[1],
                                                                                dims[2], R.vsvec(), t * 1e3)}
+
+
+def run_reference(args, which):
+    """--impl reference: the reference's own CPU implementation of the path (oracle/_ref: its
+    codegen brick kernel under OpenMP, all host threads) on this arm's metric/config; each step
+    is a bounded sample (a 256^3 subdomain) of the workload.  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import oracle as O
+    from oracle import refload as R
+    from bricklib_b200 import capi, synth
+    st_iter = capi.ST_ITER[which]
+    dims = (256, 256, 256)
+    dec = O.Decomp(dims, 8)
+    n = dec.nbricks * 512
+    a, b = R.aligned_empty(n), R.aligned_empty(n)
+    a[:] = synth.uniform(n, seed=1)
+    b[:] = 0.0
+    blist = np.ascontiguousarray(dec.grid.reshape(-1), np.uint32)
+    adjf = np.ascontiguousarray(dec.adj.reshape(-1), np.uint32)
+    sweep = getattr(R.lib(), "ref%d_brick_sweep" % which)
+    # a step = one (self) exchange + ST_ITER sweeps, as weak/main.cpp:172-213 on one rank
+    regions = [((int(g["pos"]) + int(g["first_pad"])) * 512, (int(k["pos"]) + int(k["first_pad"])) * 512,
+                (int(g["len"]) - int(g["first_pad"]) - int(g["last_pad"])) * 512) for g, k in zip(dec.ghost, dec.skin)]
+
+    def step():
+        for d0, s0, cnt in regions:  # BrickDecomp::exchange on one periodic rank: ghost[i] <- skin[i]
+            a[d0:d0 + cnt] = a[s0:s0 + cnt]
+        src, dst = a, b
+        for _ in range(st_iter):  # native fold order of this build: layout does not matter for timing
+            sweep(adjf, dec.nbricks, blist, blist.size, src, dst, 512, None)
+            src, dst = dst, src
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = float(np.prod(dims)) * st_iter / dt * 1e-9
+    line = {"impl": "reference", "metric": "fp64 GStencil/s", "value": val, "unit": "GStencil/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": make_config(which, args.gpus),
+            "cpu_baseline": {"value": val, "unit": "GStencil/s", "cores": R.max_threads(), "kind": "reference",
+                             "sample": "%d steps x (self exchange + %d sweeps) over a 256^3 subdomain, codegen brick "
+                                       "kernel %s under OpenMP" % (args.steps, st_iter, R.vsvec())},
+            "e2e": {"value": val, "unit": "GStencil/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def make_config(which, ngpus):
+    from bricklib_b200 import capi
+    return {"workload": workload_name(which), "subdomain_per_gpu": list(SUBDOMAIN), "brick": [8, 8, 8],
+            "ghost_depth": 8, "st_iter": capi.ST_ITER[which], "process_grid": capi.cart_dims(ngpus),
+            "l2_policy": "working set 2.36 GB per GPU per sweep >> 126 MB L2 (inputs larger than L2)"}
+
+
+def workload_name(which):
+    return ("weak-scaling step: %d-point %s stencil, fp64, 512^3 subdomain per GPU in 8x8x8 bricks "
+            "(BrickDecomp layout), 1 periodic halo exchange + %d sweeps per step"
+            % (which, "cube" if which == 125 else "star", {125: 4, 7: 8, 13: 4, 25: 2}[which]))
+
+
+def kernel_probe(ctx, sub, which, reps=10):
+    """Average duration of the dominant kernel (one full-grid sweep, 66^3 bricks), CUDA events on
+    the stream it is launched on, back to back ping-pong launches."""
+    from bricklib_b200 import capi
+    for _ in range(2):
+        sub.plan_full.stencil(which, sub.d_a, sub.d_b, 512, 512)
+        sub.plan_full.stencil(which, sub.d_b, sub.d_a, 512, 512)
+    ctx.timer_start(1)
+    for _ in range(reps):
+        sub.plan_full.stencil(which, sub.d_a, sub.d_b, 512, 512)
+        sub.plan_full.stencil(which, sub.d_b, sub.d_a, 512, 512)
+    ctx.timer_stop(1)
+    return ctx.timer_ms(1) / (2 * reps)
+
+
+def run_gpu(args, which):
+    import torch
+    import torch.distributed as dist
+    from bricklib_b200 import capi, weak
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d"
+                             % (args.gpus, args.gpus))
+        args.gpus = world
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    ctx = capi.Context(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid = torch.frombuffer(bytearray(capi.unique_id()), dtype=torch.uint8).cuda()
+        dist.broadcast(uid, 0)
+        ctx.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+
+    def barrier():
+        ctx.sync()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    procdims = capi.cart_dims(world)
+    st_iter = capi.ST_ITER[which]
+    sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims)
+    nb = sub.dec.nbricks
+    field = sub.host_field()
+    sub.upload(field)
+
+    # ---- device-resident timing: W warm-up steps, then exactly K steps
+    for _ in range(max(args.warmup, 3)):
+        sub.step(overlap=not args.no_overlap)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    n0 = capi.launch_count()
+    ctx.timer_start(0)
+    for _ in range(args.steps):
+        sub.step(overlap=not args.no_overlap)
+    ctx.timer_stop(0)
+    ms = ctx.timer_ms(0)
+    barrier()
+    launches = capi.launch_count() - n0
+    clocks = sampler.summary() if sampler else None
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_step = ms / args.steps
+    pts_step = float(np.prod(SUBDOMAIN)) * world * st_iter
+    value = pts_step / (ms_step * 1e-3) * 1e-9
+
+    # ---- dominant kernel: one full-grid sweep
+    sub.upload(field)
+    k_ms = kernel_probe(ctx, sub, which)
+    g = sub.gdims
+    launch_pts = float(g[0] * g[1] * g[2] * 512)
+    achieved = launch_pts * BYTES_PER_POINT / (k_ms * 1e-3) * 1e-9
+    peak, peak_src = measured_peak()
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(str(which))
+        except Exception:  # noqa: BLE001
+            traffic = None
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src, "kernel": "march_kernel (one sweep over 66^3 bricks)",
+                "kernel_ms": k_ms, "algorithmic_bytes_per_launch": launch_pts * BYTES_PER_POINT,
+                "interior_gstencil_per_s_kernel_only": float(np.prod(SUBDOMAIN)) / (k_ms * 1e-3) * 1e-9,
+                "frac_of_8TBps_nominal": achieved / 8000.0}
+
+    # ---- end to end through the C ABI with HOST buffers: H2D of the step's input field from
+    # pinned memory, exchange + ST_ITER sweeps, D2H of the step's result
+    e2e = end_to_end(ctx, sub, field, args, barrier, world, dist if world > 1 else None, pts_step)
+
+    line = None
+    if rank == 0:
+        line = {"metric": "fp64 GStencil/s", "value": value, "unit": "GStencil/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": make_config(which, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+                "roofline": roofline,
+                "overlap": not args.no_overlap,
+                "exchange_bytes_per_step_per_gpu": sub.exchange_bytes}
+        if not args.no_cpu:
+            try:
+                line["cpu_baseline"] = cpu_reference_rate(which, budget_s=args.cpu_seconds)
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"] = {"value": None, "unit": "GStencil/s", "cores": 0, "kind": "reference",
+                                        "sample": "unavailable: %r" % (e,)}
+        if args.all_stencils:
+            line["kernels"] = all_stencils(ctx, sub, peak)
+    if world > 1:
+        dist.barrier()
+    if line:
+        print(json.dumps(line), flush=True)
+    sub.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def end_to_end(ctx, sub, field, args, barrier, world, dist, pts_step):
+    """Same step, HOST buffers: every step copies its input field host->device from pinned
+    memory, runs exchange + sweeps, and copies the resulting field device->host."""
+    import ctypes as C
+    from bricklib_b200 import capi
+    n = sub.dec.nbricks * 512
+    ptrs = []
+    for _ in range(2):
+        p = C.c_void_p()
+        capi.check(capi.lib().bricks_host_alloc(C.byref(p), n * 8))
+        ptrs.append(p)
+    h_in = np.ctypeslib.as_array((C.c_double * n).from_address(ptrs[0].value))
+    h_out = np.ctypeslib.as_array((C.c_double * n).from_address(ptrs[1].value))
+    h_in[:] = field
+    steps = max(1, min(args.steps, args.e2e_steps))
+
+    def one():
+        ctx.h2d(sub.d_a, h_in)
+        sub.step(overlap=not args.no_overlap)
+        ctx.d2h(h_out, sub.d_a)
+
+    one()
+    barrier()
+    ctx.timer_start(2)
+    for _ in range(steps):
+        one()
+    ctx.timer_stop(2)
+    ms = ctx.timer_ms(2)
+    barrier()
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ok = bool(np.isfinite(h_out[512:1024]).all())
+    for p in ptrs:
+        capi.check(capi.lib().bricks_host_free(p))
+    return {"value": pts_step / (ms / steps * 1e-3) * 1e-9, "unit": "GStencil/s", "h2d_bytes_per_step": n * 8,
+            "d2h_bytes_per_step": n * 8, "ms_per_step": ms / steps, "steps": steps, "result_finite": ok,
+            "what": "per step: H2D of the whole input field from pinned host memory, exchange + sweeps, D2H of the "
+                    "whole result field (per GPU)"}
+
+
+def all_stencils(ctx, sub, peak):
+    """Kernel-only numbers for every stencil of the path on the same 66^3-brick grid."""
+    out = {}
+    g = sub.gdims
+    launch_pts = float(g[0] * g[1] * g[2] * 512)
+    for w in (7, 13, 25, 125):
+        sub.upload(sub.host_field())
+        ms = kernel_probe(ctx, sub, w, reps=5)
+        gbs = launch_pts * BYTES_PER_POINT / (ms * 1e-3) * 1e-9
+        out[str(w)] = {"ms_per_sweep": ms, "achieved_gbs": gbs, "frac_of_measured_peak": gbs / peak,
+                       "interior_gstencil_per_s": float(np.prod(SUBDOMAIN)) / (ms * 1e-3) * 1e-9}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="weak125", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-overlap", action="store_true", help="serial exchange then sweeps (reference schedule)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--all-stencils", action="store_true", help="add kernel-only numbers for 7/13/25/125-point")
+    args = ap.parse_args()
+    which = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        return run_reference(args, which)
+    return run_gpu(args, which)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

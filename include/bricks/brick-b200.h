@@ -1,0 +1,138 @@
+// brick-b200.h -- device glue for host drivers, over the C ABI of libbricks_b200.
+//
+// Drop-in for the reference's include/brick-cuda.h:12-24 (gpu* macro map) and
+// include/brick-gpu.h:23-99 (gpuCheck, movBrickInfo, movBrickStorage).  Host code that includes
+// this header never sees cuda_runtime.h; every call goes through include/bricks_b200.h.  Byte
+// counts are size_t (the reference keeps them in `unsigned`, which overflows above 4 GiB).
+// The macros need a "current" device context: set it once with bricksSetContext(ctx).
+#ifndef BRICKS_B200_BRICK_B200_H
+#define BRICKS_B200_BRICK_B200_H
+
+#include <cassert>
+#include <cstdio>
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../bricks_b200.h"
+#include "brick.h"
+
+namespace bricks_detail {
+inline bricks_ctx *&current_ctx() {
+  static thread_local bricks_ctx *c = nullptr;
+  return c;
+}
+}  // namespace bricks_detail
+
+/// the context the gpu* macros and mov* helpers act on (per host thread)
+inline void bricksSetContext(bricks_ctx *ctx) { bricks_detail::current_ctx() = ctx; }
+inline bricks_ctx *bricksContext() {
+  if (!bricks_detail::current_ctx()) throw std::runtime_error("bricksSetContext() was not called on this thread");
+  return bricks_detail::current_ctx();
+}
+
+enum gpuMemcpyKind { gpuMemcpyHostToDevice = 1, gpuMemcpyDeviceToHost = 2, gpuMemcpyDeviceToDevice = 3 };
+#define gpuSuccess 0
+#define gpuGetErrorString(e) bricks_last_error()
+
+inline int gpuMalloc_(void **p, size_t bytes) { return bricks_malloc(bricksContext(), p, bytes); }
+#define gpuMalloc(p, s) gpuMalloc_((void **)(p), (size_t)(s))
+#define gpuFree(p) bricks_free(bricksContext(), (void *)(p))
+inline int gpuMemcpy(void *dst, const void *src, size_t bytes, gpuMemcpyKind kind) {
+  bricks_ctx *c = bricksContext();
+  int rc = kind == gpuMemcpyHostToDevice   ? bricks_h2d(c, dst, src, bytes, BRICKS_STREAM_COMPUTE)
+           : kind == gpuMemcpyDeviceToHost ? bricks_d2h(c, dst, src, bytes, BRICKS_STREAM_COMPUTE)
+                                           : bricks_d2d(c, dst, src, bytes, BRICKS_STREAM_COMPUTE);
+  return rc ? rc : bricks_sync(c, BRICKS_STREAM_COMPUTE);  // cudaMemcpy semantics: blocking
+}
+#define gpuDeviceSynchronize() bricks_sync(bricksContext(), -1)
+
+/// Always checks (the reference only checks when NDEBUG is defined, brick-gpu.h:12-20) and
+/// throws instead of exit()ing.
+#define gpuCheck(x) _gpuCheck((x), #x, __FILE__, __LINE__)
+inline void _gpuCheck(int e, const char *func, const char *file, const int line) {
+  if (e != gpuSuccess) {
+    char msg[1200];
+    snprintf(msg, sizeof msg, "\"%s\" at %d in %s\n\treturned %d\n-> %s", func, line, file, e, bricks_last_error());
+    throw std::runtime_error(msg);
+  }
+}
+
+/// Copy the adjacency list to the device (H2D) or back (D2H); the returned BrickInfo's `adj`
+/// points at the copy.  Ownership as in the reference: the caller frees it (gpuFree / free).
+template <unsigned dims>
+BrickInfo<dims> movBrickInfo(BrickInfo<dims> &bInfo, gpuMemcpyKind kind) {
+  assert(kind == gpuMemcpyHostToDevice || kind == gpuMemcpyDeviceToHost);
+  BrickInfo<dims> ret = bInfo;
+  const size_t size = (size_t)bInfo.nbricks * static_power<3, dims>::value * sizeof(unsigned);
+  if (kind == gpuMemcpyHostToDevice)
+    gpuCheck(gpuMalloc(&ret.adj, size));
+  else
+    ret.adj = (typename BrickInfo<dims>::adjlist)malloc(size);
+  gpuCheck(gpuMemcpy(ret.adj, bInfo.adj, size, kind));
+  return ret;
+}
+
+/// Copy a whole storage to the device (H2D) or back to fresh host memory (D2H).  The returned
+/// storage owns its memory through the shared_ptr deleter (bricks_free / free).
+inline BrickStorage movBrickStorage(BrickStorage &bStorage, gpuMemcpyKind kind) {
+  assert(kind == gpuMemcpyHostToDevice || kind == gpuMemcpyDeviceToHost);
+  const bool to_device = kind == gpuMemcpyHostToDevice;
+  BrickStorage ret = bStorage;
+  const size_t size = bStorage.step * (size_t)bStorage.chunks * sizeof(bElem);
+  bElem *p = nullptr;
+  if (to_device)
+    gpuCheck(gpuMalloc(&p, size));
+  else
+    p = (bElem *)malloc(size);
+  gpuCheck(gpuMemcpy(p, bStorage.dat.get(), size, kind));
+  if (to_device) {
+    bricks_ctx *c = bricksContext();
+    ret.dat = std::shared_ptr<bElem>(p, [c](bElem *q) { bricks_free(c, q); });
+  } else {
+    ret.dat = std::shared_ptr<bElem>(p, [](bElem *q) { free(q); });
+  }
+  return ret;
+}
+
+/// A launch plan over boxes of a brick grid: the host side of
+/// `brick_kernel<<<dim3(strideb...), 32>>>` (weak/main.cu:277).  Owns the device copies of the
+/// grid and the adjacency list.
+class BrickStencilPlan {
+ public:
+  struct Box {
+    unsigned lo[3], hi[3];  // contiguous axis first, hi exclusive
+  };
+  BrickStencilPlan(bricks_ctx *ctx, const unsigned *grid, const unsigned gdims[3], const unsigned *adj,
+                   unsigned nbricks, const std::vector<Box> &boxes) {
+    std::vector<unsigned> flat;
+    for (const Box &b : boxes) {
+      flat.insert(flat.end(), b.lo, b.lo + 3);
+      flat.insert(flat.end(), b.hi, b.hi + 3);
+    }
+    gpuCheck(bricks_plan_create(ctx, grid, gdims, adj, nbricks, (int)boxes.size(), flat.data(), &plan_));
+  }
+  BrickStencilPlan(const BrickStencilPlan &) = delete;
+  BrickStencilPlan &operator=(const BrickStencilPlan &) = delete;
+  ~BrickStencilPlan() { bricks_plan_destroy(plan_); }
+
+  /// out = stencil(in) for one pair of Brick views on DEVICE storages (asynchronous)
+  template <typename B>
+  void run(int stencil_id, B &in, B &out, const double *coeff = nullptr, int stream = BRICKS_STREAM_COMPUTE) {
+    const double *i[1] = {in.dat};
+    double *o[1] = {out.dat};
+    gpuCheck(bricks_stencil(plan_, stencil_id, 1, i, o, in.step, out.step, coeff, stream));
+  }
+  /// batched over many storage pairs that share the grid/adjacency (strong scaling)
+  void run(int stencil_id, const std::vector<const double *> &in, const std::vector<double *> &out, size_t in_step,
+           size_t out_step, const double *coeff = nullptr, int stream = BRICKS_STREAM_COMPUTE) {
+    gpuCheck(bricks_stencil(plan_, stencil_id, (int)in.size(), in.data(), out.data(), in_step, out_step, coeff, stream));
+  }
+  bricks_plan *handle() { return plan_; }
+
+ private:
+  bricks_plan *plan_ = nullptr;
+};
+
+#endif  // BRICKS_B200_BRICK_B200_H
