@@ -429,3 +429,104 @@ def uniform(n, seed=0, start=0):
     out = np.empty(n, np.float64)
     check(lib().bricks_uniform_fill(_np_ptr(out), n, seed, start))
     return out
+
+
+# ---------------------------------------------------------------------------
+# strong scaling (include/bricks/strong-plan.h through bricks_strong_*) and reusable link tables
+class _StrongLink(C.Structure):
+    _fields_ = [("src_sub", C.c_uint), ("dst_sub", C.c_uint), ("src_off", C.c_size_t), ("dst_off", C.c_size_t),
+                ("len", C.c_size_t)]
+
+
+class _StrongPiece(C.Structure):
+    _fields_ = [("sub", C.c_uint), ("region", C.c_uint), ("off", C.c_size_t), ("len", C.c_size_t),
+                ("buf_off", C.c_size_t), ("sender_id", C.c_ulong)]
+
+
+_SIGS.update({
+    "bricks_exchange_create_v": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vpp]),
+    "bricks_strong_plan_create": (C.c_int, [C.c_uint, C.c_uint, C.c_int, C.c_int, _vp, C.c_size_t, _vpp]),
+    "bricks_strong_plan_destroy": (C.c_int, [_vp]),
+    "bricks_strong_plan_sizes": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "bricks_strong_plan_links": (C.c_int, [_vp, _vp]),
+    "bricks_strong_plan_peer": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
+    "bricks_strong_plan_pieces": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "bricks_strong_owner": (C.c_int, [_vp, C.c_ulong, _vp]),
+    "bricks_strong_neighbor": (C.c_int, [_vp, C.c_ulong, C.c_uint64, _vp]),
+    "bricks_strong_coords": (C.c_int, [_vp, C.c_ulong, _vp]),
+})
+
+
+class StrongPlan(object):
+    """Ownership and exchange lists of the two-level decomposition (strong/args.cpp:36-56,104-113,
+    strong/main.cu:188-395), from the product's C++ planner."""
+
+    def __init__(self, dom, sdom, nranks, rank, dec, step=512):
+        L = lib()
+        self._h = C.c_void_p()
+        check(L.bricks_strong_plan_create(dom, sdom, nranks, rank, dec._h, step, C.byref(self._h)))
+        lo, hi, nl = C.c_ulong(), C.c_ulong(), C.c_size_t()
+        ns, nr = C.c_int(), C.c_int()
+        check(L.bricks_strong_plan_sizes(self._h, C.byref(lo), C.byref(hi), C.byref(nl), C.byref(ns), C.byref(nr)))
+        self.first_id, self.last_id = lo.value, hi.value
+        self.nsub = hi.value - lo.value
+        arr = (_StrongLink * max(nl.value, 1))()
+        check(L.bricks_strong_plan_links(self._h, arr))
+        self.links = [(l.src_sub, l.dst_sub, l.src_off, l.dst_off, l.len) for l in arr[:nl.value]]
+        self.send, self.recv = [], []
+        for d, out, n in ((0, self.send, ns.value), (1, self.recv, nr.value)):
+            for i in range(n):
+                rk, by, npc = C.c_int(), C.c_size_t(), C.c_int()
+                check(L.bricks_strong_plan_peer(self._h, d, i, C.byref(rk), C.byref(by), C.byref(npc)))
+                pcs = (_StrongPiece * max(npc.value, 1))()
+                check(L.bricks_strong_plan_pieces(self._h, d, i, pcs))
+                out.append({"rank": rk.value, "bytes": by.value,
+                            "pieces": [(p.sub, p.region, p.off, p.len, p.buf_off, p.sender_id) for p in pcs[:npc.value]]})
+
+    def owner(self, sid):
+        r = C.c_int()
+        check(lib().bricks_strong_owner(self._h, sid, C.byref(r)))
+        return r.value
+
+    def neighbor(self, sid, direction_set):
+        n = C.c_ulong()
+        check(lib().bricks_strong_neighbor(self._h, sid, direction_set, C.byref(n)))
+        return n.value
+
+    def coords(self, sid):
+        c = (C.c_uint * 3)()
+        check(lib().bricks_strong_coords(self._h, sid, c))
+        return (c[0], c[1], c[2])
+
+    def close(self):
+        if self._h:
+            lib().bricks_strong_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+
+class LinkTable(object):
+    """A device-resident RegionLink list (bricks_links_upload) that can be run many times."""
+
+    def __init__(self, ctx, links):
+        self.ctx, self.n = ctx, len(links)
+        self._dev = C.c_void_p()
+        if self.n:
+            arr = (RegionLink * self.n)(*[RegionLink(s, d, n) for s, d, n in links])
+            check(lib().bricks_links_upload(ctx._h, arr, self.n, C.byref(self._dev)))
+        self.bytes = sum(n for _, _, n in links)
+
+    def run(self, stream=STREAM_COMPUTE):
+        if self.n:
+            check(lib().bricks_copy_regions(self.ctx._h, self._dev, self.n, stream))
+
+
+class ExchangeV(Exchange):
+    """bricks_exchange_create_v: independent receive / send sizes per entry."""
+
+    def __init__(self, ctx, rank, recv_off, recv_bytes, recv_peer, send_off, send_bytes, send_peer):
+        a = [np.ascontiguousarray(x, np.uint64) for x in (recv_off, recv_bytes, send_off, send_bytes)]
+        p = [np.ascontiguousarray(x, np.int32) for x in (recv_peer, send_peer)]
+        self._h = C.c_void_p()
+        self.ctx = ctx
+        check(lib().bricks_exchange_create_v(ctx._h, rank, len(a[0]), _np_ptr(a[0]), _np_ptr(a[1]), _np_ptr(p[0]),
+                                             _np_ptr(a[2]), _np_ptr(a[3]), _np_ptr(p[1]), C.byref(self._h)))

@@ -110,7 +110,7 @@ struct bricks_exchange {
   bricks_ctx *ctx = nullptr;
   int rank = 0;
   struct Msg {
-    size_t recv_off, send_off, nbytes;
+    size_t recv_off, send_off, recv_bytes, send_bytes;
     int recv_peer, send_peer;
   };
   std::vector<Msg> msgs;

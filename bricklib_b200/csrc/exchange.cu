@@ -143,31 +143,36 @@ int bricks_comm_destroy(bricks_ctx *ctx) {
   return 0;
 }
 
-int bricks_exchange_create(bricks_ctx *ctx, int rank, int nregions, const size_t *recv_off,
-                           const size_t *send_off, const size_t *nbytes, const int *recv_peer,
-                           const int *send_peer, bricks_exchange **out) {
-  BRK_ARG(ctx && out && nregions > 0 && recv_off && send_off && nbytes && recv_peer && send_peer);
+int bricks_exchange_create_v(bricks_ctx *ctx, int rank, int nregions, const size_t *recv_off,
+                             const size_t *recv_bytes, const int *recv_peer, const size_t *send_off,
+                             const size_t *send_bytes, const int *send_peer, bricks_exchange **out) {
+  BRK_ARG(ctx && out && nregions > 0 && recv_off && send_off && recv_bytes && send_bytes && recv_peer && send_peer);
   BRK_CUDA(cudaSetDevice(ctx->device));
+  std::vector<bricks_exchange::Msg> msgs;
+  for (int i = 0; i < nregions; ++i) {
+    BRK_ARG((recv_off[i] & 15) == 0 && (send_off[i] & 15) == 0 && (recv_bytes[i] & 15) == 0 &&
+            (send_bytes[i] & 15) == 0);
+    /* a self neighbour pairs this rank's own send i with its own receive i */
+    BRK_ARG((recv_peer[i] == rank) == (send_peer[i] == rank));
+    BRK_ARG(recv_peer[i] != rank || recv_bytes[i] == send_bytes[i]);
+    if (recv_bytes[i] == 0 && send_bytes[i] == 0) continue;
+    bricks_exchange::Msg m = {recv_off[i], send_off[i], recv_bytes[i], send_bytes[i], recv_peer[i], send_peer[i]};
+    msgs.push_back(m);
+  }
   bricks_exchange *ex = new bricks_exchange;
   ex->ctx = ctx;
   ex->rank = rank;
-  std::vector<bricks_region_link> self;
-  for (int i = 0; i < nregions; ++i) {
-    BRK_ARG((recv_off[i] & 15) == 0 && (send_off[i] & 15) == 0 && (nbytes[i] & 15) == 0);
-    BRK_ARG((recv_peer[i] == rank) == (send_peer[i] == rank));
-    if (nbytes[i] == 0) continue;
-    bricks_exchange::Msg m = {recv_off[i], send_off[i], nbytes[i], recv_peer[i], send_peer[i]};
-    ex->msgs.push_back(m);
-  }
+  ex->msgs = msgs;
   /* Region i is received from recv_peer[i] and sent to send_peer[i].  When recv_peer[i] is this
-   * rank, the matching send is this rank's own region i (periodic process grid of extent 1 or
-   * 2 in that direction), i.e. ghost[i] <- skin[i] on the device. */
+   * rank, the matching send is this rank's own region i (periodic process grid of extent 1 in
+   * that direction), i.e. ghost[i] <- skin[i] on the device. */
+  std::vector<bricks_region_link> self;
   for (auto &m : ex->msgs)
-    if (m.recv_peer == rank) {
+    if (m.recv_peer == rank && m.recv_bytes) {
       bricks_region_link l;
       l.from = (double *)m.send_off; /* relative to the storage base */
       l.to = (double *)m.recv_off;
-      l.len = m.nbytes;
+      l.len = m.recv_bytes;
       self.push_back(l);
     }
   ex->nself = (int)self.size();
@@ -175,12 +180,21 @@ int bricks_exchange_create(bricks_ctx *ctx, int rank, int nregions, const size_t
     void *blob = nullptr;
     unsigned nchunks = 0;
     int rc = upload_links(ctx, self.data(), ex->nself, &blob, &nchunks);
-    if (rc) return rc;
+    if (rc) {
+      delete ex;
+      return rc;
+    }
     g_link_meta[blob] = std::make_pair(ex->nself, nchunks);
     ex->self_links_dev = (bricks_region_link *)blob;
   }
   *out = ex;
   return 0;
+}
+
+int bricks_exchange_create(bricks_ctx *ctx, int rank, int nregions, const size_t *recv_off,
+                           const size_t *send_off, const size_t *nbytes, const int *recv_peer,
+                           const int *send_peer, bricks_exchange **out) {
+  return bricks_exchange_create_v(ctx, rank, nregions, recv_off, nbytes, recv_peer, send_off, nbytes, send_peer, out);
 }
 
 int bricks_exchange_destroy(bricks_exchange *ex) {
@@ -211,10 +225,10 @@ int bricks_exchange_run(bricks_exchange *ex, double *storage, int stream) {
      * NCCL matches send/recv pairs per peer in issue order */
     BRK_NCCL(ncclGroupStart());
     for (auto &m : ex->msgs) {
-      if (m.recv_peer != ex->rank)
-        BRK_NCCL(ncclRecv(base + m.recv_off, m.nbytes, ncclChar, m.recv_peer, ctx->comm, s));
-      if (m.send_peer != ex->rank)
-        BRK_NCCL(ncclSend(base + m.send_off, m.nbytes, ncclChar, m.send_peer, ctx->comm, s));
+      if (m.recv_peer != ex->rank && m.recv_bytes)
+        BRK_NCCL(ncclRecv(base + m.recv_off, m.recv_bytes, ncclChar, m.recv_peer, ctx->comm, s));
+      if (m.send_peer != ex->rank && m.send_bytes)
+        BRK_NCCL(ncclSend(base + m.send_off, m.send_bytes, ncclChar, m.send_peer, ctx->comm, s));
     }
     BRK_NCCL(ncclGroupEnd());
   }

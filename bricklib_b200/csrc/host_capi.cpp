@@ -9,6 +9,7 @@
 #include "../../include/bricks/brickcompare.h"
 #include "../../include/bricks/bricksetup.h"
 #include "../../include/bricks/multiarray.h"
+#include "../../include/bricks/strong-plan.h"
 #include "../../include/bricks/zmort.h"
 
 namespace bricks {
@@ -20,6 +21,9 @@ typedef Brick<Dim<8, 8, 8>, Dim<8>> Brick3;
 
 struct bricks_decomp {
   Decomp3 *dec;
+};
+struct bricks_strong_plan {
+  StrongPlan *plan;
 };
 
 namespace {
@@ -204,6 +208,92 @@ int bricks_compare_brick3(const long dimlist[3], const long padding[3], const lo
     if (match) *match = compareBrick<3>(dl, pd, gh, arr, const_cast<unsigned *>(grid), b) ? 1 : 0;
     if (max_rel) *max_rel = maxRelErrBrick<3>(dl, pd, gh, arr, const_cast<unsigned *>(grid), b);
   });
+}
+
+int bricks_strong_plan_create(unsigned dom_size, unsigned sdom_size, int nranks, int rank, const bricks_decomp *d,
+                              size_t step, bricks_strong_plan **out) {
+  if (!d || !out || nranks < 1 || rank < 0 || rank >= nranks || !sdom_size) return -1;
+  return guarded([&] {
+    const Decomp3 &D = *d->dec;
+    const size_t sb = step * sizeof(double);
+    std::vector<StrongRegion> regs(D.ghost.size());
+    for (size_t i = 0; i < regs.size(); ++i) {
+      regs[i].ghost_neighbor = D.ghost[i].neighbor.set;
+      regs[i].ghost_off = (size_t)(D.ghost[i].pos + D.ghost[i].first_pad) * sb;
+      regs[i].skin_off = (size_t)(D.skin[i].pos + D.skin[i].first_pad) * sb;
+      regs[i].len = (size_t)(D.ghost[i].len - D.ghost[i].first_pad - D.ghost[i].last_pad) * sb;
+    }
+    *out = new bricks_strong_plan{new StrongPlan(dom_size, sdom_size, nranks, rank, regs)};
+  });
+}
+
+int bricks_strong_plan_destroy(bricks_strong_plan *p) {
+  if (p) {
+    delete p->plan;
+    delete p;
+  }
+  return 0;
+}
+
+int bricks_strong_plan_sizes(const bricks_strong_plan *p, unsigned long *first_id, unsigned long *last_id,
+                             size_t *nlinks, int *nsend_peers, int *nrecv_peers) {
+  if (!p) return -1;
+  if (first_id) *first_id = p->plan->first_id;
+  if (last_id) *last_id = p->plan->last_id;
+  if (nlinks) *nlinks = p->plan->links.size();
+  if (nsend_peers) *nsend_peers = (int)p->plan->send.size();
+  if (nrecv_peers) *nrecv_peers = (int)p->plan->recv.size();
+  return 0;
+}
+
+int bricks_strong_plan_links(const bricks_strong_plan *p, bricks_strong_link *out) {
+  if (!p || !out) return -1;
+  for (size_t i = 0; i < p->plan->links.size(); ++i) {
+    const StrongLink &l = p->plan->links[i];
+    out[i] = bricks_strong_link{l.src_sub, l.dst_sub, l.src_off, l.dst_off, l.len};
+  }
+  return 0;
+}
+
+static const std::vector<StrongPeer> *peer_list(const bricks_strong_plan *p, int dir) {
+  return dir == 0 ? &p->plan->send : (dir == 1 ? &p->plan->recv : nullptr);
+}
+
+int bricks_strong_plan_peer(const bricks_strong_plan *p, int dir, int idx, int *rank, size_t *bytes, int *npieces) {
+  if (!p || !peer_list(p, dir) || idx < 0 || idx >= (int)peer_list(p, dir)->size()) return -1;
+  const StrongPeer &q = (*peer_list(p, dir))[idx];
+  if (rank) *rank = q.rank;
+  if (bytes) *bytes = q.bytes;
+  if (npieces) *npieces = (int)q.pieces.size();
+  return 0;
+}
+
+int bricks_strong_plan_pieces(const bricks_strong_plan *p, int dir, int idx, bricks_strong_piece *out) {
+  if (!p || !out || !peer_list(p, dir) || idx < 0 || idx >= (int)peer_list(p, dir)->size()) return -1;
+  const StrongPeer &q = (*peer_list(p, dir))[idx];
+  for (size_t i = 0; i < q.pieces.size(); ++i) {
+    const StrongPiece &c = q.pieces[i];
+    out[i] = bricks_strong_piece{c.sub, c.region, c.off, c.len, c.buf_off, c.sender_id};
+  }
+  return 0;
+}
+
+int bricks_strong_owner(const bricks_strong_plan *p, unsigned long id, int *rank) {
+  if (!p || !rank) return -1;
+  *rank = p->plan->owner(id);
+  return 0;
+}
+
+int bricks_strong_neighbor(const bricks_strong_plan *p, unsigned long id, uint64_t set, unsigned long *nid) {
+  if (!p || !nid) return -1;
+  *nid = p->plan->neighbor_id(id, BitSet(set));
+  return 0;
+}
+
+int bricks_strong_coords(const bricks_strong_plan *p, unsigned long id, unsigned coords[3]) {
+  if (!p || !coords) return -1;
+  p->plan->coords(id, coords);
+  return 0;
 }
 
 int bricks_cart_dims(int nranks, int ndims, int *dims) {

@@ -19,7 +19,8 @@ struct MarchParams {
 };
 
 template <int R, bool CUBE, int VAR, int P>
-__global__ void __launch_bounds__(32) march_kernel(const __grid_constant__ MarchParams prm) {
+/* register cap for the cube: measured best on B200 (profiles/r01_maxnreg_sweep.txt) */
+__global__ void __launch_bounds__(32) __maxnreg__(CUBE ? 176 : 255) march_kernel(const __grid_constant__ MarchParams prm) {
   using L = dev::StageLayout<R, CUBE, P>;
   constexpr int H = 8 / P;
   extern __shared__ __align__(1024) char smem[];

@@ -130,6 +130,12 @@ int bricks_comm_destroy(bricks_ctx *ctx);
 int bricks_exchange_create(bricks_ctx *ctx, int rank, int nregions, const size_t *recv_off,
                            const size_t *send_off, const size_t *nbytes, const int *recv_peer,
                            const int *send_peer, bricks_exchange **ex);
+/* general form: receive and send sizes of a region may differ (either may be 0).  Used for the
+ * per-peer packed messages of the strong-scaling driver (strong/main.cu:416-435): region = peer,
+ * offsets point into one arena that holds every packed send and receive buffer. */
+int bricks_exchange_create_v(bricks_ctx *ctx, int rank, int nregions, const size_t *recv_off,
+                             const size_t *recv_bytes, const int *recv_peer, const size_t *send_off,
+                             const size_t *send_bytes, const int *send_peer, bricks_exchange **ex);
 int bricks_exchange_destroy(bricks_exchange *ex);
 /* enqueue the whole exchange of one storage on `stream` (normally BRICKS_STREAM_COMM) */
 int bricks_exchange_run(bricks_exchange *ex, double *storage_dev, int stream);

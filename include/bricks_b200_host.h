@@ -59,6 +59,34 @@ int bricks_copy_brick3(int to_brick, const long dimlist[3], const long padding[3
 int bricks_compare_brick3(const long dimlist[3], const long padding[3], const long ghost[3], double *arr,
                           const unsigned *grid, double *brick_dat, size_t step, const unsigned *adj,
                           unsigned nbricks, int *match, double *max_rel);
+/* ---- strong scaling: two-level decomposition (strong/args.cpp:36-56,104-113; strong/main.cu:188-395).
+ * A dom^3 domain in (dom/sdom)^3 subdomains named by Z-Morton id; rank r owns a contiguous id
+ * range; all subdomains share the BrickDecomp `d` (built for sdom^3).  Offsets are bytes inside
+ * one subdomain storage of `step` elements per brick. */
+typedef struct bricks_strong_plan bricks_strong_plan;
+typedef struct {
+  unsigned src_sub, dst_sub;      /* local subdomain indices */
+  size_t src_off, dst_off, len;   /* neighbour's skin[i] -> my ghost[i] */
+} bricks_strong_link;
+typedef struct {
+  unsigned sub, region;           /* local subdomain index, BrickDecomp region i */
+  size_t off, len, buf_off;       /* range inside the storage, position in the packed message */
+  unsigned long sender_id;        /* Morton id of the sending subdomain */
+} bricks_strong_piece;
+int bricks_strong_plan_create(unsigned dom_size, unsigned sdom_size, int nranks, int rank, const bricks_decomp *d,
+                              size_t step, bricks_strong_plan **out);
+int bricks_strong_plan_destroy(bricks_strong_plan *p);
+int bricks_strong_plan_sizes(const bricks_strong_plan *p, unsigned long *first_id, unsigned long *last_id,
+                             size_t *nlinks, int *nsend_peers, int *nrecv_peers);
+int bricks_strong_plan_links(const bricks_strong_plan *p, bricks_strong_link *out);
+/* dir 0 = send, 1 = receive; peers in ascending rank order */
+int bricks_strong_plan_peer(const bricks_strong_plan *p, int dir, int idx, int *rank, size_t *bytes, int *npieces);
+int bricks_strong_plan_pieces(const bricks_strong_plan *p, int dir, int idx, bricks_strong_piece *out);
+/* owner rank / Morton neighbour of a subdomain id (getrank) and its grid coordinates (i,j,k) */
+int bricks_strong_owner(const bricks_strong_plan *p, unsigned long id, int *rank);
+int bricks_strong_neighbor(const bricks_strong_plan *p, unsigned long id, uint64_t direction_set, unsigned long *nid);
+int bricks_strong_coords(const bricks_strong_plan *p, unsigned long id, unsigned coords[3]);
+
 /* MPI_Dims_create / MPI_Cart_rank / MPI_Cart_coords equivalents (weak/args.cpp:105-115) */
 int bricks_cart_dims(int nranks, int ndims, int *dims);
 int bricks_cart_rank(int ndims, const int *dims, const int *coo, int *rank);

@@ -224,3 +224,59 @@ def exchange(storages, dec, procdims, step=512):
             s0 = (int(s["pos"]) + int(s["first_pad"])) * step
             storages[r][d0:d0 + n] = snap[src][s0:s0 + n]
     return storages
+
+
+# ---------------------------------------------------------------------------
+# strong scaling: restatement of strong/args.cpp:36-56,104-113 (getrank, ownership split) and of the
+# link construction of strong/main.cu:188-247 -- ghost[i] of subdomain T is skin[i] of the periodic
+# neighbour of T in direction ghost[i].neighbor.  Morton coordinate d <-> axis d+1 (zmort.h:18-105).
+def morton3(ci, cj, ck):
+    """ZMORT()[ck][cj][ci]: bit b of ci lands on bit 3b, cj on 3b+1, ck on 3b+2."""
+    z = 0
+    for b in range(21):
+        z |= ((ci >> b) & 1) << (3 * b) | ((cj >> b) & 1) << (3 * b + 1) | ((ck >> b) & 1) << (3 * b + 2)
+    return z
+
+
+def morton3_coords(z):
+    c = [0, 0, 0]
+    for b in range(21):
+        for d in range(3):
+            c[d] |= ((z >> (3 * b + d)) & 1) << b
+    return tuple(c)
+
+
+def strong_owner(sid, total, nranks):
+    base, extra = divmod(total, nranks)
+    split = extra * (base + 1)
+    return sid // (base + 1) if sid < split else extra + (sid - split) // base
+
+
+def strong_range(rank, total, nranks):
+    base, extra = divmod(total, nranks)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def strong_neighbor(sid, neighbor_set, subdim):
+    c = list(morton3_coords(sid))
+    for d in range(3):
+        if neighbor_set & (1 << (d + 1)):
+            c[d] = (c[d] + 1) % subdim
+        elif neighbor_set & (1 << (31 + d + 1)):
+            c[d] = (c[d] - 1) % subdim
+    return morton3(*c)
+
+
+def strong_exchange(storages, dec, subdim, step=512):
+    """storages: {morton id: 1-D float64 storage}.  In-place ghost fill of every subdomain."""
+    snap = {k: v.copy() for k, v in storages.items()}
+    for sid, st in storages.items():
+        for i in range(len(dec.ghost)):
+            g, s = dec.ghost[i], dec.skin[i]
+            src = strong_neighbor(sid, int(g["neighbor"]), subdim)
+            n = (int(g["len"]) - int(g["first_pad"]) - int(g["last_pad"])) * step
+            d0 = (int(g["pos"]) + int(g["first_pad"])) * step
+            s0 = (int(s["pos"]) + int(s["first_pad"])) * step
+            st[d0:d0 + n] = snap[src][s0:s0 + n]
+    return storages
