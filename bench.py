@@ -23,8 +23,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WORKLOADS = {"weak125": 125, "weak7": 7, "weak13": 13, "weak25": 25}
+WORKLOADS = {"weak125": 125, "weak7": 7, "weak13": 13, "weak25": 25, "strong125": 125, "strong7": 7}
 SUBDOMAIN = (512, 512, 512)
+STRONG_DOM, STRONG_SDOM = 1024, 128  # BASELINE.json configs[4]: 1024^3 global grid in 128^3 subdomains
 BYTES_PER_POINT = 16.0  # one 8-byte read + one 8-byte write per point per sweep
 
 
@@ -106,7 +107,10 @@ def run_reference(args, which):
     from oracle import refload as R
     from bricklib_b200 import capi, synth
     st_iter = capi.ST_ITER[which]
-    dims = (256, 256, 256)
+    strong = args.workload.startswith("strong")
+    # strong: a step of the sample = one subdomain of the decomposition (its 26 periodic neighbours
+    # are copies of itself, as in strong/main.cu on one rank with one subdomain)
+    dims = (args.sdom,) * 3 if strong else (256, 256, 256)
     dec = O.Decomp(dims, 8)
     n = dec.nbricks * 512
     a, b = R.aligned_empty(n), R.aligned_empty(n)
@@ -135,19 +139,30 @@ def run_reference(args, which):
     val = float(np.prod(dims)) * st_iter / dt * 1e-9
     line = {"impl": "reference", "metric": "fp64 GStencil/s", "value": val, "unit": "GStencil/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": make_config(which, args.gpus),
+            "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": make_config(which, args.gpus, (args.dom, args.sdom) if strong else None),
             "cpu_baseline": {"value": val, "unit": "GStencil/s", "cores": R.max_threads(), "kind": "reference",
-                             "sample": "%d steps x (self exchange + %d sweeps) over a 256^3 subdomain, codegen brick "
-                                       "kernel %s under OpenMP" % (args.steps, st_iter, R.vsvec())},
+                             "sample": "%d steps x (self exchange + %d sweeps) over a %d^3 subdomain, codegen brick "
+                                       "kernel %s under OpenMP" % (args.steps, st_iter, dims[0], R.vsvec())},
             "e2e": {"value": val, "unit": "GStencil/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
 
 
-def make_config(which, ngpus):
+def make_config(which, ngpus, strong=None):
     from bricklib_b200 import capi
+    if strong:
+        dom, sdom = strong
+        g = sdom // 8 + 2
+        return {"workload": ("strong-scaling step: %d-point %s stencil, fp64, %d^3 global periodic grid in %d^3 subdomains "
+                             "(Z-Morton ids, contiguous ranges per GPU), 8x8x8 bricks, 1 halo exchange + %d sweeps per step"
+                             % (which, "cube" if which == 125 else "star", dom, sdom, capi.ST_ITER[which])),
+                "global_grid": [dom] * 3, "subdomain": [sdom] * 3, "subdomains": (dom // sdom) ** 3, "brick": [8, 8, 8],
+                "ghost_depth": 8, "st_iter": capi.ST_ITER[which],
+                "l2_policy": "working set %.2f GB per sweep over all GPUs >> 126 MB L2 (inputs larger than L2)"
+                             % ((dom // sdom) ** 3 * g ** 3 * 4096 * 2 / 1e9)}
     return {"workload": workload_name(which), "subdomain_per_gpu": list(SUBDOMAIN), "brick": [8, 8, 8],
             "ghost_depth": 8, "st_iter": capi.ST_ITER[which], "process_grid": capi.cart_dims(ngpus),
             "l2_policy": "working set 2.36 GB per GPU per sweep >> 126 MB L2 (inputs larger than L2)"}
@@ -174,10 +189,11 @@ def kernel_probe(ctx, sub, which, reps=10):
     return ctx.timer_ms(1) / (2 * reps)
 
 
-def run_gpu(args, which):
+def init_ranks(args):
+    """one process per GPU: context on LOCAL_RANK, NCCL communicator shared through torch.distributed"""
     import torch
     import torch.distributed as dist
-    from bricklib_b200 import capi, weak
+    from bricklib_b200 import capi
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -205,6 +221,20 @@ def run_gpu(args, which):
             dist.barrier()
             torch.cuda.synchronize()
 
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    return ctx, rank, world, local, dist, barrier, max_over_ranks
+
+
+def run_gpu(args, which):
+    from bricklib_b200 import capi, weak
+    ctx, rank, world, local, dist, barrier, max_over_ranks = init_ranks(args)
+
     procdims = capi.cart_dims(world)
     st_iter = capi.ST_ITER[which]
     sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims)
@@ -228,10 +258,7 @@ def run_gpu(args, which):
     barrier()
     launches = capi.launch_count() - n0
     clocks = sampler.summary() if sampler else None
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms = max_over_ranks(ms)
     ms_step = ms / args.steps
     pts_step = float(np.prod(SUBDOMAIN)) * world * st_iter
     value = pts_step / (ms_step * 1e-3) * 1e-9
@@ -258,7 +285,7 @@ def run_gpu(args, which):
 
     # ---- end to end through the C ABI with HOST buffers: H2D of the step's input field from
     # pinned memory, exchange + ST_ITER sweeps, D2H of the step's result
-    e2e = end_to_end(ctx, sub, field, args, barrier, world, dist if world > 1 else None, pts_step)
+    e2e = end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step)
 
     line = None
     if rank == 0:
@@ -287,7 +314,120 @@ def run_gpu(args, which):
     return 0
 
 
-def end_to_end(ctx, sub, field, args, barrier, world, dist, pts_step):
+def run_gpu_strong(args, which):
+    """Strong scaling (strong/main.cu:397-540): the global dom^3 grid is fixed, its (dom/sdom)^3
+    subdomains are shared out over the ranks.  value = dom^3 x ST_ITER / time of a step."""
+    import ctypes as C
+    from bricklib_b200 import capi, strong
+    ctx, rank, world, local, dist, barrier, max_over_ranks = init_ranks(args)
+    dom, sdom = args.dom, args.sdom
+    st_iter = capi.ST_ITER[which]
+    sd = strong.StrongDomain(ctx, dom, sdom, which, rank=rank, nranks=world)
+    # pinned host images of all local subdomain storages (input, result)
+    nbytes = sd.nsub * sd.sub_bytes
+    n = nbytes // 8
+    ptrs = []
+    for _ in range(2):
+        p = C.c_void_p()
+        capi.check(capi.lib().bricks_host_alloc(C.byref(p), nbytes))
+        ptrs.append(p)
+    h_in = np.ctypeslib.as_array((C.c_double * n).from_address(ptrs[0].value))
+    h_out = np.ctypeslib.as_array((C.c_double * n).from_address(ptrs[1].value))
+    per = sd.sub_bytes // 8
+    for s_ in range(sd.nsub):
+        h_in[s_ * per:(s_ + 1) * per] = sd.host_field(s_)
+    ctx.h2d(sd.d_a, h_in)
+    ctx.sync()
+    for _ in range(max(args.warmup, 3)):
+        sd.step(overlap=not args.no_overlap)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    n0 = capi.launch_count()
+    ctx.timer_start(0)
+    for _ in range(args.steps):
+        sd.step(overlap=not args.no_overlap)
+    ctx.timer_stop(0)
+    ms = ctx.timer_ms(0)
+    barrier()
+    launches = capi.launch_count() - n0
+    clocks = sampler.summary() if sampler else None
+    ms_step = max_over_ranks(ms) / args.steps
+    pts_step = float(dom) ** 3 * st_iter
+    value = pts_step / (ms_step * 1e-3) * 1e-9
+
+    # ---- dominant kernel: one sweep over every brick (ghost included) of all local subdomains
+    ctx.h2d(sd.d_a, h_in)
+    ctx.sync()
+    for _ in range(2):
+        sd.plan_full.stencil(which, sd.in_a, sd.in_b)
+        sd.plan_full.stencil(which, sd.in_b, sd.in_a)
+    reps = 5
+    ctx.timer_start(1)
+    for _ in range(reps):
+        sd.plan_full.stencil(which, sd.in_a, sd.in_b)
+        sd.plan_full.stencil(which, sd.in_b, sd.in_a)
+    ctx.timer_stop(1)
+    k_ms = ctx.timer_ms(1) / (2 * reps)
+    g = sd.dec.gdims
+    launch_pts = float(g[0] * g[1] * g[2] * 512) * sd.nsub
+    achieved = launch_pts * BYTES_PER_POINT / (k_ms * 1e-3) * 1e-9
+    peak, peak_src = measured_peak()
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src,
+                "kernel": "march_kernel (one sweep over %d subdomains x %d^3 bricks, one launch)" % (sd.nsub, g[0]),
+                "kernel_ms": k_ms, "algorithmic_bytes_per_launch": launch_pts * BYTES_PER_POINT,
+                "ghost_overhead": float(g[0] * g[1] * g[2] * 512) / float(sdom) ** 3}
+
+    # ---- end to end with HOST buffers: H2D of every local subdomain, step, D2H of every result
+    esteps = max(1, min(args.steps, args.e2e_steps))
+
+    def one():
+        ctx.h2d(sd.d_a, h_in)
+        sd.step(overlap=not args.no_overlap)
+        ctx.d2h(h_out, sd.d_a)
+
+    one()
+    barrier()
+    ctx.timer_start(2)
+    for _ in range(esteps):
+        one()
+    ctx.timer_stop(2)
+    ems = ctx.timer_ms(2)
+    barrier()
+    ems = max_over_ranks(ems) / esteps
+    ok = bool(np.isfinite(h_out[512:1024]).all())
+    for p in ptrs:
+        capi.check(capi.lib().bricks_host_free(p))
+    e2e = {"value": pts_step / (ems * 1e-3) * 1e-9, "unit": "GStencil/s", "h2d_bytes_per_step": nbytes,
+           "d2h_bytes_per_step": nbytes, "ms_per_step": ems, "steps": esteps, "result_finite": ok,
+           "what": "per step and GPU: H2D of all local subdomain storages from pinned host memory, exchange + sweeps, "
+                   "D2H of all result storages"}
+
+    if rank == 0:
+        line = {"metric": "fp64 GStencil/s", "value": value, "unit": "GStencil/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": make_config(which, world, (dom, sdom)), "clocks": clocks, "e2e": e2e,
+                "gpu_launches": int(launches), "roofline": roofline, "overlap": not args.no_overlap,
+                "subdomains_rank0": sd.nsub, "exchange_bytes_sent_rank0": sd.exchange_bytes,
+                "local_links_rank0": len(sd.plan.links)}
+        if not args.no_cpu:
+            try:
+                line["cpu_baseline"] = cpu_reference_rate(which, budget_s=args.cpu_seconds, dims=(sdom,) * 3)
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"] = {"value": None, "unit": "GStencil/s", "cores": 0, "kind": "reference",
+                                        "sample": "unavailable: %r" % (e,)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    sd.close()
+    return 0
+
+
+def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
     """Same step, HOST buffers: every step copies its input field host->device from pinned
     memory, runs exchange + sweeps, and copies the resulting field device->host."""
     import ctypes as C
@@ -316,11 +456,7 @@ def end_to_end(ctx, sub, field, args, barrier, world, dist, pts_step):
     ctx.timer_stop(2)
     ms = ctx.timer_ms(2)
     barrier()
-    if dist is not None:
-        import torch
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms = max_over_ranks(ms)
     ok = bool(np.isfinite(h_out[512:1024]).all())
     for p in ptrs:
         capi.check(capi.lib().bricks_host_free(p))
@@ -356,10 +492,14 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--all-stencils", action="store_true", help="add kernel-only numbers for 7/13/25/125-point")
+    ap.add_argument("--dom", type=int, default=STRONG_DOM, help="strong workloads: global grid edge")
+    ap.add_argument("--sdom", type=int, default=STRONG_SDOM, help="strong workloads: subdomain edge")
     args = ap.parse_args()
     which = WORKLOADS[args.workload]
     if args.impl == "reference":
         return run_reference(args, which)
+    if args.workload.startswith("strong"):
+        return run_gpu_strong(args, which)
     return run_gpu(args, which)
 
 
