@@ -72,12 +72,29 @@ _SIGS = {
 }
 
 
+def _preload_nccl():
+    """libbricks_b200.so needs libnccl.so.2.  When PyTorch's bundled NCCL wheel is installed, load
+    THAT copy first so that this library and a later `import torch` share one NCCL (the system
+    copy is older and lacks symbols libtorch_cuda wants)."""
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for base in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(base, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                C.CDLL(path, mode=C.RTLD_GLOBAL)
+                return
+    except Exception:  # noqa: BLE001 -- fall back to the dynamic linker's search path
+        pass
+
+
 def lib():
     global _lib
     if _lib is None:
         if not os.path.exists(LIBPATH):
             raise BricksError("libbricks_b200.so is not built (run __graft_entry__.build()); "
                               "there is no CPU fallback")
+        _preload_nccl()
         L = C.CDLL(LIBPATH)
         for name, (res, args) in _SIGS.items():
             fn = getattr(L, name)
