@@ -429,41 +429,38 @@ def run_gpu_strong(args, which):
 
 def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
     """Same step, HOST buffers: every step copies its input field host->device from pinned
-    memory, runs exchange + sweeps, and copies the resulting field device->host."""
+    memory, runs exchange + sweeps, and copies the resulting field device->host.  The steps are
+    software-pipelined (WeakSubdomain.host_steps): upload of step n and download of step n-1
+    overlap the sweeps, as a host application streaming fields through the GPU would run them."""
     import ctypes as C
     from bricklib_b200 import capi
     n = sub.dec.nbricks * 512
     ptrs = []
-    for _ in range(2):
+    for _ in range(3):
         p = C.c_void_p()
         capi.check(capi.lib().bricks_host_alloc(C.byref(p), n * 8))
         ptrs.append(p)
-    h_in = np.ctypeslib.as_array((C.c_double * n).from_address(ptrs[0].value))
-    h_out = np.ctypeslib.as_array((C.c_double * n).from_address(ptrs[1].value))
+    h_in, h_out0, h_out1 = (np.ctypeslib.as_array((C.c_double * n).from_address(p.value)) for p in ptrs)
     h_in[:] = field
-    steps = max(1, min(args.steps, args.e2e_steps))
-
-    def one():
-        ctx.h2d(sub.d_a, h_in)
-        sub.step(overlap=not args.no_overlap)
-        ctx.d2h(h_out, sub.d_a)
-
-    one()
+    steps = max(2, min(args.steps, args.e2e_steps))
+    overlap = not args.no_overlap
+    sub.host_steps(h_in, [h_out0, h_out1], 2, overlap)
     barrier()
     ctx.timer_start(2)
-    for _ in range(steps):
-        one()
+    sub.host_steps(h_in, [h_out0, h_out1], steps, overlap)
     ctx.timer_stop(2)
     ms = ctx.timer_ms(2)
     barrier()
     ms = max_over_ranks(ms)
-    ok = bool(np.isfinite(h_out[512:1024]).all())
+    ok = bool(np.isfinite(h_out0[512:1024]).all() and np.isfinite(h_out1[512:1024]).all()
+              and np.array_equal(h_out0[:4096], h_out1[:4096]))
     for p in ptrs:
         capi.check(capi.lib().bricks_host_free(p))
     return {"value": pts_step / (ms / steps * 1e-3) * 1e-9, "unit": "GStencil/s", "h2d_bytes_per_step": n * 8,
             "d2h_bytes_per_step": n * 8, "ms_per_step": ms / steps, "steps": steps, "result_finite": ok,
-            "what": "per step: H2D of the whole input field from pinned host memory, exchange + sweeps, D2H of the "
-                    "whole result field (per GPU)"}
+            "what": "per step and GPU: H2D of the whole input field from pinned host memory, exchange + sweeps, D2H of "
+                    "the whole result field; steps software-pipelined over two device buffer sets and two copy "
+                    "streams (upload n+1 and download n-1 overlap the sweeps of n)"}
 
 
 def all_stencils(ctx, sub, peak):

@@ -9,13 +9,17 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
-LIB = os.path.join(LIBDIR, "libbricks_b200.so")
+# kernel experiments: BRICKS_EXP_NAME=x BRICKS_EXP_FLAGS="-DFOO" builds lib/libbricks_b200_x.so beside the
+# product library (load it with BRICKS_LIB=...); the product build never sets these
+EXP = os.environ.get("BRICKS_EXP_NAME", "")
+LIB = os.path.join(LIBDIR, "libbricks_b200%s.so" % ("_" + EXP if EXP else ""))
 SOURCES = ["context.cu", "plan.cu", "stencil_march.cu", "stencil_naive.cu", "exchange.cu", "probe.cu",
            "host_capi.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "-Xcompiler", "-Wno-unused-function",
          "--expt-relaxed-constexpr", "-ccbin", "/usr/bin/g++", "-Xcompiler", "-fopenmp"]
+FLAGS += os.environ.get("BRICKS_EXP_FLAGS", "").split()
 
 
 def _stale(target, deps):
@@ -27,7 +31,7 @@ def _stale(target, deps):
 
 def build(verbose=False, force=False, ptxas_v=False):
     os.makedirs(LIBDIR, exist_ok=True)
-    objdir = os.path.join(LIBDIR, "obj")
+    objdir = os.path.join(LIBDIR, "obj" + ("_" + EXP if EXP else ""))
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     for root, _, files in os.walk(os.path.join(HERE, "..", "include")):

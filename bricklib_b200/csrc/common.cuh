@@ -44,7 +44,7 @@ extern unsigned long long g_launches;
     }                                                                                   \
   } while (0)
 
-constexpr int kNumStreams = 2;
+constexpr int kNumStreams = 4;
 constexpr int kNumTimers = 16;
 
 }  // namespace bricks
@@ -52,7 +52,7 @@ constexpr int kNumTimers = 16;
 struct bricks_ctx {
   int device = 0;
   int sm_count = 0;
-  cudaStream_t streams[bricks::kNumStreams] = {nullptr, nullptr};
+  cudaStream_t streams[bricks::kNumStreams] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t xev = nullptr; /* cross-stream dependency */
   cudaEvent_t t0[bricks::kNumTimers] = {}, t1[bricks::kNumTimers] = {};
   ncclComm_t comm = nullptr;
@@ -99,8 +99,13 @@ struct bricks_plan {
   unsigned nbricks = 0;
   unsigned *grid_dev = nullptr;
   unsigned *adj_dev = nullptr;
-  MarchItem *items_dev = nullptr; /* items for a given max column length */
-  int nitems = 0;
+  /* work items per column-segment length: the best length differs by stencil (plan.cu) */
+  struct ItemList {
+    MarchItem *dev = nullptr;
+    int n = 0;
+  };
+  std::map<unsigned, ItemList> items;
+  std::vector<unsigned> boxes; /* kept to build further item lists */
   unsigned *blist_dev = nullptr; /* flat list of every brick in the boxes (naive kernel) */
   long nlist = 0;
   std::map<FieldKey, FieldDev *> fields; /* device arrays, one FieldDev per field */
@@ -119,6 +124,11 @@ struct bricks_exchange {
 };
 
 namespace bricks {
+/* longest column (brick layers) one warp marches for this stencil; measured on B200
+ * (profiles/r01_column_length.txt) */
+unsigned column_length(int stencil_id);
+/* the plan's item list for that column length (built and uploaded on first use) */
+int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems);
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
                unsigned bj, unsigned bk, bool swizzle64);
 }

@@ -4,6 +4,8 @@
 #include <algorithm>
 #include <cstring>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace bricks {
@@ -52,10 +54,25 @@ int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_e
 
 /* longest column a single warp marches; chosen so a 66-layer column splits evenly and the
  * pre/post-roll overhead stays below ~5 % */
-static const unsigned kMaxColumn = 11;
+unsigned column_length(int stencil_id) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char *e = getenv("BRICKS_MAXCOL"); /* tuning knob for experiments */
+    forced = (e && atoi(e) > 0 && atoi(e) < 32) ? atoi(e) : 0;
+  }
+  if (forced) return (unsigned)forced;
+  /* short columns give the scheduler more, smaller items (bandwidth-bound stars); long columns
+   * amortise the pre-/post-roll planes (arithmetic-bound cube) */
+  switch (stencil_id) {
+    case BRICKS_ST_125PT: return 17;
+    case BRICKS_ST_25PT: return 10;
+    case BRICKS_ST_13PT: return 9;
+    default: return 7;
+  }
+}
 
-static void build_items(const unsigned gdims[3], int nboxes, const unsigned *boxes,
-                        std::vector<MarchItem> &items, std::vector<unsigned> &cells) {
+static void build_items(const unsigned gdims[3], int nboxes, const unsigned *boxes, unsigned kMaxColumn,
+                        std::vector<MarchItem> &items, std::vector<unsigned> *cells) {
   for (int b = 0; b < nboxes; ++b) {
     const unsigned *lo = boxes + 6 * b, *hi = lo + 3;
     if (hi[0] <= lo[0] || hi[1] <= lo[1] || hi[2] <= lo[2]) continue;
@@ -78,11 +95,30 @@ static void build_items(const unsigned gdims[3], int nboxes, const unsigned *box
           items.push_back(it);
         }
     }
+    if (!cells) continue;
     for (unsigned k = lo[2]; k < hi[2]; ++k)
       for (unsigned j = lo[1]; j < hi[1]; ++j)
         for (unsigned i = lo[0]; i < hi[0]; ++i)
-          cells.push_back((k * gdims[1] + j) * gdims[0] + i);
+          cells->push_back((k * gdims[1] + j) * gdims[0] + i);
   }
+}
+
+int plan_items(bricks_plan *p, unsigned maxcol, const MarchItem **items_dev, int *nitems) {
+  auto it = p->items.find(maxcol);
+  if (it == p->items.end()) {
+    std::vector<MarchItem> items;
+    build_items(p->gdims, (int)(p->boxes.size() / 6), p->boxes.data(), maxcol, items, nullptr);
+    bricks_plan::ItemList l;
+    l.n = (int)items.size();
+    cudaStream_t s = p->ctx->streams[BRICKS_STREAM_COMPUTE];
+    BRK_CUDA(cudaMalloc(&l.dev, items.size() * sizeof(MarchItem)));
+    BRK_CUDA(cudaMemcpyAsync(l.dev, items.data(), items.size() * sizeof(MarchItem), cudaMemcpyHostToDevice, s));
+    BRK_CUDA(cudaStreamSynchronize(s)); /* `items` dies here */
+    it = p->items.emplace(maxcol, l).first;
+  }
+  *items_dev = it->second.dev;
+  *nitems = it->second.n;
+  return 0;
 }
 
 }  // namespace bricks
@@ -110,25 +146,22 @@ int bricks_plan_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigne
   for (size_t c = 0; c < ncell; ++c) BRK_ARG(grid_host[c] < nbricks);
   std::vector<MarchItem> items;
   std::vector<unsigned> cells;
-  build_items(gdims, nboxes, boxes, items, cells);
+  build_items(gdims, nboxes, boxes, 11, items, &cells);
   BRK_ARG(!items.empty());
+  p->boxes.assign(boxes, boxes + 6 * (size_t)nboxes);
   std::vector<unsigned> blist(cells.size());
   for (size_t n = 0; n < cells.size(); ++n) blist[n] = grid_host[cells[n]];
 
   cudaStream_t s = ctx->streams[BRICKS_STREAM_COMPUTE];
   BRK_CUDA(cudaMalloc(&p->grid_dev, ncell * sizeof(unsigned)));
   BRK_CUDA(cudaMalloc(&p->adj_dev, (size_t)nbricks * 27 * sizeof(unsigned)));
-  BRK_CUDA(cudaMalloc(&p->items_dev, items.size() * sizeof(MarchItem)));
   BRK_CUDA(cudaMalloc(&p->blist_dev, blist.size() * sizeof(unsigned)));
   BRK_CUDA(cudaMemcpyAsync(p->grid_dev, grid_host, ncell * sizeof(unsigned), cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaMemcpyAsync(p->adj_dev, adj_host, (size_t)nbricks * 27 * sizeof(unsigned),
                            cudaMemcpyHostToDevice, s));
-  BRK_CUDA(cudaMemcpyAsync(p->items_dev, items.data(), items.size() * sizeof(MarchItem),
-                           cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaMemcpyAsync(p->blist_dev, blist.data(), blist.size() * sizeof(unsigned),
                            cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaStreamSynchronize(s)); /* host vectors die here */
-  p->nitems = (int)items.size();
   p->nlist = (long)blist.size();
   *out = p;
   return 0;
@@ -139,7 +172,7 @@ int bricks_plan_destroy(bricks_plan *p) {
   cudaSetDevice(p->ctx->device);
   cudaFree(p->grid_dev);
   cudaFree(p->adj_dev);
-  cudaFree(p->items_dev);
+  for (auto &kv : p->items) cudaFree(kv.second.dev);
   cudaFree(p->blist_dev);
   for (auto &kv : p->fields) cudaFree(kv.second);
   delete p;

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? 176 : 255) march_kernel
 }
 
 template <int R, bool CUBE, int VAR, int P>
-int launch(bricks_plan *plan, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
+int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
   using L = dev::StageLayout<R, CUBE, P>;
   const int smem = 2 * L::BYTES + 64;
   auto kern = march_kernel<R, CUBE, VAR, P>;
@@ -157,14 +157,15 @@ int launch(bricks_plan *plan, const FieldDev *fields, int nfields, const double 
     done = true;
   }
   MarchParams prm;
-  prm.items = plan->items_dev;
+  int nitems = 0;
+  if (int rc = bricks::plan_items(plan, bricks::column_length(stencil_id), &prm.items, &nitems)) return rc;
   prm.grid = plan->grid_dev;
   prm.adj = plan->adj_dev;
   prm.fields = fields;
   prm.gd0 = plan->gdims[0];
   prm.gd1 = plan->gdims[1];
   for (int i = 0; i < 10; ++i) prm.c[i] = c[i];
-  kern<<<dim3(plan->nitems, nfields), 32, smem, s>>>(prm);
+  kern<<<dim3(nitems, nfields), 32, smem, s>>>(prm);
   BRK_CUDA(cudaGetLastError());
   ++bricks::g_launches;
   return 0;
@@ -247,25 +248,25 @@ extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, co
     case BRICKS_ST_7PT_COEFF:
       BRK_ARG(coeff_host);
       for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
-      return P == 8 ? launch<1, false, 1, 8>(plan, fields, nfields, c, s)
-                    : launch<1, false, 1, 4>(plan, fields, nfields, c, s);
+      return P == 8 ? launch<1, false, 1, 8>(plan, stencil_id, fields, nfields, c, s)
+                    : launch<1, false, 1, 4>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_7PT: /* MPI_ALPHA, MPI_BETA (stencils/fake.h:11-12) */
       c[0] = 0.4, c[1] = 0.1;
-      return P == 8 ? launch<1, false, 0, 8>(plan, fields, nfields, c, s)
-                    : launch<1, false, 0, 4>(plan, fields, nfields, c, s);
+      return P == 8 ? launch<1, false, 0, 8>(plan, stencil_id, fields, nfields, c, s)
+                    : launch<1, false, 0, 4>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_13PT: /* MPI_B0..B2 (fake.h:20-22) */
       c[0] = 0.4, c[1] = 0.07, c[2] = 0.03;
-      return P == 8 ? launch<2, false, 0, 8>(plan, fields, nfields, c, s)
-                    : launch<2, false, 0, 4>(plan, fields, nfields, c, s);
+      return P == 8 ? launch<2, false, 0, 8>(plan, stencil_id, fields, nfields, c, s)
+                    : launch<2, false, 0, 4>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_25PT: /* MPI_A0..A4 (fake.h:14-18) */
       c[0] = 0.1, c[1] = 0.06, c[2] = 0.045, c[3] = 0.03, c[4] = 0.015;
-      return P == 8 ? launch<4, false, 0, 8>(plan, fields, nfields, c, s)
-                    : launch<4, false, 0, 4>(plan, fields, nfields, c, s);
+      return P == 8 ? launch<4, false, 0, 8>(plan, stencil_id, fields, nfields, c, s)
+                    : launch<4, false, 0, 4>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_125PT: { /* MPI_C0..C9 (fake.h:24-33) */
       const double cc[10] = {0.1, 0.04, 0.03, 0.01, 0.006, 0.004, 0.005, 0.002, 0.003, 0.001};
       for (int i = 0; i < 10; ++i) c[i] = cc[i];
-      return P == 8 ? launch<2, true, 0, 8>(plan, fields, nfields, c, s)
-                    : launch<2, true, 0, 4>(plan, fields, nfields, c, s);
+      return P == 8 ? launch<2, true, 0, 8>(plan, stencil_id, fields, nfields, c, s)
+                    : launch<2, true, 0, 4>(plan, stencil_id, fields, nfields, c, s);
     }
     default:
       bricks::set_error("unknown stencil id %d", stencil_id);

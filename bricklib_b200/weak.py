@@ -79,16 +79,18 @@ class WeakSubdomain(object):
         return self.ctx.download(self.d_a, self.dec.nbricks * 512)
 
     # ------------------------------------------------------------------ one step
-    def step(self, overlap=True, coeff=None):
+    def step(self, overlap=True, coeff=None, pair=None):
         """exchange(d_a) + ST_ITER ping-pong sweeps; the result ends in d_a (ST_ITER is even).
-        Everything is enqueued asynchronously; returns the number of kernels launched."""
+        Everything is enqueued asynchronously; returns the number of kernels launched.
+        `pair` = (in/out storage, scratch storage) overrides (d_a, d_b)."""
         C, X = capi.STREAM_COMPUTE, capi.STREAM_COMM
         n0 = capi.launch_count()
         ctx, st = self.ctx, self.stencil
+        d_a, d_b = pair if pair is not None else (self.d_a, self.d_b)
         # the exchange reads the skin written by the previous step's last sweep
         ctx.stream_wait(X, C)
-        self.exchange.run(self.d_a, X)
-        src, dst = self.d_a, self.d_b
+        self.exchange.run(d_a, X)
+        src, dst = d_a, d_b
         for it in range(self.st_iter):
             last = it == self.st_iter - 1
             if it == 0:
@@ -104,15 +106,47 @@ class WeakSubdomain(object):
             else:
                 self.plan_full.stencil(st, src, dst, 512, 512, coeff, C)
             src, dst = dst, src
-        assert src == self.d_a
+        assert src == d_a
         # NCCL launches its own kernels; count ours plus one per remote exchange
         self.launches_per_step = capi.launch_count() - n0
         return self.launches_per_step
+
+    # ------------------------------------------------------------------ host-fed steps
+    def host_steps(self, h_in, h_outs, steps, overlap=True):
+        """`steps` independent steps fed from and drained to HOST memory (pinned numpy views):
+        step n uploads h_in, runs exchange + sweeps and downloads the result to h_outs[n % 2].
+        Software-pipelined over two device storage pairs and the two copy streams: the upload
+        of step n and the download of step n-1 run while step n-1 / n computes, so a step costs
+        max(upload, download, compute) instead of their sum.  Returns after everything is
+        enqueued; the caller synchronises."""
+        ctx = self.ctx
+        C, U, D = capi.STREAM_COMPUTE, capi.STREAM_H2D, capi.STREAM_D2H
+        if not hasattr(self, "_pairs"):
+            a1, b1 = ctx.malloc(self.nbytes), ctx.malloc(self.nbytes)
+            ctx.memset(b1, 0, self.nbytes)
+            ctx.memset(a1, 0, self.nbytes)
+            self._pairs = [(self.d_a, self.d_b), (a1, b1)]
+        for n in range(steps + 1):
+            if n < steps:
+                pa = self._pairs[n & 1]
+                ctx.stream_wait(U, D)          # the download of step n-2 has drained this pair
+                ctx.h2d(pa[0], h_in, stream=U)
+            if n >= 1:
+                pb = self._pairs[(n - 1) & 1]
+                ctx.stream_wait(D, C)          # step n-1 has finished computing
+                ctx.d2h(h_outs[(n - 1) & 1], pb[0], stream=D)
+            if n < steps:
+                ctx.stream_wait(C, U)          # the upload of step n has landed
+                self.step(overlap=overlap, pair=pa)
+        ctx.stream_wait(C, D)
 
     def close(self):
         for p in (self.plan_full, self.plan_inner, self.plan_shell, self.plan_owned):
             p.close()
         self.exchange.close()
+        for a1, b1 in getattr(self, "_pairs", [])[1:]:
+            self.ctx.free(a1)
+            self.ctx.free(b1)
         self.ctx.free(self.d_a)
         self.ctx.free(self.d_b)
         self.dec.close()

@@ -45,8 +45,9 @@ enum {
   BRICKS_ST_125PT = 125
 };
 
-/* streams of a context */
-enum { BRICKS_STREAM_COMPUTE = 0, BRICKS_STREAM_COMM = 1 };
+/* streams of a context: sweeps, halo exchange (highest priority), and two copy streams so that a
+ * host-fed pipeline can upload the next field and download the last result while sweeps run */
+enum { BRICKS_STREAM_COMPUTE = 0, BRICKS_STREAM_COMM = 1, BRICKS_STREAM_H2D = 2, BRICKS_STREAM_D2H = 3 };
 
 /* ---- context, memory, copies: replaces gpuMalloc/gpuMemcpy/gpuFree (brick-cuda.h:12-24),
  * movBrickInfo / movBrickStorage (brick-gpu.h:39-99, whose `unsigned` byte counts overflow

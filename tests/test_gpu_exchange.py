@@ -204,3 +204,21 @@ def test_multi_gpu_weak_step_equals_global_periodic_array(built, oracle, nranks)
         ck, cj, ci = where(r)
         e = exp[32 * ck:32 * ck + 32, 32 * cj:32 * cj + 32, 32 * ci:32 * ci + 32]
         assert relerr(interior_of(got[r]), e) <= REL_TOL, r
+
+
+def test_host_steps_pipeline_matches_plain_step(ctx, built):
+    """the software-pipelined host-fed steps (two device pairs, copy streams) give the same field
+    as upload -> step -> download, for every step of the pipeline"""
+    from bricklib_b200 import weak
+    sub = weak.WeakSubdomain(ctx, (32, 32, 32), 125)
+    f = sub.host_field()
+    sub.upload(f)
+    sub.step(overlap=True)
+    ctx.sync()
+    want = sub.download()
+    outs = [np.zeros_like(f), np.zeros_like(f)]
+    sub.host_steps(f, outs, 5, overlap=True)
+    ctx.sync()
+    for o in outs:
+        assert np.array_equal(o.view(np.uint64), want.view(np.uint64))
+    sub.close()
