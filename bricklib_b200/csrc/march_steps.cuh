@@ -46,17 +46,16 @@ __device__ __forceinline__ void gather_i(const double (&x)[4], const double (&h)
   }
 }
 
+/* Every lane loads the i-face row of its (brick, row): the two lanes of a row read the same 16
+ * bytes (a broadcast, no extra wavefront), so the load needs neither a predicate nor a zero fill;
+ * only the lane on the footprint edge uses the value (gather_i). */
 template <int HW>
-__device__ __forceinline__ void ld_halo(const char *st, int off, bool halo, double (&h)[HW]) {
+__device__ __forceinline__ void ld_halo(const char *st, int off, bool /*halo*/, double (&h)[HW]) {
 #pragma unroll
-  for (int q = 0; q < HW; ++q) h[q] = 0.0;
-  if (halo) {
-#pragma unroll
-    for (int q = 0; q < HW / 2; ++q) {
-      const double2 v = *reinterpret_cast<const double2 *>(st + off + 16 * q);
-      h[2 * q] = v.x;
-      h[2 * q + 1] = v.y;
-    }
+  for (int q = 0; q < HW / 2; ++q) {
+    const double2 v = *reinterpret_cast<const double2 *>(st + off + 16 * q);
+    h[2 * q] = v.x;
+    h[2 * q + 1] = v.y;
   }
 }
 
@@ -181,12 +180,17 @@ __device__ __forceinline__ void cube_step(const char *st, const LaneK<2, true, P
       /* coefficient classes of stencils/mpi125pt.py:12-33: c[0]=(0,0,0) c[1]=(0,0,1) c[2]=(0,0,2)
        * c[3]=(0,1,1) c[4]=(0,1,2) c[5]=(0,2,2) c[6]=(1,1,1) c[7]=(1,1,2) c[8]=(1,2,2) c[9]=(2,2,2) */
       double g[3];
-      g[0] = 0.0;
-      if (MODE == 1)
-        g[0] = c[0] * q00 + c[1] * q01 + c[2] * q02 + c[3] * q11 + c[4] * q12 + c[5] * q22;
+      if (MODE == 1) { /* the in-plane part goes straight into its accumulator: six FMAs */
+        double a0 = acc[z + 2][m];
+        a0 = fma(c[0], q00, a0);
+        a0 = fma(c[1], q01, a0);
+        a0 = fma(c[2], q02, a0);
+        a0 = fma(c[3], q11, a0);
+        a0 = fma(c[4], q12, a0);
+        acc[z + 2][m] = fma(c[5], q22, a0);
+      }
       g[1] = c[1] * q00 + c[3] * q01 + c[4] * q02 + c[6] * q11 + c[7] * q12 + c[8] * q22;
       g[2] = c[2] * q00 + c[4] * q01 + c[5] * q02 + c[7] * q11 + c[8] * q12 + c[9] * q22;
-      if (MODE == 1) acc[z + 2][m] += g[0];
       if (MODE != 0) {
         acc[z + 1][m] += g[1];
         acc[z][m] += g[2];

@@ -7,6 +7,11 @@
 
 #include "march_steps.cuh"
 
+/* register cap of the cube kernel: 168 keeps twelve one-warp CTAs per SM */
+#ifndef MARCH_CUBE_REGS
+#define MARCH_CUBE_REGS 168
+#endif
+
 namespace {
 
 struct MarchParams {
@@ -20,7 +25,7 @@ struct MarchParams {
 
 template <int R, bool CUBE, int VAR, int P>
 /* register cap for the cube: measured best on B200 (profiles/r01_maxnreg_sweep.txt) */
-__global__ void __launch_bounds__(32) __maxnreg__(CUBE ? 176 : 255) march_kernel(const __grid_constant__ MarchParams prm) {
+__global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : 255) march_kernel(const __grid_constant__ MarchParams prm) {
   using L = dev::StageLayout<R, CUBE, P>;
   constexpr int H = 8 / P;
   extern __shared__ __align__(1024) char smem[];
