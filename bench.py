@@ -456,11 +456,13 @@ def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
               and np.array_equal(h_out0[:4096], h_out1[:4096]))
     for p in ptrs:
         capi.check(capi.lib().bricks_host_free(p))
-    return {"value": pts_step / (ms / steps * 1e-3) * 1e-9, "unit": "GStencil/s", "h2d_bytes_per_step": n * 8,
-            "d2h_bytes_per_step": n * 8, "ms_per_step": ms / steps, "steps": steps, "result_finite": ok,
-            "what": "per step and GPU: H2D of the whole input field from pinned host memory, exchange + sweeps, D2H of "
-                    "the whole result field; steps software-pipelined over two device buffer sets and two copy "
-                    "streams (upload n+1 and download n-1 overlap the sweeps of n)"}
+    return {"value": pts_step / (ms / steps * 1e-3) * 1e-9, "unit": "GStencil/s",
+            "h2d_bytes_per_step": sub.host_step_bytes, "d2h_bytes_per_step": sub.host_step_bytes,
+            "ms_per_step": ms / steps, "steps": steps, "result_finite": ok,
+            "what": "per step and GPU: H2D of the input field (all owned bricks; ghost bricks are filled by the "
+                    "exchange) from pinned host memory, exchange + sweeps, D2H of the result field (all owned bricks); "
+                    "steps software-pipelined over two device buffer sets and two copy streams (upload n+1 and "
+                    "download n-1 overlap the sweeps of n)"}
 
 
 def all_stencils(ctx, sub, peak):

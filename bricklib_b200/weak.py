@@ -121,6 +121,10 @@ class WeakSubdomain(object):
         enqueued; the caller synchronises."""
         ctx = self.ctx
         C, U, D = capi.STREAM_COMPUTE, capi.STREAM_H2D, capi.STREAM_D2H
+        # ghost bricks are neither input (the exchange fills them) nor result: BrickDecomp numbers
+        # them last, so only bricks [0, sep_pos[1]) cross the bus
+        nbytes = int(self.dec.sep_pos[1]) * 512 * 8
+        self.host_step_bytes = nbytes
         if not hasattr(self, "_pairs"):
             a1, b1 = ctx.malloc(self.nbytes), ctx.malloc(self.nbytes)
             ctx.memset(b1, 0, self.nbytes)
@@ -130,11 +134,11 @@ class WeakSubdomain(object):
             if n < steps:
                 pa = self._pairs[n & 1]
                 ctx.stream_wait(U, D)          # the download of step n-2 has drained this pair
-                ctx.h2d(pa[0], h_in, stream=U)
+                ctx.h2d(pa[0], h_in, stream=U, nbytes=nbytes)
             if n >= 1:
                 pb = self._pairs[(n - 1) & 1]
                 ctx.stream_wait(D, C)          # step n-1 has finished computing
-                ctx.d2h(h_outs[(n - 1) & 1], pb[0], stream=D)
+                ctx.d2h(h_outs[(n - 1) & 1], pb[0], stream=D, nbytes=nbytes)
             if n < steps:
                 ctx.stream_wait(C, U)          # the upload of step n has landed
                 self.step(overlap=overlap, pair=pa)
