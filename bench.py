@@ -243,8 +243,9 @@ def run_gpu(args, which):
     sub.upload(field)
 
     # ---- device-resident timing: W warm-up steps, then exactly K steps
+    early = not args.no_early  # start the next step's exchange behind the last sweep's skin bricks
     for _ in range(max(args.warmup, 3)):
-        sub.step(overlap=not args.no_overlap)
+        sub.step(overlap=not args.no_overlap, early=early)
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
@@ -252,7 +253,8 @@ def run_gpu(args, which):
     n0 = capi.launch_count()
     ctx.timer_start(0)
     for _ in range(args.steps):
-        sub.step(overlap=not args.no_overlap)
+        sub.step(overlap=not args.no_overlap, early=early)
+    ctx.stream_wait(capi.STREAM_COMPUTE, capi.STREAM_COMM)  # nothing of the K steps is left in flight
     ctx.timer_stop(0)
     ms = ctx.timer_ms(0)
     barrier()
@@ -294,7 +296,7 @@ def run_gpu(args, which):
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": make_config(which, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": roofline,
-                "overlap": not args.no_overlap,
+                "overlap": not args.no_overlap, "early_exchange": early and not args.no_overlap,
                 "exchange_bytes_per_step_per_gpu": sub.exchange_bytes}
         if not args.no_cpu:
             try:
@@ -487,6 +489,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="weak125", choices=sorted(WORKLOADS))
     ap.add_argument("--no-overlap", action="store_true", help="serial exchange then sweeps (reference schedule)")
+    ap.add_argument("--no-early", action="store_true", help="start each exchange at the step boundary only")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=10)

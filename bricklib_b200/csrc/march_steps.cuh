@@ -106,13 +106,16 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
     for (int r = 1; r <= R; ++r)
 #pragma unroll
       for (int m = 0; m < 4; ++m) {
-        /* input plane z feeds output planes z-r (needs x(k+r)) and z+r (needs x(k-r)) */
-        if (MODE != 0) acc[z + R - r][m] += (VAR ? c[5] : c[r]) * x[m];
+        /* input plane z feeds output planes z-r (needs x(k+r)) and z+r (needs x(k-r)).  Explicit
+         * FMAs: left to the compiler, the product shared by both directions becomes one rounded
+         * DMUL in the main stage but an FMA in the rolls, and results would depend (in the last
+         * bit) on where a column starts. */
+        if (MODE != 0) acc[z + R - r][m] = fma(VAR ? c[5] : c[r], x[m], acc[z + R - r][m]);
         if (MODE != 2) {
           if (r == R)
             acc[z + R + r][m] = (VAR ? c[6] : c[r]) * x[m];
           else
-            acc[z + R + r][m] += (VAR ? c[6] : c[r]) * x[m];
+            acc[z + R + r][m] = fma(VAR ? c[6] : c[r], x[m], acc[z + R + r][m]);
         }
       }
     store_done<R, MODE>(o, zbase, z, acc[z]);

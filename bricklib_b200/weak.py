@@ -28,6 +28,15 @@ def shell_boxes(g, inner_lo, inner_hi):
             ((0, a1, a2), (a0, b1, b2)), ((b0, a1, a2), (g0, b1, b2))]
 
 
+def shell_between(outer_lo, outer_hi, inner_lo, inner_hi):
+    """Six disjoint slabs covering [outer_lo, outer_hi) minus [inner_lo, inner_hi) (i fastest)."""
+    (o0, o1, o2), (g0, g1, g2) = outer_lo, outer_hi
+    (a0, a1, a2), (b0, b1, b2) = inner_lo, inner_hi
+    return [((o0, o1, o2), (g0, g1, a2)), ((o0, o1, b2), (g0, g1, g2)),
+            ((o0, o1, a2), (g0, a1, b2)), ((o0, b1, a2), (g0, g1, b2)),
+            ((o0, a1, a2), (a0, b1, b2)), ((b0, a1, a2), (g0, b1, b2))]
+
+
 class WeakSubdomain(object):
     """One rank's subdomain: BrickDecomp tables, two ping-pong storages on the device, the box
     plans of the sweep schedule and the exchange plan."""
@@ -57,6 +66,10 @@ class WeakSubdomain(object):
         self.plan_inner = capi.Plan(ctx, self.dec.grid, self.dec.adj, [inner])
         self.plan_shell = capi.Plan(ctx, self.dec.grid, self.dec.adj, shell_boxes(g, inner[0], inner[1]))
         self.plan_owned = capi.Plan(ctx, self.dec.grid, self.dec.adj, [owned])
+        # the owned bricks that some neighbour needs (skin) = owned box minus the inner box
+        self.plan_oskin = capi.Plan(ctx, self.dec.grid, self.dec.adj,
+                                    shell_between(owned[0], owned[1], inner[0], inner[1]))
+        self._exchange_in_flight = None  # storage whose exchange was started by the previous step
         ro, so, nbts, rp, sp = self.dec.exchange_plan(512)
         self.exchange = capi.Exchange(ctx, rank, ro, so, nbts, rp, sp)
         self.exchange_bytes = int(nbts.sum())
@@ -72,6 +85,8 @@ class WeakSubdomain(object):
         return f
 
     def upload(self, field):
+        self.ctx.sync()
+        self._exchange_in_flight = None
         self.ctx.h2d(self.d_a, field)
         self.ctx.sync()
 
@@ -79,17 +94,23 @@ class WeakSubdomain(object):
         return self.ctx.download(self.d_a, self.dec.nbricks * 512)
 
     # ------------------------------------------------------------------ one step
-    def step(self, overlap=True, coeff=None, pair=None):
+    def step(self, overlap=True, coeff=None, pair=None, early=False):
         """exchange(d_a) + ST_ITER ping-pong sweeps; the result ends in d_a (ST_ITER is even).
         Everything is enqueued asynchronously; returns the number of kernels launched.
-        `pair` = (in/out storage, scratch storage) overrides (d_a, d_b)."""
+        `pair` = (in/out storage, scratch storage) overrides (d_a, d_b).
+        `early`: the last sweep computes the skin bricks first and the exchange of the NEXT step
+        starts as soon as they are written, so it also hides behind the rest of that sweep (only
+        valid when the next step continues from this result; any host access to the field must
+        be preceded by ctx.sync(), which covers the communication stream too)."""
         C, X = capi.STREAM_COMPUTE, capi.STREAM_COMM
         n0 = capi.launch_count()
         ctx, st = self.ctx, self.stencil
         d_a, d_b = pair if pair is not None else (self.d_a, self.d_b)
-        # the exchange reads the skin written by the previous step's last sweep
-        ctx.stream_wait(X, C)
-        self.exchange.run(d_a, X)
+        if self._exchange_in_flight != d_a:
+            # the exchange reads the skin written by the previous step's last sweep
+            ctx.stream_wait(X, C)
+            self.exchange.run(d_a, X)
+        self._exchange_in_flight = None
         src, dst = d_a, d_b
         for it in range(self.st_iter):
             last = it == self.st_iter - 1
@@ -101,6 +122,12 @@ class WeakSubdomain(object):
                 else:
                     ctx.stream_wait(C, X)
                     self.plan_full.stencil(st, src, dst, 512, 512, coeff, C)
+            elif last and early and overlap:
+                self.plan_oskin.stencil(st, src, dst, 512, 512, coeff, C)
+                ctx.stream_wait(X, C)
+                self.exchange.run(dst, X)  # dst == d_a: input of the next step
+                self._exchange_in_flight = dst
+                self.plan_inner.stencil(st, src, dst, 512, 512, coeff, C)
             elif last:
                 self.plan_owned.stencil(st, src, dst, 512, 512, coeff, C)
             else:
@@ -121,6 +148,9 @@ class WeakSubdomain(object):
         enqueued; the caller synchronises."""
         ctx = self.ctx
         C, U, D = capi.STREAM_COMPUTE, capi.STREAM_H2D, capi.STREAM_D2H
+        if self._exchange_in_flight is not None:  # an early exchange of a device-resident run
+            ctx.sync()
+            self._exchange_in_flight = None
         # ghost bricks are neither input (the exchange fills them) nor result: BrickDecomp numbers
         # them last, so only bricks [0, sep_pos[1]) cross the bus
         nbytes = int(self.dec.sep_pos[1]) * 512 * 8
@@ -145,7 +175,7 @@ class WeakSubdomain(object):
         ctx.stream_wait(C, D)
 
     def close(self):
-        for p in (self.plan_full, self.plan_inner, self.plan_shell, self.plan_owned):
+        for p in (self.plan_full, self.plan_inner, self.plan_shell, self.plan_owned, self.plan_oskin):
             p.close()
         self.exchange.close()
         for a1, b1 in getattr(self, "_pairs", [])[1:]:

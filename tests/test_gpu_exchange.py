@@ -156,8 +156,9 @@ def test_multi_gpu_exchange_matches_oracle_bit_exact(built, oracle, nranks):
         assert np.array_equal(got[r].view(np.uint64), exp[r].view(np.uint64)), r
 
 
+@pytest.mark.parametrize("early", (False, True))
 @pytest.mark.parametrize("nranks", (2, 8))
-def test_multi_gpu_weak_step_equals_global_periodic_array(built, oracle, nranks):
+def test_multi_gpu_weak_step_equals_global_periodic_array(built, oracle, nranks, early):
     """Weak scaling end to end: P subdomains on a periodic process grid, exchange over NCCL,
     ST_ITER sweeps with the overlapped schedule == periodic sweeps of the assembled global array."""
     if _ndev(built) < nranks:
@@ -173,11 +174,13 @@ def test_multi_gpu_weak_step_equals_global_periodic_array(built, oracle, nranks)
         subs[r] = sub
         f0[r] = sub.host_field()
         sub.upload(f0[r])
-        sub.step(overlap=True)
+        for _ in range(nsteps):
+            sub.step(overlap=True, early=early)
         c.sync()
         out = sub.download()
         return out
 
+    nsteps = 2 if early else 1
     got = _ranks_in_threads(built, nranks, fn)
     odec = oracle.Decomp(dims, 8)
     ext = [48, 48, 48]
@@ -199,7 +202,7 @@ def test_multi_gpu_weak_step_equals_global_periodic_array(built, oracle, nranks)
     for r in range(nranks):
         ck, cj, ci = where(r)
         glob[32 * ck:32 * ck + 32, 32 * cj:32 * cj + 32, 32 * ci:32 * ci + 32] = interior_of(f0[r])
-    exp = _periodic_reference(oracle, which, glob, built.ST_ITER[which])
+    exp = _periodic_reference(oracle, which, glob, nsteps * built.ST_ITER[which])
     for r in range(nranks):
         ck, cj, ci = where(r)
         e = exp[32 * ck:32 * ck + 32, 32 * cj:32 * cj + 32, 32 * ci:32 * ci + 32]
@@ -224,4 +227,23 @@ def test_host_steps_pipeline_matches_plain_step(ctx, built):
     for o in outs:
         assert np.array_equal(o[:n].view(np.uint64), want[:n].view(np.uint64))
         assert not o[n:].any()
+    sub.close()
+
+
+@pytest.mark.parametrize("which", (7, 25, 125))
+def test_early_exchange_schedule_is_bitwise_the_plain_schedule(ctx, built, which):
+    """starting the next step's exchange right after the last sweep's skin bricks (early=True)
+    changes the order of launches only: three steps give the same bits on the owned bricks"""
+    from bricklib_b200 import weak
+    sub = weak.WeakSubdomain(ctx, (32, 40, 48), which)
+    f = sub.host_field()
+    res = []
+    for early in (False, True):
+        sub.upload(f)
+        for _ in range(3):
+            sub.step(overlap=True, early=early)
+        ctx.sync()
+        res.append(sub.download())
+    n = int(sub.dec.sep_pos[1]) * 512
+    assert np.array_equal(res[0][:n].view(np.uint64), res[1][:n].view(np.uint64))
     sub.close()
