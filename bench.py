@@ -243,7 +243,9 @@ def run_gpu(args, which):
     sub.upload(field)
 
     # ---- device-resident timing: W warm-up steps, then exactly K steps
-    early = not args.no_early  # start the next step's exchange behind the last sweep's skin bricks
+    # start the next step's exchange behind the last sweep's skin bricks: pays off when the
+    # exchange crosses NVLink (N > 1); on one GPU the plain schedule is faster (measured)
+    early = (not args.no_early) and world > 1
     for _ in range(max(args.warmup, 3)):
         sub.step(overlap=not args.no_overlap, early=early)
     barrier()
