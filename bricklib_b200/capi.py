@@ -70,6 +70,8 @@ _SIGS = {
     "bricks_probe_read": (C.c_int, [_vp, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
     "bricks_probe_mio": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "bricks_probe_tma_image": (C.c_int, [_vp, _vp, C.c_uint, C.c_size_t, C.c_uint, _vp]),
+    "bricks_probe_tma_issue": (C.c_int, [_vp, _vp, C.c_uint, C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_double),
+                                          C.POINTER(C.c_double)]),
 }
 
 
@@ -300,6 +302,12 @@ def probe_read(ctx, nbytes, reps=10):
 def probe_mio(ctx, mode):
     a, b = C.c_double(), C.c_double()
     check(lib().bricks_probe_mio(ctx._h, mode, C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
+def probe_tma_issue(ctx, field_dev, nbricks, mode, nops=240, step=512):
+    a, b = C.c_double(), C.c_double()
+    check(lib().bricks_probe_tma_issue(ctx._h, C.c_void_p(field_dev), nbricks, step, mode, nops, C.byref(a), C.byref(b)))
     return a.value, b.value
 
 

@@ -68,10 +68,13 @@ struct MarchItem {
 
 /* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane
  * pieces used for the pre-/post-roll of a column.  [0]=centre 8x8, [1]=i-face HWx8,
- * [2]=j-face 8xR, [3]=corner HWxR. */
+ * [2]=j-face 8xR, [3]=corner HWxR.  pair: the centre and j-face boxes over TWO bricks that are
+ * consecutive in storage (main stages only): the two pieces of a pair sit back to back in the
+ * stage, so one copy fills both. */
 struct alignas(64) MapSet {
   CUtensorMap main[4];
   CUtensorMap roll[4];
+  CUtensorMap pair[2]; /* [0]=centres of bricks b, b+1; [1]=j-face rows of bricks b, b+1 */
 };
 
 struct alignas(64) FieldDev {
@@ -80,6 +83,7 @@ struct alignas(64) FieldDev {
   unsigned long long out_step;
   unsigned long long pad[6];
 };
+static_assert(sizeof(FieldDev) % 64 == 0, "tensor maps in a FieldDev array must stay 64-byte aligned");
 
 struct FieldKey {
   int variant;
@@ -130,5 +134,5 @@ unsigned column_length(int stencil_id);
 /* the plan's item list for that column length (built and uploaded on first use) */
 int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems);
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
-               unsigned bj, unsigned bk, bool swizzle64);
+               unsigned bj, unsigned bk, bool swizzle64, unsigned bb = 1);
 }

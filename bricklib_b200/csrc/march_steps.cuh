@@ -135,6 +135,17 @@ __device__ __forceinline__ void cube_step(const char *st, const LaneK<2, true, P
                                           const double *__restrict__ c, double (&carry)[4][4],
                                           const OutPtrs &o, int zbase) {
   constexpr int R = 2, HW = 2;
+#ifdef MARCH_EXP_NOMATH /* experiment build only: the load/store skeleton without arithmetic */
+  if (MODE == 1) {
+#pragma unroll
+    for (int z = 0; z < NZ; ++z) {
+      double x[4];
+      ld_quad(st, lk.row0[R] + z * lk.rpitch[R], lk.row1[R] + z * lk.rpitch[R], x);
+      if (o.curv) st_quad(o.cur + (zbase + z) * 64, x);
+    }
+  }
+  return;
+#endif
   double acc[NZ + 4][4];
 #pragma unroll
   for (int a = 0; a < NZ + 4; ++a)

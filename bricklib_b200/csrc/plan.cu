@@ -30,7 +30,7 @@ static EncodeTiledFn get_encode() {
 /* A field is viewed as the 4-D tensor [brick][k][j][i] of fp64 with strides
  * (step*8, 512, 64, 8) bytes: the layout contract of include/brick.h:229-246 for fold <4,8>. */
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
-               unsigned bj, unsigned bk, bool swizzle64) {
+               unsigned bj, unsigned bk, bool swizzle64, unsigned bb) {
   EncodeTiledFn fn = get_encode();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -38,7 +38,7 @@ int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_e
   }
   cuuint64_t dims[4] = {8, 8, 8, nbricks};
   cuuint64_t strides[3] = {64, 512, (cuuint64_t)step_elems * 8};
-  cuuint32_t box[4] = {bi, bj, bk, 1};
+  cuuint32_t box[4] = {bi, bj, bk, bb};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<void *>(base), dims, strides, box,
                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE,

@@ -88,6 +88,51 @@ __global__ void __launch_bounds__(32) tma_image_kernel(const __grid_constant__ C
   for (int i = threadIdx.x; i < 512; i += 32) out[i] = reinterpret_cast<const double *>(smem)[i];
 }
 
+
+/* how many cycles one warp spends issuing TMA copies: mode 0 = one elected lane in a loop,
+ * mode 1 = one elected lane, eight copies per iteration in straight-line code, mode 2 = twelve
+ * lanes each issuing their own copy (the compiler's divergent-lane loop, as in march_kernel) */
+__global__ void tma_issue_kernel(const __grid_constant__ CUtensorMap map, int mode, int nops, unsigned nbricks,
+                                 long long *cycles) {
+  extern __shared__ __align__(1024) char smem[];
+  const uint32_t smem0 = dev::smem_u32(smem), bar = smem0 + 16 * 2048;
+  const int lane = threadIdx.x;
+  if (lane == 0) {
+    dev::mbar_init(bar, 1);
+    dev::fence_barrier_init();
+    dev::fence_proxy_async();
+    dev::mbar_expect_tx(bar, (uint32_t)nops * 2048u);
+  }
+  __syncwarp();
+  const long long t0 = clock64();
+  if (mode == 0) {
+    if (lane == 0)
+      for (int n = 0; n < nops; ++n)
+        dev::tma_load_4d(smem0 + (n & 15) * 2048, &map, 0, 0, 4 * (n & 1), (int)((unsigned)(n * 7 + 1) % nbricks), bar);
+  } else if (mode == 1) {
+    if (lane == 0)
+      for (int n = 0; n < nops; n += 8) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          dev::tma_load_4d(smem0 + ((n + u) & 15) * 2048, &map, 0, 0, 4 * (u & 1), (int)((unsigned)((n + u) * 7 + 1) % nbricks), bar);
+      }
+  } else {
+    for (int n = 0; n < nops; n += 12) {
+      if (lane < 12 && n + lane < nops)
+        dev::tma_load_4d(smem0 + ((n + lane) & 15) * 2048, &map, 0, 0, 4 * (lane & 1), (int)((unsigned)((n + lane) * 7 + 1) % nbricks), bar);
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  const long long t1 = clock64();
+  dev::mbar_wait(bar, 0);
+  const long long t2 = clock64();
+  if (lane == 0) {
+    cycles[0] = t1 - t0;
+    cycles[1] = t2 - t0;
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -190,6 +235,31 @@ int bricks_probe_tma_image(bricks_ctx *ctx, const double *field_dev, unsigned nb
   BRK_CUDA(cudaStreamSynchronize(s));
   ++bricks::g_launches;
   BRK_CUDA(cudaFree(out));
+  return 0;
+}
+
+int bricks_probe_tma_issue(bricks_ctx *ctx, const double *field_dev, unsigned nbricks, size_t step, int mode,
+                           int nops, double *issue_cycles_per_op, double *total_cycles_per_op) {
+  BRK_ARG(ctx && field_dev && issue_cycles_per_op && total_cycles_per_op && mode >= 0 && mode <= 2);
+  BRK_ARG(nops > 0 && nops % 24 == 0 && nops <= 480 && nbricks > 8);
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->streams[0];
+  CUtensorMap map;
+  int rc = bricks::encode_map(&map, field_dev, nbricks, step, 8, 8, 4, true);
+  if (rc) return rc;
+  long long *cyc;
+  BRK_CUDA(cudaMalloc(&cyc, 16));
+  const int smem = 16 * 2048 + 64;
+  BRK_CUDA(cudaFuncSetAttribute(tma_issue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  for (int rep = 0; rep < 2; ++rep) tma_issue_kernel<<<1, 32, smem, s>>>(map, mode, nops, nbricks, cyc);
+  BRK_CUDA(cudaGetLastError());
+  long long h[2];
+  BRK_CUDA(cudaMemcpyAsync(h, cyc, 16, cudaMemcpyDeviceToHost, s));
+  BRK_CUDA(cudaStreamSynchronize(s));
+  bricks::g_launches += 2;
+  *issue_cycles_per_op = (double)h[0] / nops;
+  *total_cycles_per_op = (double)h[1] / nops;
+  BRK_CUDA(cudaFree(cyc));
   return 0;
 }
 

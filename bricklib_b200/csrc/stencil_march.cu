@@ -84,9 +84,18 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : 255) 
     const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
     if (lane == 0) dev::mbar_expect_tx(bar, roll ? R * ROLL_PLANE_BYTES : P * MAIN_PLANE_BYTES);
     const int np = roll ? L::NPIECE_ROLL : L::NPIECE_MAIN;
-    if (lane < np)
-      dev::tma_load_4d(dst, roll ? &fd.maps.roll[pk.map] : &fd.maps.main[pk.map], pk.ci, pk.cj, ck,
-                       (int)nb, bar);
+    /* pieces 0/1 (centres), 4/5 and 6/7 (j-faces) sit back to back in the stage: when their two
+     * bricks are consecutive in storage -- the rule inside a BrickDecomp region -- the even lane
+     * fills both with one two-brick copy and the odd lane stays idle.  The per-SM TMA engine
+     * accepts a copy every ~46 cycles, so a stage costs by its NUMBER of copies. */
+    const unsigned nb_up = __shfl_down_sync(0xffffffffu, nb, 1), nb_dn = __shfl_up_sync(0xffffffffu, nb, 1);
+    const bool pairable = !roll && (lane < 2 || (lane >= 4 && lane < 8));
+    const bool lead = pairable && !(lane & 1) && nb_up == nb + 1;
+    const bool follow = pairable && (lane & 1) && nb == nb_dn + 1;
+    if (lane < np && !follow) {
+      const CUtensorMap *map = roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[lane < 2 ? 0 : 1] : &fd.maps.main[pk.map]);
+      dev::tma_load_4d(dst, map, pk.ci, pk.cj, ck, (int)nb, bar);
+    }
   };
 
   double carry[2 * R][4];
@@ -220,6 +229,9 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
       if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false);
       if (rc) return rc;
     }
+    int rc = bricks::encode_map(&fd.maps.pair[0], in[f], plan->nbricks, in_step, 8, 8, P, true, 2);
+    if (!rc) rc = bricks::encode_map(&fd.maps.pair[1], in[f], plan->nbricks, in_step, 8, R, P, false, 2);
+    if (rc) return rc;
   }
   FieldDev *d = nullptr;
   BRK_CUDA(cudaMalloc(&d, sizeof(FieldDev) * nfields));

@@ -24,6 +24,11 @@ int bricks_probe_mio(bricks_ctx *ctx, int mode, double *lds_per_clk, double *shf
  * copy the raw 4096-byte shared-memory image to raw512 (host, 512 doubles) */
 int bricks_probe_tma_image(bricks_ctx *ctx, const double *field_dev, unsigned nbricks, size_t step,
                            unsigned b, double *raw512);
+/* cycles one warp spends per TMA copy it issues (2 KiB boxes, `nops` copies, multiple of 24):
+ * mode 0 one lane in a loop, 1 one lane with 8 copies per iteration unrolled, 2 twelve lanes each
+ * issuing their own copy; total = until the last byte has landed */
+int bricks_probe_tma_issue(bricks_ctx *ctx, const double *field_dev, unsigned nbricks, size_t step, int mode,
+                           int nops, double *issue_cycles_per_op, double *total_cycles_per_op);
 #ifdef __cplusplus
 }
 #endif
