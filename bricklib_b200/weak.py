@@ -70,6 +70,8 @@ class WeakSubdomain(object):
         self.plan_oskin = capi.Plan(ctx, self.dec.grid, self.dec.adj,
                                     shell_between(owned[0], owned[1], inner[0], inner[1]))
         self._exchange_in_flight = None  # storage whose exchange was started by the previous step
+        self._pairs = None               # device storage pairs of the host-fed pipeline (host_steps)
+        self.host_step_bytes = int(self.dec.sep_pos[1]) * 512 * 8
         ro, so, nbts, rp, sp = self.dec.exchange_plan(512)
         self.exchange = capi.Exchange(ctx, rank, ro, so, nbts, rp, sp)
         self.exchange_bytes = int(nbts.sum())
@@ -155,7 +157,7 @@ class WeakSubdomain(object):
         # them last, so only bricks [0, sep_pos[1]) cross the bus
         nbytes = int(self.dec.sep_pos[1]) * 512 * 8
         self.host_step_bytes = nbytes
-        if not hasattr(self, "_pairs"):
+        if self._pairs is None:
             a1, b1 = ctx.malloc(self.nbytes), ctx.malloc(self.nbytes)
             ctx.memset(b1, 0, self.nbytes)
             ctx.memset(a1, 0, self.nbytes)
@@ -178,7 +180,7 @@ class WeakSubdomain(object):
         for p in (self.plan_full, self.plan_inner, self.plan_shell, self.plan_owned, self.plan_oskin):
             p.close()
         self.exchange.close()
-        for a1, b1 in getattr(self, "_pairs", [])[1:]:
+        for a1, b1 in (self._pairs or [])[1:]:
             self.ctx.free(a1)
             self.ctx.free(b1)
         self.ctx.free(self.d_a)
