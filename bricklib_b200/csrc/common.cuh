@@ -81,7 +81,9 @@ struct alignas(64) FieldDev {
   MapSet maps;
   double *out;
   unsigned long long out_step;
-  unsigned long long pad[6];
+  const double *in; /* same field the maps describe: per-lane cp.async of halo pieces */
+  unsigned long long in_step;
+  unsigned long long pad[4];
 };
 static_assert(sizeof(FieldDev) % 64 == 0, "tensor maps in a FieldDev array must stay 64-byte aligned");
 

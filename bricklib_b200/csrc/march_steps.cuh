@@ -126,6 +126,47 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
     for (int m = 0; m < 4; ++m) carry[a][m] = acc[NZ + a][m];
 }
 
+/* One input plane of the cube: e[b][0..7] = v_b over the lane's quad and two columns either side.
+ * Adds the plane's contributions to the five output planes it feeds (acc[z..z+4]). */
+template <int NZ, int MODE>
+__device__ __forceinline__ void cube_scatter(const double (&e)[3][8], const double *__restrict__ c,
+                                             double (&acc)[NZ + 4][4], int z) {
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+      double t[3][3]; /* t[a][b]: i-offset a, j-offset b */
+#pragma unroll
+      for (int b = 0; b < 3; ++b) {
+        t[0][b] = e[b][2 + m];
+        t[1][b] = e[b][3 + m] + e[b][1 + m];
+        t[2][b] = e[b][4 + m] + e[b][m];
+      }
+      const double q00 = t[0][0], q11 = t[1][1], q22 = t[2][2];
+      const double q01 = t[0][1] + t[1][0], q02 = t[0][2] + t[2][0], q12 = t[1][2] + t[2][1];
+      /* coefficient classes of stencils/mpi125pt.py:12-33: c[0]=(0,0,0) c[1]=(0,0,1) c[2]=(0,0,2)
+       * c[3]=(0,1,1) c[4]=(0,1,2) c[5]=(0,2,2) c[6]=(1,1,1) c[7]=(1,1,2) c[8]=(1,2,2) c[9]=(2,2,2) */
+      double g[3];
+      if (MODE == 1) { /* the in-plane part goes straight into its accumulator: six FMAs */
+        double a0 = acc[z + 2][m];
+        a0 = fma(c[0], q00, a0);
+        a0 = fma(c[1], q01, a0);
+        a0 = fma(c[2], q02, a0);
+        a0 = fma(c[3], q11, a0);
+        a0 = fma(c[4], q12, a0);
+        acc[z + 2][m] = fma(c[5], q22, a0);
+      }
+      g[1] = c[1] * q00 + c[3] * q01 + c[4] * q02 + c[6] * q11 + c[7] * q12 + c[8] * q22;
+      g[2] = c[2] * q00 + c[4] * q01 + c[5] * q02 + c[7] * q11 + c[8] * q12 + c[9] * q22;
+      if (MODE != 0) {
+        acc[z + 1][m] += g[1];
+        acc[z][m] += g[2];
+      }
+      if (MODE != 2) {
+        acc[z + 3][m] += g[1];
+        acc[z + 4][m] = g[2];
+      }
+    }
+}
+
 /* ------------------------------------------------------------------ 125-point cube
  * Factorisation: per input plane, with v_b = x(j+b)+x(j-b) (v_0 = x),
  * t_ab = v_b(i+a)+v_b(i-a), Q_ab = t_ab + t_ba (a<b), the plane's contribution to output plane
@@ -180,40 +221,7 @@ __device__ __forceinline__ void cube_step(const char *st, const LaneK<2, true, P
 #pragma unroll
     for (int b = 0; b < 3; ++b) gather_i<R, HW>(v[b], hv[b], lk.halo, lk.bb, lk.srcL, lk.srcR, e[b]);
 
-#pragma unroll
-    for (int m = 0; m < 4; ++m) {
-      double t[3][3]; /* t[a][b]: i-offset a, j-offset b */
-#pragma unroll
-      for (int b = 0; b < 3; ++b) {
-        t[0][b] = e[b][2 + m];
-        t[1][b] = e[b][3 + m] + e[b][1 + m];
-        t[2][b] = e[b][4 + m] + e[b][m];
-      }
-      const double q00 = t[0][0], q11 = t[1][1], q22 = t[2][2];
-      const double q01 = t[0][1] + t[1][0], q02 = t[0][2] + t[2][0], q12 = t[1][2] + t[2][1];
-      /* coefficient classes of stencils/mpi125pt.py:12-33: c[0]=(0,0,0) c[1]=(0,0,1) c[2]=(0,0,2)
-       * c[3]=(0,1,1) c[4]=(0,1,2) c[5]=(0,2,2) c[6]=(1,1,1) c[7]=(1,1,2) c[8]=(1,2,2) c[9]=(2,2,2) */
-      double g[3];
-      if (MODE == 1) { /* the in-plane part goes straight into its accumulator: six FMAs */
-        double a0 = acc[z + 2][m];
-        a0 = fma(c[0], q00, a0);
-        a0 = fma(c[1], q01, a0);
-        a0 = fma(c[2], q02, a0);
-        a0 = fma(c[3], q11, a0);
-        a0 = fma(c[4], q12, a0);
-        acc[z + 2][m] = fma(c[5], q22, a0);
-      }
-      g[1] = c[1] * q00 + c[3] * q01 + c[4] * q02 + c[6] * q11 + c[7] * q12 + c[8] * q22;
-      g[2] = c[2] * q00 + c[4] * q01 + c[5] * q02 + c[7] * q11 + c[8] * q12 + c[9] * q22;
-      if (MODE != 0) {
-        acc[z + 1][m] += g[1];
-        acc[z][m] += g[2];
-      }
-      if (MODE != 2) {
-        acc[z + 3][m] += g[1];
-        acc[z + 4][m] = g[2];
-      }
-    }
+    cube_scatter<NZ, MODE>(e, c, acc, z);
     store_done<R, MODE>(o, zbase, z, acc[z]);
   }
 #pragma unroll
