@@ -63,7 +63,7 @@ struct bricks_ctx {
 struct MarchItem {
   unsigned short gi, gj, gk0, nk;
   unsigned valid1; /* second brick of the pair is inside the box */
-  unsigned pad;
+  unsigned validj; /* 2x2-brick footprints (cube tile kernel): the +j brick row is inside the box */
 };
 
 /* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane
@@ -133,8 +133,9 @@ namespace bricks {
 /* longest column (brick layers) one warp marches for this stencil; measured on B200
  * (profiles/r01_column_length.txt) */
 unsigned column_length(int stencil_id);
-/* the plan's item list for that column length (built and uploaded on first use) */
-int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems);
+/* the plan's item list for that column length (built and uploaded on first use); fj = bricks per
+ * footprint along j (1: brick pairs, 2: 2x2 bricks) */
+int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems, int fj = 1);
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
                unsigned bj, unsigned bk, bool swizzle64, unsigned bb = 1);
 }

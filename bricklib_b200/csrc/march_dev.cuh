@@ -65,9 +65,30 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void st_quad(double *p, const double (&v)[4]) {
-  /* 32 contiguous bytes per lane = one full L2 sector, streaming (written once per sweep) */
-  __stcs(reinterpret_cast<double2 *>(p), make_double2(v[0], v[1]));
-  __stcs(reinterpret_cast<double2 *>(p) + 1, make_double2(v[2], v[3]));
+  /* 32 contiguous bytes per lane = one full L2 sector, streaming (written once per sweep), as ONE
+   * 256-bit store (SASS STG.E.EF.256): half the store instructions and L1TEX tag requests of two
+   * 128-bit stores, and the sector reaches L2 whole instead of as two 16-byte partial writes
+   * (measured: 125-point sweep 0.606 -> 0.581 ms, profiles/r02_cube_experiments.md) */
+  asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3])
+               : "memory");
+}
+
+/* predicated 256-bit streaming store without a branch and without a compiler memory barrier: the
+ * planes of a stage stay one basic block, so ptxas can start the next plane's shared-memory loads
+ * under the current plane's arithmetic (nothing in these kernels reads `out`) */
+__device__ __forceinline__ void st_quad_if(double *p, const double (&v)[4], bool on) {
+  asm volatile(
+      "{\n"
+      ".reg .pred q;\n"
+      "setp.ne.b32 q, %5, 0;\n"
+      "@q st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};\n"
+      "}\n" ::"l"(p),
+      "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]), "r"((int)on));
+}
+/* cp.async without the compiler memory barrier: ordering against the loads of a stage comes from
+ * cp_async_wait / __syncwarp, which keep theirs */
+__device__ __forceinline__ void cp_async16_nb(uint32_t dst, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
 }
 
 /* Byte layout of one pipeline stage.  P = planes per main stage (4 or 8). */

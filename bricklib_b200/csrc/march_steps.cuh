@@ -19,15 +19,18 @@ struct OutPtrs {
   bool curv, prevv;
 };
 
+/* store a finished output plane, branch-free (see st_quad_if) */
+template <int R, int MODE>
+__device__ __forceinline__ void store_done_nb(const OutPtrs &o, int zbase, int z, const double (&v)[4]) {
+  if (MODE == 0) return;
+  const int op = zbase + z - R;
+  const bool here = op >= 0;
+  st_quad_if((here ? o.cur : o.prev) + (here ? op : op + 8) * 64, v, here ? o.curv : o.prevv);
+}
+
 template <int R, int MODE>
 __device__ __forceinline__ void store_done(const OutPtrs &o, int zbase, int z, const double (&v)[4]) {
-  if (MODE == 0) return;
-  const int op = zbase + z - R; /* output plane relative to the current layer */
-  if (op >= 0) {
-    if (o.curv) st_quad(o.cur + op * 64, v);
-  } else {
-    if (o.prevv) st_quad(o.prev + (op + 8) * 64, v);
-  }
+  store_done_nb<R, MODE>(o, zbase, z, v);
 }
 
 /* i-neighbours of the lane's quad: R values on each side, by shuffle from the adjacent lane or,

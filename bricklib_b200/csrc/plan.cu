@@ -72,7 +72,7 @@ unsigned column_length(int stencil_id) {
 }
 
 static void build_items(const unsigned gdims[3], int nboxes, const unsigned *boxes, unsigned kMaxColumn,
-                        std::vector<MarchItem> &items, std::vector<unsigned> *cells) {
+                        std::vector<MarchItem> &items, std::vector<unsigned> *cells, unsigned fj = 1) {
   for (int b = 0; b < nboxes; ++b) {
     const unsigned *lo = boxes + 6 * b, *hi = lo + 3;
     if (hi[0] <= lo[0] || hi[1] <= lo[1] || hi[2] <= lo[2]) continue;
@@ -83,7 +83,7 @@ static void build_items(const unsigned gdims[3], int nboxes, const unsigned *box
       unsigned k0 = lo[2] + s * seglen;
       unsigned k1 = std::min(hi[2], k0 + seglen);
       if (k0 >= k1) continue;
-      for (unsigned j = lo[1]; j < hi[1]; ++j)
+      for (unsigned j = lo[1]; j < hi[1]; j += fj)
         for (unsigned i = lo[0]; i < hi[0]; i += 2) {
           MarchItem it;
           it.gi = (unsigned short)i;
@@ -91,7 +91,7 @@ static void build_items(const unsigned gdims[3], int nboxes, const unsigned *box
           it.gk0 = (unsigned short)k0;
           it.nk = (unsigned short)(k1 - k0);
           it.valid1 = (i + 1 < hi[0]) ? 1u : 0u;
-          it.pad = 0;
+          it.validj = (fj > 1 && j + 1 < hi[1]) ? 1u : 0u;
           items.push_back(it);
         }
     }
@@ -103,18 +103,19 @@ static void build_items(const unsigned gdims[3], int nboxes, const unsigned *box
   }
 }
 
-int plan_items(bricks_plan *p, unsigned maxcol, const MarchItem **items_dev, int *nitems) {
-  auto it = p->items.find(maxcol);
+int plan_items(bricks_plan *p, unsigned maxcol, const MarchItem **items_dev, int *nitems, int fj) {
+  const unsigned key = maxcol | (fj > 1 ? 0x100u : 0u);
+  auto it = p->items.find(key);
   if (it == p->items.end()) {
     std::vector<MarchItem> items;
-    build_items(p->gdims, (int)(p->boxes.size() / 6), p->boxes.data(), maxcol, items, nullptr);
+    build_items(p->gdims, (int)(p->boxes.size() / 6), p->boxes.data(), maxcol, items, nullptr, fj > 1 ? 2 : 1);
     bricks_plan::ItemList l;
     l.n = (int)items.size();
     cudaStream_t s = p->ctx->streams[BRICKS_STREAM_COMPUTE];
     BRK_CUDA(cudaMalloc(&l.dev, items.size() * sizeof(MarchItem)));
     BRK_CUDA(cudaMemcpyAsync(l.dev, items.data(), items.size() * sizeof(MarchItem), cudaMemcpyHostToDevice, s));
     BRK_CUDA(cudaStreamSynchronize(s)); /* `items` dies here */
-    it = p->items.emplace(maxcol, l).first;
+    it = p->items.emplace(key, l).first;
   }
   *items_dev = it->second.dev;
   *nitems = it->second.n;
