@@ -58,6 +58,7 @@ _SIGS = {
     "bricks_launch_count": (C.c_int, [C.POINTER(C.c_ulonglong)]),
     "bricks_links_upload": (C.c_int, [_vp, _vp, C.c_int, _vpp]),
     "bricks_copy_regions": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "bricks_copy_array": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_int]),
     "bricks_comm_unique_id": (C.c_int, [_vp]),
     "bricks_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
     "bricks_comm_destroy": (C.c_int, [_vp]),
@@ -244,6 +245,12 @@ class Plan(object):
             cp = _np_ptr(coeff)
         check(fn(self._h, stencil, n, ia, oa, in_step, out_step, cp, stream))
 
+    def device_tables(self):
+        """(adj_dev, grid_dev) device pointers held by the plan."""
+        a, g = C.c_void_p(), C.c_void_p()
+        check(lib().bricks_plan_device_tables(self._h, C.byref(a), C.byref(g)))
+        return a.value, g.value
+
     def stencil(self, stencil, ins, outs, in_step=512, out_step=512, coeff=None, stream=STREAM_COMPUTE):
         self._run(lib().bricks_stencil, stencil, ins, outs, in_step, out_step, coeff, stream)
 
@@ -417,6 +424,15 @@ def copy_brick(to_brick, dimlist, padding, ghost, arr, grid, bdat, adj, step=512
     assert arr.flags["C_CONTIGUOUS"] and bdat.flags["C_CONTIGUOUS"]
     check(lib().bricks_copy_brick3(1 if to_brick else 0, _np_ptr(d), _np_ptr(p), _np_ptr(g), _np_ptr(arr),
                                    _np_ptr(grid), _np_ptr(bdat), step, _np_ptr(adj), adj.shape[0]))
+
+
+def copy_array_dev(ctx, to_brick, dimlist, padding, ghost, arr_dev, grid_dev, bricks_dev, step=512,
+                   stream=STREAM_COMPUTE):
+    """copyToBrick<3> / copyFromBrick<3> on the device (bricks_copy_array): array and bricks are device
+    pointers, grid_dev the device brick-index grid (Plan.device_tables()[1])."""
+    d, p, g = (np.ascontiguousarray(x, np.int64) for x in (dimlist, padding, ghost))
+    check(lib().bricks_copy_array(ctx._h, 1 if to_brick else 0, _np_ptr(d), _np_ptr(p), _np_ptr(g), arr_dev,
+                                  grid_dev, bricks_dev, step, stream))
 
 
 def compare_brick(dimlist, padding, ghost, arr, grid, bdat, adj, step=512):

@@ -96,6 +96,26 @@ inline BrickStorage movBrickStorage(BrickStorage &bStorage, gpuMemcpyKind kind) 
   return ret;
 }
 
+/// copyToBrick / copyFromBrick (bricksetup.h:172-221) between a DEVICE array and a Brick view on a
+/// DEVICE storage; grid_dev is the device brick-index grid (BrickStencilPlan::gridDevice()).
+/// Same dimlist / padding / ghost meaning as the host versions; asynchronous on `stream`.
+template <unsigned dims, typename T>
+inline void copyToBrickDevice(const std::vector<long> &dimlist, const std::vector<long> &padding,
+                              const std::vector<long> &ghost, bElem *arr_dev, const unsigned *grid_dev, T &brick,
+                              int stream = BRICKS_STREAM_COMPUTE) {
+  static_assert(dims == 3, "device copies implement the 3-D case");
+  gpuCheck(bricks_copy_array(bricksContext(), 1, dimlist.data(), padding.data(), ghost.data(), arr_dev, grid_dev,
+                             brick.dat, brick.step, stream));
+}
+template <unsigned dims, typename T>
+inline void copyFromBrickDevice(const std::vector<long> &dimlist, const std::vector<long> &padding,
+                                const std::vector<long> &ghost, bElem *arr_dev, const unsigned *grid_dev, T &brick,
+                                int stream = BRICKS_STREAM_COMPUTE) {
+  static_assert(dims == 3, "device copies implement the 3-D case");
+  gpuCheck(bricks_copy_array(bricksContext(), 0, dimlist.data(), padding.data(), ghost.data(), arr_dev, grid_dev,
+                             brick.dat, brick.step, stream));
+}
+
 /// A launch plan over boxes of a brick grid: the host side of
 /// `brick_kernel<<<dim3(strideb...), 32>>>` (weak/main.cu:277).  Owns the device copies of the
 /// grid and the adjacency list.
@@ -130,6 +150,17 @@ class BrickStencilPlan {
     gpuCheck(bricks_stencil(plan_, stencil_id, (int)in.size(), in.data(), out.data(), in_step, out_step, coeff, stream));
   }
   bricks_plan *handle() { return plan_; }
+  /// device copies of the grid and the adjacency list held by the plan
+  const unsigned *gridDevice() const {
+    const unsigned *a = nullptr, *g = nullptr;
+    gpuCheck(bricks_plan_device_tables(plan_, &a, &g));
+    return g;
+  }
+  const unsigned *adjDevice() const {
+    const unsigned *a = nullptr, *g = nullptr;
+    gpuCheck(bricks_plan_device_tables(plan_, &a, &g));
+    return a;
+  }
 
  private:
   bricks_plan *plan_ = nullptr;

@@ -119,6 +119,17 @@ int bricks_links_upload(bricks_ctx *ctx, const bricks_region_link *links_host, i
                         bricks_region_link **links_dev);
 int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, int n, int stream);
 
+/* ---- array <-> brick copies on the device: replaces copyToBrick<3> / copyFromBrick<3>
+ * (include/bricksetup.h:172-221; cell range and strides of iter_grid, :139-160) for arrays that
+ * already live in device memory.  dimlist / padding / ghost are in elements, i first, with the
+ * reference's meaning: the array has dimlist + 2*(padding + ghost) elements per axis, the brick grid
+ * (dimlist + 2*ghost)/8 cells per axis, and only the cells of the interior `dimlist` region are
+ * copied.  grid_dev is the device brick-index grid (e.g. from bricks_plan_device_tables); `step` in
+ * elements.  to_brick != 0: array -> bricks, else bricks -> array.  Asynchronous on `stream`. */
+int bricks_copy_array(bricks_ctx *ctx, int to_brick, const long dimlist[3], const long padding[3],
+                      const long ghost[3], double *arr_dev, const unsigned *grid_dev,
+                      double *bricks_dev, size_t step, int stream);
+
 /* ---- halo exchange: replaces BrickDecomp::exchange(BrickStorage&) (brick-mpi.h:466-495),
  * ExchangeView::exchange (brick-mpi.h:96-123) and the D2H / MPI / H2D staging of
  * weak/main.cu:251-275.  Region i: receive nbytes[i] at recv_off[i] of the storage from
