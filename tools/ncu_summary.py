@@ -1,3 +1,7 @@
+"""Summarise one ncu --set full capture: python tools/ncu_summary.py raw.csv source.csv
+(raw.csv = ncu -i X.ncu-rep --page raw --csv, source.csv = --page source --csv).  Prints the unit
+utilisations, the stall mix from the warp samples, per-opcode sample shares, the L1TEX cost of the
+memory instructions and the hottest instructions."""
 import csv,sys
 raw,srcf=sys.argv[1],sys.argv[2]
 rows=list(csv.reader(open(raw)))
@@ -6,7 +10,7 @@ keys=["gpu__time_duration.sum","dram__bytes_read.sum","dram__bytes_write.sum","l
 for i,h in enumerate(hdr):
     if h in keys: print(h, units[i], vals[i])
 rows=list(csv.reader(open(srcf)))
-hdr=rows[1]; data=rows[2:]
+hdr=rows[1]; data=[r for r in rows[2:] if len(r)==len(hdr) and r[0]!="Address"]
 ix={h:i for i,h in enumerate(hdr)}
 tot=sum(int(r[ix["# Samples"]] or 0) for r in data)
 from collections import defaultdict
