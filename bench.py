@@ -237,7 +237,7 @@ def run_gpu(args, which):
 
     procdims = capi.cart_dims(world)
     st_iter = capi.ST_ITER[which]
-    sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims)
+    sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims, shift=args.shift_exchange)
     nb = sub.dec.nbricks
     field = sub.host_field()
     sub.upload(field)
@@ -300,7 +300,8 @@ def run_gpu(args, which):
                 "config": make_config(which, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": roofline,
                 "overlap": not args.no_overlap, "early_exchange": early and not args.no_overlap,
-                "exchange_bytes_per_step_per_gpu": sub.exchange_bytes}
+                "exchange_bytes_per_step_per_gpu": sub.exchange_bytes,
+                "exchange": "shift (3 stages, 6 messages)" if args.shift_exchange else "direct (one message per region)"}
         if not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_reference_rate(which, budget_s=args.cpu_seconds)
@@ -493,6 +494,8 @@ def main():
     ap.add_argument("--workload", default="weak125", choices=sorted(WORKLOADS))
     ap.add_argument("--no-overlap", action="store_true", help="serial exchange then sweeps (reference schedule)")
     ap.add_argument("--no-early", action="store_true", help="start each exchange at the step boundary only")
+    ap.add_argument("--shift-exchange", action="store_true",
+                    help="weak workloads: the SHIFT exchange (3 stages, 6 messages) instead of one message per region")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=10)

@@ -278,6 +278,24 @@ class Exchange(object):
             self._h = C.c_void_p()
 
 
+class ShiftExchange(object):
+    """MultiStageExchangeView (brick-mpi.h:126-176): three Exchange plans, one per axis, run in order
+    on one stream.  Build from Decomp.shift_plan()."""
+
+    def __init__(self, ctx, rank, stages):
+        self.stages = [Exchange(ctx, rank, *st) for st in stages]
+        self.npieces = [len(st[0]) for st in stages]
+
+    def run(self, storage_dev, stream=STREAM_COMM):
+        for ex in self.stages:
+            ex.run(storage_dev, stream)
+
+    def close(self):
+        for ex in self.stages:
+            ex.close()
+        self.stages = []
+
+
 def copy_regions(ctx, links, stream=STREAM_COMPUTE):
     """links: list of (src_dev, dst_dev, nbytes).  Uploads the table then runs the copy kernel."""
     arr = (RegionLink * len(links))(*[RegionLink(s, d, n) for s, d, n in links])
@@ -338,6 +356,7 @@ _SIGS.update({
     "bricks_decomp_tables": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "bricks_decomp_rank_map": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "bricks_decomp_exchange_plan": (C.c_int, [_vp, C.c_size_t, _vp, _vp, _vp, _vp, _vp]),
+    "bricks_decomp_shift_plan": (C.c_int, [_vp, C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_int), _vp, _vp, _vp, _vp, _vp]),
     "bricks_init_grid3": (C.c_int, [_vp, _vp, _vp]),
     "bricks_copy_brick3": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp, C.c_uint]),
     "bricks_compare_brick3": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp, C.c_uint, _vp, _vp]),
@@ -394,6 +413,21 @@ class Decomp(object):
         check(lib().bricks_decomp_exchange_plan(self._h, step, _np_ptr(ro), _np_ptr(so), _np_ptr(nb),
                                                 _np_ptr(rp), _np_ptr(sp)))
         return ro, so, nb, rp, sp
+
+    def shift_plan(self, step=512):
+        """The SHIFT exchange (multiStageExchangeView, brick-mpi.h:587-681) for the rank map set by the
+        last rank_map() call: three (recv_off, send_off, nbytes, recv_peer, send_peer) tuples, one
+        per axis, each the arguments of an Exchange; stages must run in order."""
+        out = []
+        for stage in range(3):
+            n = C.c_int()
+            check(lib().bricks_decomp_shift_plan(self._h, step, stage, 0, C.byref(n), None, None, None, None, None))
+            ro, so, nb = (np.zeros(n.value, np.uint64) for _ in range(3))
+            rp, sp = np.zeros(n.value, np.int32), np.zeros(n.value, np.int32)
+            check(lib().bricks_decomp_shift_plan(self._h, step, stage, n.value, C.byref(n), _np_ptr(ro), _np_ptr(so),
+                                                 _np_ptr(nb), _np_ptr(rp), _np_ptr(sp)))
+            out.append((ro, so, nb, rp, sp))
+        return out
 
     def close(self):
         if self._h:

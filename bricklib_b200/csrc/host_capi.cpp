@@ -171,6 +171,32 @@ int bricks_decomp_exchange_plan(bricks_decomp *d, size_t step, size_t *recv_off,
   return 0;
 }
 
+int bricks_decomp_shift_plan(bricks_decomp *d, size_t step, int stage, int cap, int *npieces, size_t *recv_off,
+                             size_t *send_off, size_t *nbytes, int *recv_peer, int *send_peer) {
+  if (!d || !npieces || stage < 0 || stage > 2) return -1;
+  Decomp3 &D = *d->dec;
+  if (D.rank_map.empty()) {
+    bricks::set_error("bricks_decomp_shift_plan: call bricks_decomp_rank_map first");
+    return -1;
+  }
+  return guarded([&] {
+    const auto stages = D.shiftPieces();
+    const auto &st = stages[(size_t)stage];
+    *npieces = (int)st.size();
+    if (cap <= 0) return;
+    if (!recv_off || !send_off || !nbytes || !recv_peer || !send_peer || cap < (int)st.size())
+      throw std::runtime_error("bricks_decomp_shift_plan: arrays too small");
+    const size_t sb = step * sizeof(double);
+    for (size_t i = 0; i < st.size(); ++i) {
+      recv_off[i] = (size_t)st[i].recv_pos * sb;
+      send_off[i] = (size_t)st[i].send_pos * sb;
+      nbytes[i] = (size_t)st[i].len * sb;
+      recv_peer[i] = D.rank_map[st[i].from.set];
+      send_peer[i] = D.rank_map[(!st[i].from).set];
+    }
+  });
+}
+
 int bricks_init_grid3(const long dimlist[3], unsigned *grid, unsigned *adj) {
   if (!dimlist || !grid || !adj) return -1;
   return guarded([&] {

@@ -73,6 +73,14 @@ __device__ __forceinline__ void st_quad(double *p, const double (&v)[4]) {
                : "memory");
 }
 
+/* ld.global.nc that the compiler may not sink to its use: adjacency rows are fetched a whole
+ * stage before the copies that need them */
+__device__ __forceinline__ unsigned ld_nc_pinned(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
 /* predicated 256-bit streaming store without a branch and without a compiler memory barrier: the
  * planes of a stage stay one basic block, so ptxas can start the next plane's shared-memory loads
  * under the current plane's arithmetic (nothing in these kernels reads `out`) */

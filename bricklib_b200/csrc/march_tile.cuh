@@ -35,14 +35,6 @@ struct TileLayout {
   static constexpr int BYTES = P * PLANE;
 };
 
-/* ld.global.nc that the compiler may not sink to its use: adjacency rows are fetched a whole
- * stage before the copies that need them */
-__device__ __forceinline__ unsigned ld_nc_pinned(const unsigned *p) {
-  unsigned v;
-  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p));
-  return v;
-}
-
 /* Producer side.  A stage is filled by 16-byte cp.async whose lanes walk memory in its own order, so
  * that one instruction touches as few 128-byte lines as possible (the SM's L1TEX queue serves one
  * line of a scattered LDGSTS every ~2 cycles and is shared with every LDS): per plane

@@ -90,7 +90,11 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
     const unsigned rowb = pk.useb1 ? b1 : b0;
     unsigned nb = 0;
+#ifdef MARCH_PIN_ADJ /* experiment: a load the compiler may not sink towards its use */
+    if (lane < 12) nb = dev::ld_nc_pinned(prm.adj + (size_t)rowb * 27 + (dk + 1) * 9 + (pk.dj + 1) * 3 + (pk.di + 1));
+#else
     if (lane < 12) nb = prm.adj[(size_t)rowb * 27 + (dk + 1) * 9 + (pk.dj + 1) * 3 + (pk.di + 1)];
+#endif
     return nb;
   };
   auto issue = [&](int s, unsigned nb) {
@@ -120,8 +124,18 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     }
     dev::cp_async_commit();
 #else
+#ifdef MARCH_CORNER_LDGSTS /* experiment: the four 2x2 corner pieces of the cube by one cp.async per lane */
+    constexpr int XB = CUBE ? 4 * L::X_PL : 0;
+    if (lane == 0) dev::mbar_expect_tx(bar, roll ? R * (ROLL_PLANE_BYTES - XB) : P * (MAIN_PLANE_BYTES - XB));
+    const int np = CUBE ? 8 : (roll ? L::NPIECE_ROLL : L::NPIECE_MAIN);
+    if constexpr (CUBE)
+      dev::halo_group_ldgsts<R, CUBE, P, 2>(smem0 + (s & 1) * L::BYTES, reinterpret_cast<const char *>(fd.in),
+                                            (size_t)fd.in_step * 8, nb, ck, roll ? R : P, lane);
+    dev::cp_async_commit();
+#else
     if (lane == 0) dev::mbar_expect_tx(bar, roll ? R * ROLL_PLANE_BYTES : P * MAIN_PLANE_BYTES);
     const int np = roll ? L::NPIECE_ROLL : L::NPIECE_MAIN;
+#endif
     /* pieces 0/1 (centres), 4/5 and 6/7 (j-faces) sit back to back in the stage: when their two
      * bricks are consecutive in storage -- the rule inside a BrickDecomp region -- the even lane
      * fills both with one two-brick copy and the odd lane stays idle.  The per-SM TMA engine
@@ -157,7 +171,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
       dev::fence_proxy_async();
       issue(s + 1, nbn);
       if (s + 2 < nsteps) nbn = load_nb(s + 2);
-#ifdef MARCH_HALO_LDGSTS
+#if defined(MARCH_HALO_LDGSTS) || defined(MARCH_CORNER_LDGSTS)
       dev::cp_async_wait<1>(); /* this lane's halo chunks of stage s have landed ... */
     } else {
       dev::cp_async_wait<0>();

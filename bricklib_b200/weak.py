@@ -41,7 +41,7 @@ class WeakSubdomain(object):
     """One rank's subdomain: BrickDecomp tables, two ping-pong storages on the device, the box
     plans of the sweep schedule and the exchange plan."""
 
-    def __init__(self, ctx, dims, stencil, rank=0, procdims=(1, 1, 1), depth=8, seed=20240601):
+    def __init__(self, ctx, dims, stencil, rank=0, procdims=(1, 1, 1), depth=8, seed=20240601, shift=False):
         self.ctx, self.stencil, self.rank = ctx, stencil, rank
         self.procdims = list(procdims)
         self.nranks = int(np.prod(procdims))
@@ -73,8 +73,12 @@ class WeakSubdomain(object):
         self._pairs = None               # device storage pairs of the host-fed pipeline (host_steps)
         self.host_step_bytes = int(self.dec.sep_pos[1]) * 512 * 8
         ro, so, nbts, rp, sp = self.dec.exchange_plan(512)
-        self.exchange = capi.Exchange(ctx, rank, ro, so, nbts, rp, sp)
         self.exchange_bytes = int(nbts.sum())
+        if shift:
+            # SHIFT exchange (multiStageExchangeView, brick-mpi.h:587-681): 3 stages, 6 messages
+            self.exchange = capi.ShiftExchange(ctx, rank, self.dec.shift_plan(512))
+        else:
+            self.exchange = capi.Exchange(ctx, rank, ro, so, nbts, rp, sp)
         self.seed = seed + 1000 * rank
         self.launches_per_step = None
 

@@ -2,7 +2,7 @@
 // stencil sweeps.  Drop-in for the reference's weak/main.cu (flow :45-338) and weak/args.cpp
 // (flags -d -s -I -b -h), with -S 7|13|25|125 selecting the stencil at run time (the reference
 // picks it with -DMPI_7PT...), -G ngpus replacing `mpirun -np`, -v for the validation twin and
-// -n for the reference's serial schedule (no exchange/compute overlap).
+// -n for the reference's serial schedule (no exchange/compute overlap).  -m uses the SHIFT exchange.
 //
 // Prints the reference's lines (weak/main.cu:304-318): Bri / calc / move / call / wait /
 // "  | MPI size (MB)" / "  | MPI speed (GB/s)" / "perf X GStencil/s".
@@ -37,6 +37,7 @@ const char *help =
     "  -S: stencil 7|13|25|125, default 7\n"
     "  -v: validate against the naive device kernel\n"
     "  -n: no overlap (exchange, then sweeps)\n"
+    "  -m: SHIFT exchange (three stages, six messages) instead of one message per region\n"
     "Example usage:\n"
     "  %s -G 8 -s 512,512,512 -S 125\n";
 
@@ -57,8 +58,8 @@ std::vector<Box> shell_of(const unsigned g[3], const unsigned lo[3], const unsig
 int main(int argc, char **argv) {
   std::vector<unsigned> dom(3, 64);
   int sel = 0, iters = 100, ngpus = 1, which = 7, c;
-  bool bin = false, validate = false, overlap = true;
-  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vn")) != -1) {
+  bool bin = false, validate = false, overlap = true, shift = false;
+  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vnm")) != -1) {
     switch (c) {
       case 'b': bin = true; break;
       case 'd': drv::parse_tuple(optarg, dom, 3); sel = sel ? -2 : 1; break;
@@ -68,6 +69,7 @@ int main(int argc, char **argv) {
       case 'S': which = std::stoi(optarg); break;
       case 'v': validate = true; break;
       case 'n': overlap = false; break;
+      case 'm': shift = true; break;
       default: printf("Unknown options %c\n", c);  // fall through
       case 'h': printf(help, argv[0], iters, argv[0]); sel = sel ? -2 : -1;
     }
@@ -175,9 +177,18 @@ int main(int argc, char **argv) {
       inner.reset(new BrickStencilPlan(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, one(in_lo, in_hi)));
       shell.reset(new BrickStencilPlan(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, shell_of(g, in_lo, in_hi)));
     }
-    ExchangeView ev = bDecomp.exchangeView(bStorage_dev);
+    ExchangeView ev_direct = bDecomp.exchangeView(bStorage_dev);
     size_t tsize = 0;
-    for (size_t n : ev.seclen) tsize += n;
+    for (size_t n : ev_direct.seclen) tsize += n;
+    // -m: the SHIFT exchange (multiStageExchangeView, brick-mpi.h:587-681): 3 stages, 6 messages
+    MultiStageExchangeView ev_shift;
+    if (shift) ev_shift = bDecomp.multiStageExchangeView(bStorage_dev);
+    struct {
+      ExchangeView *d;
+      MultiStageExchangeView *m;
+      void start() { m ? m->start() : d->start(); }
+      void wait() { m ? m->wait() : d->wait(); }
+    } ev = {&ev_direct, shift ? &ev_shift : nullptr};
 
     double calltime_l = 0;
     // one step = exchange + ST_ITER sweeps (weak/main.cu:246-287); everything is asynchronous

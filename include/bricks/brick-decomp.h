@@ -169,6 +169,36 @@ struct ExchangeView {
   void wait() { bricks_detail::require(bricks_stream_wait(comm.ctx, BRICKS_STREAM_COMPUTE, BRICKS_STREAM_COMM), "exchange"); }
 };
 
+/// SHIFT exchange (brick-mpi.h:126-176, 587-681): one stage per axis, two messages per stage.  What
+/// an edge or corner neighbour owns arrives in several hops through the ghost zones of the face
+/// neighbours, so a rank talks to 6 peers instead of 26.  The reference glues the pieces of a
+/// message into one virtual range with mmap; here a message is a run of (send range, receive range)
+/// pairs of equal length that both ends derive from the same tables, issued inside one NCCL group per
+/// stage (self-neighbours become device copies).  Stages are ordered on the communication stream: a
+/// stage forwards ghost bricks the previous one received.
+struct MultiStageExchangeView {
+  BricksComm comm;
+  std::vector<bricks_exchange *> stages;  ///< owned by the BrickDecomp that made the view
+  bElem *storage_dev = nullptr;
+
+  void exchange() {
+    start();
+    wait();
+  }
+  void start() {
+    bricks_detail::require(bricks_stream_wait(comm.ctx, BRICKS_STREAM_COMM, BRICKS_STREAM_COMPUTE), "exchange");
+    for (bricks_exchange *st : stages)
+      bricks_detail::require(bricks_exchange_run(st, storage_dev, BRICKS_STREAM_COMM), "exchange");
+  }
+  void wait() { bricks_detail::require(bricks_stream_wait(comm.ctx, BRICKS_STREAM_COMPUTE, BRICKS_STREAM_COMM), "exchange"); }
+};
+
+/// One (send range, receive range) pair of a SHIFT-exchange stage, in bricks.
+struct ShiftPiece {
+  unsigned recv_pos, send_pos, len;
+  BitSet from;  ///< direction received from; the send goes to the mirrored direction
+};
+
 template <unsigned dim, unsigned... BDims>
 class BrickDecomp {
  public:
@@ -207,6 +237,8 @@ class BrickDecomp {
   BrickDecomp &operator=(const BrickDecomp &) = delete;
   ~BrickDecomp() {
     for (auto &kv : plans) bricks_exchange_destroy(kv.second);
+    for (auto &kv : shift_plans)
+      for (bricks_exchange *ex : kv.second) bricks_exchange_destroy(ex);
     delete[] grid;
     if (bInfo) {
       free(bInfo->adj);
@@ -317,6 +349,9 @@ class BrickDecomp {
     for (unsigned c = 0; c < cells; ++c) fill_adjacency(c, bInfo->adj[grid[c]]);
     for (auto &kv : plans) bricks_exchange_destroy(kv.second);
     plans.clear();
+    for (auto &kv : shift_plans)
+      for (bricks_exchange *ex : kv.second) bricks_exchange_destroy(ex);
+    shift_plans.clear();
   }
 
   /// grid lookup including the ghost band: decomp[k][j][i]
@@ -371,8 +406,113 @@ class BrickDecomp {
     return v;
   }
 
+  /// The SHIFT exchange as piece tables: result[d-1] lists the pieces of stage d (axis d), grouped
+  /// by direction in allneighbors() order.  Per direction n the receive side is the ghost regions n
+  /// owns followed by every ghost region not yet filled whose owner is n plus axes already
+  /// exchanged; the send side is the skin facing the mirrored direction followed, for those further
+  /// regions, by the same skin sections inside this rank's ghost copy of the (owner minus n)
+  /// neighbour (brick-mpi.h:611-664).  Both lists cover the same bytes in the same order; they are
+  /// cut at each other's boundaries so that every piece is one contiguous range on both ends.
+  std::vector<std::vector<ShiftPiece>> shiftPieces() const {
+    typedef std::pair<unsigned, unsigned> Run;  // first brick, count
+    std::vector<std::vector<ShiftPiece>> out;
+    std::vector<BitSet> nbrs;
+    allneighbors(BitSet(), 1, dim, nbrs);
+    BitSet done;
+    for (long d = 1; d <= (long)dim; ++d) {
+      BitSet axis;
+      axis.flip(d);
+      axis.flip(-d);
+      out.emplace_back();
+      for (const BitSet n : nbrs) {
+        if (n.set == 0 || !(n <= axis)) continue;
+        std::vector<Run> recv, send;
+        auto push = [](std::vector<Run> &v, unsigned pos, unsigned len) {
+          if (!len) return;
+          if (!v.empty() && v.back().first + v.back().second == pos)
+            v.back().second += len;  // contiguous with the previous run
+          else
+            v.push_back(Run(pos, len));
+        };
+        const BitSet mirrored = !n;
+        for (const auto &g : ghost)
+          if (g.neighbor.set == n.set) push(recv, g.pos + g.first_pad, g.len - g.first_pad - g.last_pad);
+        for (const auto &k : skin)
+          if (k.neighbor.set == mirrored.set) push(send, k.pos + k.first_pad, k.len - k.first_pad - k.last_pad);
+        const BitSet reach = n | done;
+        for (const auto &g : ghost) {
+          if (g.neighbor.set == n.set || !(g.neighbor <= reach) || g.neighbor <= done) continue;
+          if (g.first_pad || g.last_pad) throw std::runtime_error("shiftPieces: padded regions are not supported");
+          push(recv, g.pos, g.len);
+          const BitSet via = g.neighbor ^ n;
+          for (unsigned sec = g.skin_st; sec < g.skin_ed; ++sec)
+            for (const auto &h : ghost)
+              if (h.neighbor.set == via.set && sec >= h.skin_st && sec < h.skin_ed) {
+                unsigned pos = h.pos;
+                for (unsigned j = h.skin_st; j < sec; ++j) pos += (unsigned)skin_size[j];
+                push(send, pos, (unsigned)skin_size[sec]);
+              }
+        }
+        // cut both run lists at each other's boundaries
+        size_t ir = 0, is = 0;
+        unsigned ur = 0, us = 0;  // bricks of the current runs already paired
+        while (ir < recv.size() && is < send.size()) {
+          const unsigned l = std::min(recv[ir].second - ur, send[is].second - us);
+          ShiftPiece p;
+          p.recv_pos = recv[ir].first + ur;
+          p.send_pos = send[is].first + us;
+          p.len = l;
+          p.from = n;
+          out.back().push_back(p);
+          ur += l;
+          us += l;
+          if (ur == recv[ir].second) ++ir, ur = 0;
+          if (us == send[is].second) ++is, us = 0;
+        }
+        if (ir != recv.size() || is != send.size())
+          throw std::runtime_error("shiftPieces: send and receive sides of a stage differ in size");
+      }
+      done = done | axis;
+    }
+    return out;
+  }
+
+  /// SHIFT exchange bound to a device storage (brick-mpi.h:587: multiStageExchangeView)
+  MultiStageExchangeView multiStageExchangeView(BrickStorage storage_dev) {
+    if (!comm.ctx) throw std::runtime_error("BrickDecomp::comm has no device context");
+    MultiStageExchangeView v;
+    v.comm = comm;
+    v.storage_dev = storage_dev.dat.get();
+    auto it = shift_plans.find(storage_dev.step);
+    if (it == shift_plans.end()) {
+      const size_t sb = storage_dev.step * sizeof(bElem);
+      std::vector<bricks_exchange *> made;
+      for (const auto &stage : shiftPieces()) {
+        const size_t n = stage.size();
+        std::vector<size_t> roff(n), soff(n), bytes(n);
+        std::vector<int> rpeer(n), speer(n);
+        for (size_t i = 0; i < n; ++i) {
+          roff[i] = (size_t)stage[i].recv_pos * sb;
+          soff[i] = (size_t)stage[i].send_pos * sb;
+          bytes[i] = (size_t)stage[i].len * sb;
+          rpeer[i] = rank_map.at(stage[i].from.set);
+          speer[i] = rank_map.at((!stage[i].from).set);
+        }
+        bricks_exchange *ex = nullptr;
+        bricks_detail::require(bricks_exchange_create(comm.ctx, comm.rank, (int)n, roff.data(), soff.data(),
+                                                      bytes.data(), rpeer.data(), speer.data(), &ex),
+                               "bricks_exchange_create");
+        made.push_back(ex);
+      }
+      it = shift_plans.emplace(storage_dev.step, made).first;
+    }
+    v.stages = it->second;
+    return v;
+  }
+
  private:
   static constexpr unsigned NSLOT = static_power<3, dim>::value;
+  std::map<size_t, std::vector<bricks_exchange *>> shift_plans;  ///< SHIFT exchange stages by storage step
   unsigned nb[dim];      ///< interior extent in bricks
   unsigned gd[dim];      ///< ghost depth in bricks
   unsigned td[dim];      ///< extent incl. ghost

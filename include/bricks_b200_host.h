@@ -48,6 +48,13 @@ int bricks_decomp_rank_map(bricks_decomp *d, const int procdims[3], const int co
 int bricks_decomp_exchange_plan(bricks_decomp *d, size_t step, size_t *recv_off, size_t *send_off,
                                 size_t *nbytes, int *recv_peer, int *send_peer);
 
+/* the SHIFT exchange (BrickDecomp::multiStageExchangeView, brick-mpi.h:587-681) as the arguments of
+ * one bricks_exchange_create per stage: stage = 0..2 (axis stage+1); writes up to `cap` pieces and
+ * returns their number in *npieces (call with cap = 0 to size the arrays) */
+int bricks_decomp_shift_plan(bricks_decomp *d, size_t step, int stage, int cap, int *npieces,
+                             size_t *recv_off, size_t *send_off, size_t *nbytes, int *recv_peer,
+                             int *send_peer);
+
 /* init_grid<3> (bricksetup.h:73-90): grid[n0*n1*n2], adj[n0*n1*n2][27] */
 int bricks_init_grid3(const long dimlist[3], unsigned *grid, unsigned *adj);
 /* copyToBrick<3> (to_brick != 0) / copyFromBrick<3> (bricksetup.h:172-221) on row-major bricks */

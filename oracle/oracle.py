@@ -226,6 +226,67 @@ def exchange(storages, dec, procdims, step=512):
     return storages
 
 
+def multistage_packages(dec):
+    """Restated BrickDecomp::multiStageExchangeView (include/brick-mpi.h:587-681): the SHIFT exchange.
+    Stage d = 1..3 exchanges along axis d only; what a corner or edge neighbour owns travels in
+    several hops through the ghost zones of the face neighbours.  Returns, per stage, a list of
+    (n, recv_pieces, send_pieces) in allneighbors order, n = the direction received from (the matching
+    send goes to the mirrored direction); pieces are (first brick, brick count), in packing order.
+    Receive side: the ghost regions owned by n, then every not yet received ghost region whose owner
+    is n plus already exchanged axes.  Send side: the skin regions facing the mirrored direction, then,
+    for each of those further ghost regions and each skin section it spans, the same section inside
+    this rank's own ghost copy of the owner-minus-n neighbour (received in an earlier stage)."""
+    ghost, skin, ssz = dec.ghost, dec.skin, [int(x) for x in dec.skin_size]
+    stages, done = [], 0
+    for d in (1, 2, 3):
+        axis = bitset((d,)) | bitset((-d,))
+        pkgs = []
+        for n in allneighbors():
+            if n == 0 or (n & ~axis):
+                continue
+            recv = [(int(g["pos"]), int(g["len"])) for g in ghost if int(g["neighbor"]) == n]
+            mirrored = bitset_neg(n)
+            send = [(int(k["pos"]), int(k["len"])) for k in skin if int(k["neighbor"]) == mirrored]
+            reach = n | done
+            for g in ghost:
+                owner = int(g["neighbor"])
+                if owner == n or (owner & ~reach) or not (owner & ~done):
+                    continue
+                recv.append((int(g["pos"]), int(g["len"])))
+                via = owner ^ n
+                for sec in range(int(g["skin_st"]), int(g["skin_ed"])):
+                    for g2 in ghost:
+                        if int(g2["neighbor"]) == via and int(g2["skin_st"]) <= sec < int(g2["skin_ed"]):
+                            first = int(g2["pos"]) + sum(ssz[int(g2["skin_st"]):sec])
+                            send.append((first, ssz[sec]))
+            pkgs.append((n, recv, send))
+        stages.append(pkgs)
+        done |= axis
+    return stages
+
+
+def multistage_exchange(storages, dec, procdims, step=512):
+    """In-place emulation of MultiStageExchangeView::exchange (brick-mpi.h:126-176) on P virtual
+    ranks: per stage every rank packs its send pieces, the package for direction n goes to the rank
+    in the mirrored direction, and is unpacked over that rank's receive pieces for n."""
+    P = len(storages)
+    maps = [rank_map(procdims, cart_coords(r, procdims)) for r in range(P)]
+    for pkgs in multistage_packages(dec):
+        snap = [s.copy() for s in storages]
+        for r in range(P):
+            for n, recv, _ in pkgs:
+                src = maps[r][n]
+                sent = [sp for (m, _, sp) in pkgs if m == n][0]
+                packed = np.concatenate([snap[src][a * step:(a + l) * step] for a, l in sent])
+                assert maps[src][bitset_neg(n)] == r
+                at = 0
+                for a, l in recv:
+                    storages[r][a * step:(a + l) * step] = packed[at:at + l * step]
+                    at += l * step
+                assert at == packed.size
+    return storages
+
+
 # ---------------------------------------------------------------------------
 # strong scaling: restatement of strong/args.cpp:36-56,104-113 (getrank, ownership split) and of the
 # link construction of strong/main.cu:188-247 -- ghost[i] of subdomain T is skin[i] of the periodic

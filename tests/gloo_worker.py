@@ -52,6 +52,27 @@ def weak(rank, world, outdir):
     np.save(os.path.join(outdir, "weak_out_%d.npy" % rank), buf.numpy().view(np.float64))
 
 
+def shift(rank, world, outdir):
+    """the SHIFT exchange (bricks_decomp_shift_plan): three stages in order, piece i of a stage is
+    piece i on both ends (both ranks hold the same tables), so the piece index is the tag"""
+    import torch
+    import torch.distributed as dist
+    from bricklib_b200 import capi
+    dims = (32, 16, 16)
+    procdims = capi.cart_dims(world)
+    dec = capi.Decomp(dims, 8)
+    dec.rank_map(procdims, capi.cart_coords(rank, procdims))
+    field = capi.uniform(dec.nbricks * 512, seed=500 + rank)  # same input as weak()
+    buf = torch.from_numpy(field.view(np.uint8).copy())
+    for stage, (ro, so, nb, rp, sp) in enumerate(dec.shift_plan(512)):
+        n = len(ro)
+        _exchange_bytes(dist, torch, rank, buf,
+                        [(int(rp[i]), int(ro[i]), int(nb[i]), 1000 * stage + i) for i in range(n)],
+                        [(int(sp[i]), int(so[i]), int(nb[i]), 1000 * stage + i) for i in range(n)])
+        dist.barrier()
+    np.save(os.path.join(outdir, "shift_out_%d.npy" % rank), buf.numpy().view(np.float64))
+
+
 def strong(rank, world, outdir):
     import torch
     import torch.distributed as dist
@@ -93,6 +114,8 @@ def main():
     import torch.distributed as dist
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
     weak(rank, world, outdir)
+    dist.barrier()
+    shift(rank, world, outdir)
     dist.barrier()
     strong(rank, world, outdir)
     dist.barrier()

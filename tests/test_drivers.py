@@ -69,6 +69,14 @@ def test_weak_driver_validates(drivers, which):
 
 
 @pytest.mark.gpu
+def test_weak_driver_validates_with_the_shift_exchange(drivers):
+    """-m: MultiStageExchangeView; the validation twin exchanges directly, so the two must agree"""
+    rc, out = _run(os.path.join(drivers, "weak"), "-s", "64,48,32", "-I", "3", "-S", "13", "-v", "-m")
+    assert rc == 0, out
+    assert _perf(out) > 0 and "mismatch" not in out
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("which", (7, 125))
 def test_strong_driver_validates(drivers, which):
     rc, out = _run(os.path.join(drivers, "strong"), "-d", "128", "-s", "32", "-I", "3", "-S", str(which), "-v")
@@ -87,6 +95,8 @@ def test_drivers_multi_gpu_validate(drivers, built, ngpus):
     if n.value < ngpus:
         pytest.skip("needs %d GPUs" % ngpus)
     rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "125", "-v")
+    assert rc == 0 and "mismatch" not in out, out
+    rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "7", "-v", "-m")
     assert rc == 0 and "mismatch" not in out, out
     rc, out = _run(os.path.join(drivers, "strong"), "-G", str(ngpus), "-d", "128", "-s", "32", "-I", "3", "-v")
     assert rc == 0 and "Validated" in out, out

@@ -1,5 +1,6 @@
 """world_size-2 run of the N>1 host logic on CPU (gloo): two processes execute the product's
-exchange plans -- the per-region weak plan of BrickDecomp (brick-mpi.h:466-495) and the per-peer
+exchange plans -- the per-region weak plan of BrickDecomp (brick-mpi.h:466-495), its SHIFT form
+(brick-mpi.h:587-681) and the per-peer
 packed strong plan (strong/main.cu:188-443) -- with torch.distributed messages on host buffers,
 and the result must equal the oracle's multi-rank emulation bit for bit."""
 import os
@@ -37,6 +38,9 @@ def test_two_rank_exchange_plans_over_gloo(built, oracle, tmp_path):
         got = np.load(tmp_path / ("weak_out_%d.npy" % r))
         assert np.array_equal(got.view(np.uint64), exp[r].view(np.uint64)), r
         assert not np.array_equal(got, ins[r])
+        # the SHIFT exchange (three stages, six messages) leaves the same storage
+        shifted = np.load(tmp_path / ("shift_out_%d.npy" % r))
+        assert np.array_equal(shifted.view(np.uint64), exp[r].view(np.uint64)), r
 
     # strong: 8 subdomains of 32^3, Morton ids 0-3 on rank 0 and 4-7 on rank 1
     sdec = oracle.Decomp((32, 32, 32), 8)
