@@ -66,6 +66,17 @@ struct MarchItem {
   unsigned validj; /* 2x2-brick footprints (cube tile kernel): the +j brick row is inside the box */
 };
 
+/* kernel parameters of the sweep kernels (__grid_constant__) */
+struct FieldDev;
+struct MarchParams {
+  const MarchItem *items;
+  const unsigned *grid;
+  const unsigned *adj;
+  const FieldDev *fields;
+  unsigned gd0, gd1;
+  double c[10];
+};
+
 /* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane
  * pieces used for the pre-/post-roll of a column.  [0]=centre 8x8, [1]=i-face HWx8,
  * [2]=j-face 8xR, [3]=corner HWxR.  pair: the centre and j-face boxes over TWO bricks that are

@@ -185,43 +185,6 @@ struct LaneK {
   }
 };
 
-/* Halo pieces by per-lane 16-byte cp.async instead of one TMA box per piece (MARCH_HALO_LDGSTS):
- * the SM's TMA engine accepts a copy only every ~46 cycles (profiles/r01_tma_issue_probe.txt), so a
- * stage of 9-12 small boxes is bound by their NUMBER; the same bytes are 3 (stars) to 7 (cube)
- * LDGSTS per lane.  Pieces of one kind sit back to back in the stage and keep the dense
- * [plane][row][chunk] image a TMA box would have written, so the consumers do not change.
- * KIND 0: i-face (HW x 8), 1: j-face (8 x R), 2: ij-corner (HW x R). */
-template <int R, bool CUBE, int P, int KIND>
-__device__ __forceinline__ void halo_group_ldgsts(uint32_t stage, const char *in, size_t brick_bytes,
-                                                  unsigned nb, int ck, int nplanes, int lane) {
-  using L = StageLayout<R, CUBE, P>;
-  constexpr int HW = L::HW;
-  constexpr int NPIECES = KIND == 0 ? 2 : 4, PBASE = KIND == 0 ? 2 : (KIND == 1 ? 4 : 8);
-  constexpr int OFF = KIND == 0 ? L::IL : (KIND == 1 ? L::JL0 : L::XLL);
-  constexpr int WI = KIND == 1 ? 4 : HW / 2; /* 16-byte chunks per row */
-  constexpr int NR = KIND == 0 ? 8 : R;      /* rows per plane */
-  constexpr int PLC = WI * NR, N = PLC * P, TOTAL = N * NPIECES;
-  static_assert(TOTAL % 32 == 0, "halo chunk count");
-#pragma unroll
-  for (int it = 0; it < TOTAL / 32; ++it) {
-    const int u = lane + 32 * it;
-    const int piece = u / N, q = u % N;
-    const int k = q / PLC, row = (q % PLC) / WI, c = q % WI;
-    int ci, cj;
-    if (KIND == 0) {
-      ci = piece ? 0 : 8 - HW, cj = 0;
-    } else if (KIND == 1) {
-      ci = 0, cj = (piece & 2) ? 0 : 8 - R;
-    } else {
-      ci = (piece & 1) ? 0 : 8 - HW, cj = (piece & 2) ? 0 : 8 - R;
-    }
-    const unsigned nbp = __shfl_sync(0xffffffffu, nb, PBASE + piece);
-    if (k < nplanes)
-      cp_async16(stage + OFF + piece * (P * PLC * 16) + q * 16,
-                 in + ((size_t)nbp * brick_bytes + (size_t)((ck + k) * 512 + (cj + row) * 64 + ci * 8 + c * 16)));
-  }
-}
-
 __device__ __forceinline__ void ld_quad(const char *st, int off0, int off1, double (&v)[4]) {
   const double2 a = *reinterpret_cast<const double2 *>(st + off0);
   const double2 b = *reinterpret_cast<const double2 *>(st + off1);

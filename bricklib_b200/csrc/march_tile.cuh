@@ -139,3 +139,169 @@ __device__ __forceinline__ void cube_tile_step(const char *st, const double *__r
 }
 
 }  // namespace dev
+
+#ifndef MARCH_TILE_REGS
+#define MARCH_TILE_REGS 255
+#endif
+#ifndef MARCH_TILE_STAGES
+#define MARCH_TILE_STAGES 3
+#endif
+
+namespace {
+/* 125-point cube, tile form (march_tile.cuh): 2x2-brick footprint, 2x4 points per lane */
+template <int P, int NS>
+__global__ void __maxnreg__(MARCH_TILE_REGS) cube_tile_kernel(const __grid_constant__ MarchParams prm) {
+  using T = dev::TileLayout<P>;
+  constexpr int R = 2, H = 8 / P;
+  extern __shared__ __align__(1024) char smem[];
+  const int lane = threadIdx.x;
+  const MarchItem it = prm.items[blockIdx.x];
+  const FieldDev &fd = prm.fields[blockIdx.y];
+  const int nk = it.nk, nsteps = nk * H + 2;
+  const uint32_t smem0 = dev::smem_u32(smem);
+
+  /* brick ids of the four columns of the footprint: lane t holds layer t */
+  unsigned c00 = 0, c10 = 0, c01 = 0, c11 = 0;
+  if (lane < nk) {
+    const size_t cell = ((size_t)(it.gk0 + lane) * prm.gd1 + it.gj) * prm.gd0 + it.gi;
+    c00 = prm.grid[cell];
+    c10 = it.valid1 ? prm.grid[cell + 1] : prm.adj[(size_t)c00 * 27 + 14];
+    c01 = it.validj ? prm.grid[cell + prm.gd0] : prm.adj[(size_t)c00 * 27 + 16];
+    c11 = (it.valid1 && it.validj) ? prm.grid[cell + prm.gd0 + 1] : prm.adj[(size_t)c01 * 27 + 14];
+  }
+
+  dev::TileProducer tp = {};
+  tp.template init<P>(lane);
+  const char *inb = reinterpret_cast<const char *>(fd.in);
+  const size_t brick_bytes = (size_t)fd.in_step * 8;
+
+  /* lane t < 16 fetches source brick t of stage s (march_tile.cuh: TileProducer) */
+  auto load_nb = [&](int s) -> unsigned {
+    const int dk = (s == 0) ? -1 : ((s == nsteps - 1) ? +1 : 0);
+    const int layer = (s == 0) ? 0 : ((s == nsteps - 1) ? nk - 1 : (s - 1) / H);
+    const unsigned b00 = __shfl_sync(0xffffffffu, c00, layer), b10 = __shfl_sync(0xffffffffu, c10, layer);
+    const unsigned b01 = __shfl_sync(0xffffffffu, c01, layer), b11 = __shfl_sync(0xffffffffu, c11, layer);
+    const unsigned base = tp.nb_base < 2 ? (tp.nb_base == 0 ? b00 : b10) : (tp.nb_base == 2 ? b01 : b11);
+    return dev::ld_nc_pinned(prm.adj + (size_t)base * 27 + (dk + 1) * 9 + tp.nb_slot);
+  };
+  auto issue = [&](int s, unsigned nb) {
+    const bool roll = (s == 0) || (s == nsteps - 1);
+    const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
+    const int npl = roll ? R : P;
+    const uint32_t stage = smem0 + (s % NS) * T::BYTES;
+    const char *src0 = inb + (size_t)(ck * 512);
+    const char *pc[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+      pc[b] = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, b) * brick_bytes + (size_t)(lane * 16));
+    const char *pj = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, tp.j_from) * brick_bytes + (size_t)tp.j_src);
+    const char *pi = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, tp.i_from) * brick_bytes + (size_t)tp.i_src);
+    const char *px = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, tp.x_from) * brick_bytes + (size_t)tp.x_src);
+#pragma unroll
+    for (int k = 0; k < P; ++k) {
+      if (k < npl) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) /* brick b = (row b>>1, column b&1): 4 sub-image rows, 4 chunks on */
+          dev::cp_async16_nb(stage + tp.c_dst + k * T::PLANE + (b >> 1) * 4 * T::PITCH + (b & 1) * 64, pc[b] + k * 512);
+        dev::cp_async16_nb(stage + tp.j_dst + k * T::PLANE, pj + k * 512);
+        dev::cp_async16_nb(stage + tp.i_dst + k * T::PLANE, pi + k * 512);
+      }
+    }
+    if (tp.x_valid && (lane >> 3) < npl) dev::cp_async16_nb(stage + tp.x_dst, px);
+    dev::cp_async_commit();
+  };
+
+  double carryA[2 * R][4], carryB[2 * R][4];
+#pragma unroll
+  for (int a = 0; a < 2 * R; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) carryA[a][m] = carryB[a][m] = 0.0;
+
+  /* consumer lane = 4*rp + quad: rows 2rp, 2rp+1, columns 4*quad .. 4*quad+3 of the footprint */
+  const int rp = lane >> 2, quad = lane & 3;
+  const int cbase = rp * T::PITCH + quad * 32;
+  const int lane_off = ((2 * rp) & 7) * 8 + (quad & 1) * 4;
+  const bool lane_valid = ((quad < 2) || it.valid1) && ((rp < 4) || it.validj);
+  dev::OutPtrs o;
+  o.cur = o.prev = nullptr;
+  o.curv = o.prevv = false;
+
+  /* NS-deep pipeline, one cp.async group per loop trip (empty near the end of the column), so the
+   * group of stage s is always the NS-th newest when stage s is consumed */
+  unsigned nbn;
+#pragma unroll
+  for (int t = 0; t < NS - 1; ++t) {
+    nbn = load_nb(t);
+    issue(t, nbn);
+  }
+  nbn = load_nb(NS - 1 < nsteps ? NS - 1 : 0);
+
+  for (int s = 0; s < nsteps; ++s) {
+    dev::cp_async_wait<NS - 2>(); /* this lane's chunks of stage s have landed ... */
+    __syncwarp();                 /* ... and so have every other lane's */
+    /* refill the buffer the previous trip finished with; the copies carry no compiler barrier, so
+     * their address arithmetic interleaves with this stage's loads and arithmetic */
+    if (s + NS - 1 < nsteps) {
+      issue(s + NS - 1, nbn);
+      if (s + NS < nsteps) nbn = load_nb(s + NS);
+    } else {
+      dev::cp_async_commit();
+    }
+    const char *st = smem + (s % NS) * T::BYTES + cbase;
+    int mode = 1, zbase = 0;
+    if (s == 0) {
+      mode = 0;
+    } else if (s == nsteps - 1) {
+      mode = 2;
+      zbase = 8;
+    } else {
+      const int layer = (s - 1) / H, part = (s - 1) % H;
+      zbase = part * P;
+      if (part == 0) {
+        const unsigned b00 = __shfl_sync(0xffffffffu, c00, layer), b10 = __shfl_sync(0xffffffffu, c10, layer);
+        const unsigned b01 = __shfl_sync(0xffffffffu, c01, layer), b11 = __shfl_sync(0xffffffffu, c11, layer);
+        const unsigned mine = rp < 4 ? (quad < 2 ? b00 : b10) : (quad < 2 ? b01 : b11);
+        o.prev = o.cur;
+        o.prevv = o.curv && layer > 0;
+        o.cur = fd.out + (size_t)mine * fd.out_step + lane_off;
+        o.curv = lane_valid;
+      }
+    }
+    if (mode == 1)
+      dev::cube_tile_step<P, P, 1>(st, prm.c, carryA, carryB, o, zbase);
+    else if (mode == 0)
+      dev::cube_tile_step<P, R, 0>(st, prm.c, carryA, carryB, o, zbase);
+    else
+      dev::cube_tile_step<P, R, 2>(st, prm.c, carryA, carryB, o, zbase);
+    __syncwarp(); /* every lane is done reading this stage before it is refilled */
+  }
+}
+
+template <int P, int NS>
+int launch_tile(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
+  using T = dev::TileLayout<P>;
+  const int smem = NS * T::BYTES;
+  auto kern = cube_tile_kernel<P, NS>;
+  static bool configured[64] = {false};
+  bool &done = configured[plan->ctx->device & 63];
+  if (!done) {
+    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    done = true;
+  }
+  MarchParams prm;
+  int nitems = 0;
+  if (int rc = bricks::plan_items(plan, bricks::column_length(stencil_id), &prm.items, &nitems, 2)) return rc;
+  prm.grid = plan->grid_dev;
+  prm.adj = plan->adj_dev;
+  prm.fields = fields;
+  prm.gd0 = plan->gdims[0];
+  prm.gd1 = plan->gdims[1];
+  for (int i = 0; i < 10; ++i) prm.c[i] = c[i];
+  kern<<<dim3(nitems, nfields), 32, smem, s>>>(prm);
+  BRK_CUDA(cudaGetLastError());
+  ++bricks::g_launches;
+  return 0;
+}
+
+}  // namespace

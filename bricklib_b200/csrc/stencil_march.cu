@@ -6,8 +6,13 @@
 #include <cstring>
 
 #include "march_steps.cuh"
+/* measured re-designs of the cube sweep, built only by tools/build_variants.sh */
+#ifdef MARCH_CUBE_WINDOW
 #include "march_window.cuh"
+#endif
+#ifdef MARCH_CUBE_TILE
 #include "march_tile.cuh"
+#endif
 
 /* Register caps.  The register file is 4 x 16 Ki, one quarter per scheduler, so a one-warp CTA fits
  * floor(16384 / (32 * regs)) times per scheduler: <= 128 registers -> 16 warps per SM, <= 168 ->
@@ -15,29 +20,9 @@
 #ifndef MARCH_CUBE_REGS
 #define MARCH_CUBE_REGS 168
 #endif
-#ifndef MARCH_WINDOW_REGS
-#define MARCH_WINDOW_REGS 168
-#endif
-#ifndef MARCH_TILE_REGS
-#define MARCH_TILE_REGS 255
-#endif
-#ifndef MARCH_TILE_STAGES
-#define MARCH_TILE_STAGES 3
-#endif
-#ifndef MARCH_WINDOW_STAGES
-#define MARCH_WINDOW_STAGES 2
-#endif
 
 namespace {
 
-struct MarchParams {
-  const MarchItem *items;
-  const unsigned *grid;
-  const unsigned *adj;
-  const FieldDev *fields;
-  unsigned gd0, gd1;
-  double c[10];
-};
 
 template <int R, bool CUBE, int VAR, int P>
 /* register cap for the cube: measured best on B200 (profiles/r01_maxnreg_sweep.txt) */
@@ -90,11 +75,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
     const unsigned rowb = pk.useb1 ? b1 : b0;
     unsigned nb = 0;
-#ifdef MARCH_PIN_ADJ /* experiment: a load the compiler may not sink towards its use */
-    if (lane < 12) nb = dev::ld_nc_pinned(prm.adj + (size_t)rowb * 27 + (dk + 1) * 9 + (pk.dj + 1) * 3 + (pk.di + 1));
-#else
     if (lane < 12) nb = prm.adj[(size_t)rowb * 27 + (dk + 1) * 9 + (pk.dj + 1) * 3 + (pk.di + 1)];
-#endif
     return nb;
   };
   auto issue = [&](int s, unsigned nb) {
@@ -102,44 +83,12 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     const uint32_t bar = bar0 + 8 * (s & 1);
     const uint32_t dst = smem0 + (s & 1) * L::BYTES + pk.off;
     const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
-#ifdef MARCH_HALO_LDGSTS
-    /* TMA moves the two centre bricks only (one copy when they are consecutive in storage); every
-     * halo piece is a few 16-byte cp.async per lane (march_dev.cuh: halo_group_ldgsts) */
-    if (lane == 0) dev::mbar_expect_tx(bar, (roll ? R : P) * 2 * L::C_PL);
-    const unsigned nb_up = __shfl_down_sync(0xffffffffu, nb, 1), nb_dn = __shfl_up_sync(0xffffffffu, nb, 1);
-    const bool lead = !roll && lane == 0 && nb_up == nb + 1;
-    const bool follow = !roll && lane == 1 && nb == nb_dn + 1;
-    if (lane < 2 && !follow) {
-      const CUtensorMap *map = roll ? &fd.maps.roll[0] : (lead ? &fd.maps.pair[0] : &fd.maps.main[0]);
-      dev::tma_load_4d(dst, map, pk.ci, pk.cj, ck, (int)nb, bar);
-    }
-    if (CUBE || !roll) {
-      const uint32_t stage = smem0 + (s & 1) * L::BYTES;
-      const char *inb = reinterpret_cast<const char *>(fd.in);
-      const size_t bb = (size_t)fd.in_step * 8;
-      const int npl = roll ? R : P;
-      dev::halo_group_ldgsts<R, CUBE, P, 0>(stage, inb, bb, nb, ck, npl, lane);
-      dev::halo_group_ldgsts<R, CUBE, P, 1>(stage, inb, bb, nb, ck, npl, lane);
-      if constexpr (CUBE) dev::halo_group_ldgsts<R, CUBE, P, 2>(stage, inb, bb, nb, ck, npl, lane);
-    }
-    dev::cp_async_commit();
-#else
-#ifdef MARCH_CORNER_LDGSTS /* experiment: the four 2x2 corner pieces of the cube by one cp.async per lane */
-    constexpr int XB = CUBE ? 4 * L::X_PL : 0;
-    if (lane == 0) dev::mbar_expect_tx(bar, roll ? R * (ROLL_PLANE_BYTES - XB) : P * (MAIN_PLANE_BYTES - XB));
-    const int np = CUBE ? 8 : (roll ? L::NPIECE_ROLL : L::NPIECE_MAIN);
-    if constexpr (CUBE)
-      dev::halo_group_ldgsts<R, CUBE, P, 2>(smem0 + (s & 1) * L::BYTES, reinterpret_cast<const char *>(fd.in),
-                                            (size_t)fd.in_step * 8, nb, ck, roll ? R : P, lane);
-    dev::cp_async_commit();
-#else
     if (lane == 0) dev::mbar_expect_tx(bar, roll ? R * ROLL_PLANE_BYTES : P * MAIN_PLANE_BYTES);
     const int np = roll ? L::NPIECE_ROLL : L::NPIECE_MAIN;
-#endif
     /* pieces 0/1 (centres), 4/5 and 6/7 (j-faces) sit back to back in the stage: when their two
      * bricks are consecutive in storage -- the rule inside a BrickDecomp region -- the even lane
-     * fills both with one two-brick copy and the odd lane stays idle.  The per-SM TMA engine
-     * accepts a copy every ~46 cycles, so a stage costs by its NUMBER of copies. */
+     * fills both with one two-brick copy and the odd lane stays idle (9 instead of 12 copies per
+     * cube stage: +1-2 %; going further down to 5 changed nothing, profiles/r02_experiments/). */
     const unsigned nb_up = __shfl_down_sync(0xffffffffu, nb, 1), nb_dn = __shfl_up_sync(0xffffffffu, nb, 1);
     const bool pairable = !roll && (lane < 2 || (lane >= 4 && lane < 8));
     const bool lead = pairable && !(lane & 1) && nb_up == nb + 1;
@@ -148,7 +97,6 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
       const CUtensorMap *map = roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[lane < 2 ? 0 : 1] : &fd.maps.main[pk.map]);
       dev::tma_load_4d(dst, map, pk.ci, pk.cj, ck, (int)nb, bar);
     }
-#endif
   };
 
   double carry[2 * R][4];
@@ -171,15 +119,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
       dev::fence_proxy_async();
       issue(s + 1, nbn);
       if (s + 2 < nsteps) nbn = load_nb(s + 2);
-#if defined(MARCH_HALO_LDGSTS) || defined(MARCH_CORNER_LDGSTS)
-      dev::cp_async_wait<1>(); /* this lane's halo chunks of stage s have landed ... */
-    } else {
-      dev::cp_async_wait<0>();
     }
-    __syncwarp(); /* ... and so have every other lane's */
-#else
-    }
-#endif
     dev::mbar_wait(bar0 + 8 * (s & 1), (s >> 1) & 1);
     const char *st = smem + (s & 1) * L::BYTES;
     int mode = 1, zbase = 0;
@@ -217,311 +157,6 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     }
     __syncwarp();
   }
-}
-
-/* 125-point cube, window form (march_window.cuh): padded plane images filled by per-lane cp.async */
-template <int P, int NS>
-__global__ void __maxnreg__(MARCH_WINDOW_REGS) cube_window_kernel(const __grid_constant__ MarchParams prm) {
-  using W = dev::WinLayout<P>;
-  constexpr int R = 2, H = 8 / P;
-  extern __shared__ __align__(1024) char smem[];
-  const int lane = threadIdx.x;
-  const MarchItem it = prm.items[blockIdx.x];
-  const FieldDev &fd = prm.fields[blockIdx.y];
-  const int nk = it.nk, nsteps = nk * H + 2;
-  const uint32_t smem0 = dev::smem_u32(smem);
-
-  unsigned col0 = 0, col1 = 0; /* brick ids of the column: lane t holds layer t */
-  if (lane < nk) {
-    const size_t cell = ((size_t)(it.gk0 + lane) * prm.gd1 + it.gj) * prm.gd0 + it.gi;
-    col0 = prm.grid[cell];
-    col1 = it.valid1 ? prm.grid[cell + 1] : prm.adj[(size_t)col0 * 27 + 14];
-  }
-
-  dev::WinProducer wp;
-  wp.init(lane);
-  const char *inb = reinterpret_cast<const char *>(fd.in);
-  const size_t brick_bytes = (size_t)fd.in_step * 8;
-
-  /* the three bricks (dj = -1, 0, +1) of the lane's brick column for stage s */
-  auto load_nb = [&](int s) -> dev::WinNb {
-    const int dk = (s == 0) ? -1 : ((s == nsteps - 1) ? +1 : 0);
-    const int layer = (s == 0) ? 0 : ((s == nsteps - 1) ? nk - 1 : (s - 1) / H);
-    const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
-    const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
-    const unsigned *row = prm.adj + (size_t)(wp.useb1 ? b1 : b0) * 27 + (dk + 1) * 9 + (wp.di + 1);
-    dev::WinNb nb;
-    nb.m = __ldg(row);
-    nb.z = __ldg(row + 3);
-    nb.p = __ldg(row + 6);
-    return nb;
-  };
-  auto issue = [&](int s, const dev::WinNb &nb) {
-    const bool roll = (s == 0) || (s == nsteps - 1);
-    const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
-    const int npl = roll ? R : P;
-    const char *pa = inb + ((size_t)(wp.a_low ? nb.m : nb.z) * brick_bytes + (size_t)(wp.offA + ck * 512));
-    const char *pb = inb + ((size_t)nb.z * brick_bytes + (size_t)(wp.offB + ck * 512));
-    const char *pc = inb + ((size_t)(wp.c_high ? nb.p : nb.z) * brick_bytes + (size_t)(wp.offC + ck * 512));
-    const uint32_t dst = smem0 + (s % NS) * W::BYTES + wp.dst0;
-    if (wp.valid) {
-#pragma unroll
-      for (int k = 0; k < P; ++k) {
-        if (k < npl) {
-          dev::cp_async16(dst + (k * W::NROW + 0) * W::PITCH, pa + k * 512);
-          dev::cp_async16(dst + (k * W::NROW + 3) * W::PITCH, pb + k * 512);
-          dev::cp_async16(dst + (k * W::NROW + 6) * W::PITCH, pb + k * 512 + 192);
-          dev::cp_async16(dst + (k * W::NROW + 9) * W::PITCH, pc + k * 512);
-        }
-      }
-    }
-    dev::cp_async_commit();
-  };
-
-  double carry[2 * R][4];
-#pragma unroll
-  for (int a = 0; a < 2 * R; ++a)
-#pragma unroll
-    for (int m = 0; m < 4; ++m) carry[a][m] = 0.0;
-
-  /* consumer lane = 4*j + 2*bb + ih: the eight lanes of an LDS.128 phase cover two rows x four quads */
-  const int cj = lane >> 2, cbb = (lane >> 1) & 1, cih = lane & 1;
-  const int cbase = cj * W::PITCH + cbb * 64 + cih * 32;
-  const int lane_off = cj * 8 + cih * 4;
-  dev::OutPtrs o;
-  o.cur = o.prev = nullptr;
-  o.curv = o.prevv = false;
-
-  /* NS-deep pipeline, one cp.async group per loop trip (empty near the end of the column), so the
-   * group of stage s is always the NS-th newest when stage s is consumed */
-  dev::WinNb nbn;
-#pragma unroll
-  for (int t = 0; t < NS - 1; ++t) {
-    nbn = load_nb(t < nsteps ? t : 0);
-    if (t < nsteps) issue(t, nbn);
-    else dev::cp_async_commit();
-  }
-  nbn = load_nb(NS - 1 < nsteps ? NS - 1 : 0);
-
-  for (int s = 0; s < nsteps; ++s) {
-    if (s + NS - 1 < nsteps) {
-      issue(s + NS - 1, nbn);
-      if (s + NS < nsteps) nbn = load_nb(s + NS);
-    } else {
-      dev::cp_async_commit();
-    }
-    dev::cp_async_wait<NS - 1>(); /* this lane's chunks of stage s have landed ... */
-    __syncwarp();                 /* ... and so have every other lane's */
-    const char *st = smem + (s % NS) * W::BYTES + cbase;
-    int mode = 1, zbase = 0;
-    if (s == 0) {
-      mode = 0;
-    } else if (s == nsteps - 1) {
-      mode = 2;
-      zbase = 8;
-    } else {
-      const int layer = (s - 1) / H, part = (s - 1) % H;
-      zbase = part * P;
-      if (part == 0) {
-        const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
-        const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
-        o.prev = o.cur;
-        o.prevv = o.curv && layer > 0;
-        o.cur = fd.out + (size_t)(cbb ? b1 : b0) * fd.out_step + lane_off;
-        o.curv = (cbb == 0) || (it.valid1 != 0);
-      }
-    }
-    if (mode == 1)
-      dev::cube_window_step<P, P, 1>(st, prm.c, carry, o, zbase);
-    else if (mode == 0)
-      dev::cube_window_step<P, R, 0>(st, prm.c, carry, o, zbase);
-    else
-      dev::cube_window_step<P, R, 2>(st, prm.c, carry, o, zbase);
-    __syncwarp(); /* every lane is done reading this stage before it is refilled */
-  }
-}
-
-template <int P>
-int launch_window(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
-  using W = dev::WinLayout<P>;
-  const int smem = MARCH_WINDOW_STAGES * W::BYTES;
-  auto kern = cube_window_kernel<P, MARCH_WINDOW_STAGES>;
-  static bool configured[64] = {false};
-  bool &done = configured[plan->ctx->device & 63];
-  if (!done) {
-    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    done = true;
-  }
-  MarchParams prm;
-  int nitems = 0;
-  if (int rc = bricks::plan_items(plan, bricks::column_length(stencil_id), &prm.items, &nitems)) return rc;
-  prm.grid = plan->grid_dev;
-  prm.adj = plan->adj_dev;
-  prm.fields = fields;
-  prm.gd0 = plan->gdims[0];
-  prm.gd1 = plan->gdims[1];
-  for (int i = 0; i < 10; ++i) prm.c[i] = c[i];
-  kern<<<dim3(nitems, nfields), 32, smem, s>>>(prm);
-  BRK_CUDA(cudaGetLastError());
-  ++bricks::g_launches;
-  return 0;
-}
-
-/* 125-point cube, tile form (march_tile.cuh): 2x2-brick footprint, 2x4 points per lane */
-template <int P, int NS>
-__global__ void __maxnreg__(MARCH_TILE_REGS) cube_tile_kernel(const __grid_constant__ MarchParams prm) {
-  using T = dev::TileLayout<P>;
-  constexpr int R = 2, H = 8 / P;
-  extern __shared__ __align__(1024) char smem[];
-  const int lane = threadIdx.x;
-  const MarchItem it = prm.items[blockIdx.x];
-  const FieldDev &fd = prm.fields[blockIdx.y];
-  const int nk = it.nk, nsteps = nk * H + 2;
-  const uint32_t smem0 = dev::smem_u32(smem);
-
-  /* brick ids of the four columns of the footprint: lane t holds layer t */
-  unsigned c00 = 0, c10 = 0, c01 = 0, c11 = 0;
-  if (lane < nk) {
-    const size_t cell = ((size_t)(it.gk0 + lane) * prm.gd1 + it.gj) * prm.gd0 + it.gi;
-    c00 = prm.grid[cell];
-    c10 = it.valid1 ? prm.grid[cell + 1] : prm.adj[(size_t)c00 * 27 + 14];
-    c01 = it.validj ? prm.grid[cell + prm.gd0] : prm.adj[(size_t)c00 * 27 + 16];
-    c11 = (it.valid1 && it.validj) ? prm.grid[cell + prm.gd0 + 1] : prm.adj[(size_t)c01 * 27 + 14];
-  }
-
-  dev::TileProducer tp = {};
-  tp.template init<P>(lane);
-  const char *inb = reinterpret_cast<const char *>(fd.in);
-  const size_t brick_bytes = (size_t)fd.in_step * 8;
-
-  /* lane t < 16 fetches source brick t of stage s (march_tile.cuh: TileProducer) */
-  auto load_nb = [&](int s) -> unsigned {
-    const int dk = (s == 0) ? -1 : ((s == nsteps - 1) ? +1 : 0);
-    const int layer = (s == 0) ? 0 : ((s == nsteps - 1) ? nk - 1 : (s - 1) / H);
-    const unsigned b00 = __shfl_sync(0xffffffffu, c00, layer), b10 = __shfl_sync(0xffffffffu, c10, layer);
-    const unsigned b01 = __shfl_sync(0xffffffffu, c01, layer), b11 = __shfl_sync(0xffffffffu, c11, layer);
-    const unsigned base = tp.nb_base < 2 ? (tp.nb_base == 0 ? b00 : b10) : (tp.nb_base == 2 ? b01 : b11);
-    return dev::ld_nc_pinned(prm.adj + (size_t)base * 27 + (dk + 1) * 9 + tp.nb_slot);
-  };
-  auto issue = [&](int s, unsigned nb) {
-    const bool roll = (s == 0) || (s == nsteps - 1);
-    const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
-    const int npl = roll ? R : P;
-    const uint32_t stage = smem0 + (s % NS) * T::BYTES;
-    const char *src0 = inb + (size_t)(ck * 512);
-    const char *pc[4];
-#pragma unroll
-    for (int b = 0; b < 4; ++b)
-      pc[b] = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, b) * brick_bytes + (size_t)(lane * 16));
-    const char *pj = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, tp.j_from) * brick_bytes + (size_t)tp.j_src);
-    const char *pi = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, tp.i_from) * brick_bytes + (size_t)tp.i_src);
-    const char *px = src0 + ((size_t)__shfl_sync(0xffffffffu, nb, tp.x_from) * brick_bytes + (size_t)tp.x_src);
-#pragma unroll
-    for (int k = 0; k < P; ++k) {
-      if (k < npl) {
-#pragma unroll
-        for (int b = 0; b < 4; ++b) /* brick b = (row b>>1, column b&1): 4 sub-image rows, 4 chunks on */
-          dev::cp_async16_nb(stage + tp.c_dst + k * T::PLANE + (b >> 1) * 4 * T::PITCH + (b & 1) * 64, pc[b] + k * 512);
-        dev::cp_async16_nb(stage + tp.j_dst + k * T::PLANE, pj + k * 512);
-        dev::cp_async16_nb(stage + tp.i_dst + k * T::PLANE, pi + k * 512);
-      }
-    }
-    if (tp.x_valid && (lane >> 3) < npl) dev::cp_async16_nb(stage + tp.x_dst, px);
-    dev::cp_async_commit();
-  };
-
-  double carryA[2 * R][4], carryB[2 * R][4];
-#pragma unroll
-  for (int a = 0; a < 2 * R; ++a)
-#pragma unroll
-    for (int m = 0; m < 4; ++m) carryA[a][m] = carryB[a][m] = 0.0;
-
-  /* consumer lane = 4*rp + quad: rows 2rp, 2rp+1, columns 4*quad .. 4*quad+3 of the footprint */
-  const int rp = lane >> 2, quad = lane & 3;
-  const int cbase = rp * T::PITCH + quad * 32;
-  const int lane_off = ((2 * rp) & 7) * 8 + (quad & 1) * 4;
-  const bool lane_valid = ((quad < 2) || it.valid1) && ((rp < 4) || it.validj);
-  dev::OutPtrs o;
-  o.cur = o.prev = nullptr;
-  o.curv = o.prevv = false;
-
-  /* NS-deep pipeline, one cp.async group per loop trip (empty near the end of the column), so the
-   * group of stage s is always the NS-th newest when stage s is consumed */
-  unsigned nbn;
-#pragma unroll
-  for (int t = 0; t < NS - 1; ++t) {
-    nbn = load_nb(t);
-    issue(t, nbn);
-  }
-  nbn = load_nb(NS - 1 < nsteps ? NS - 1 : 0);
-
-  for (int s = 0; s < nsteps; ++s) {
-    dev::cp_async_wait<NS - 2>(); /* this lane's chunks of stage s have landed ... */
-    __syncwarp();                 /* ... and so have every other lane's */
-    /* refill the buffer the previous trip finished with; the copies carry no compiler barrier, so
-     * their address arithmetic interleaves with this stage's loads and arithmetic */
-    if (s + NS - 1 < nsteps) {
-      issue(s + NS - 1, nbn);
-      if (s + NS < nsteps) nbn = load_nb(s + NS);
-    } else {
-      dev::cp_async_commit();
-    }
-    const char *st = smem + (s % NS) * T::BYTES + cbase;
-    int mode = 1, zbase = 0;
-    if (s == 0) {
-      mode = 0;
-    } else if (s == nsteps - 1) {
-      mode = 2;
-      zbase = 8;
-    } else {
-      const int layer = (s - 1) / H, part = (s - 1) % H;
-      zbase = part * P;
-      if (part == 0) {
-        const unsigned b00 = __shfl_sync(0xffffffffu, c00, layer), b10 = __shfl_sync(0xffffffffu, c10, layer);
-        const unsigned b01 = __shfl_sync(0xffffffffu, c01, layer), b11 = __shfl_sync(0xffffffffu, c11, layer);
-        const unsigned mine = rp < 4 ? (quad < 2 ? b00 : b10) : (quad < 2 ? b01 : b11);
-        o.prev = o.cur;
-        o.prevv = o.curv && layer > 0;
-        o.cur = fd.out + (size_t)mine * fd.out_step + lane_off;
-        o.curv = lane_valid;
-      }
-    }
-    if (mode == 1)
-      dev::cube_tile_step<P, P, 1>(st, prm.c, carryA, carryB, o, zbase);
-    else if (mode == 0)
-      dev::cube_tile_step<P, R, 0>(st, prm.c, carryA, carryB, o, zbase);
-    else
-      dev::cube_tile_step<P, R, 2>(st, prm.c, carryA, carryB, o, zbase);
-    __syncwarp(); /* every lane is done reading this stage before it is refilled */
-  }
-}
-
-template <int P, int NS>
-int launch_tile(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
-  using T = dev::TileLayout<P>;
-  const int smem = NS * T::BYTES;
-  auto kern = cube_tile_kernel<P, NS>;
-  static bool configured[64] = {false};
-  bool &done = configured[plan->ctx->device & 63];
-  if (!done) {
-    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    done = true;
-  }
-  MarchParams prm;
-  int nitems = 0;
-  if (int rc = bricks::plan_items(plan, bricks::column_length(stencil_id), &prm.items, &nitems, 2)) return rc;
-  prm.grid = plan->grid_dev;
-  prm.adj = plan->adj_dev;
-  prm.fields = fields;
-  prm.gd0 = plan->gdims[0];
-  prm.gd1 = plan->gdims[1];
-  for (int i = 0; i < 10; ++i) prm.c[i] = c[i];
-  kern<<<dim3(nitems, nfields), 32, smem, s>>>(prm);
-  BRK_CUDA(cudaGetLastError());
-  ++bricks::g_launches;
-  return 0;
 }
 
 template <int R, bool CUBE, int VAR, int P>

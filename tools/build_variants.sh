@@ -1,9 +1,21 @@
 #!/bin/bash
-# build the kernel-experiment libraries (lib/libbricks_b200_<name>.so) next to the product library
+# Build kernel-experiment libraries (lib/libbricks_b200_<name>.so) next to the product library.
+# usage: tools/build_variants.sh [name ...]   (default: all).  Time/verify them on a B200 with
+#        VARIANT=<name> BRICKS_LIB=$PWD/bricklib_b200/lib/libbricks_b200_<name>.so python tools/variant_check.py 125
 cd "$(dirname "$0")/.."
-build() { n=$1; shift; BRICKS_EXP_NAME=$n BRICKS_EXP_FLAGS="$*" python bricklib_b200/build.py >/dev/null && echo "built $n"; }
-build pinadj -DMARCH_PIN_ADJ &
-build corner -DMARCH_CORNER_LDGSTS &
-build cornerpin -DMARCH_CORNER_LDGSTS -DMARCH_PIN_ADJ &
-build tile2s4np -DMARCH_CUBE_TILE=2 -DMARCH_TILE_STAGES=4 -DMARCH_TILE_NOPAD &
+declare -A FLAGS=(
+  [win4]="-DMARCH_CUBE_WINDOW=4"
+  [win2r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128"
+  [win2s3r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128 -DMARCH_WINDOW_STAGES=3"
+  [tile2]="-DMARCH_CUBE_TILE=2"
+  [tile2s4np]="-DMARCH_CUBE_TILE=2 -DMARCH_TILE_STAGES=4 -DMARCH_TILE_NOPAD"
+  [tile2r168]="-DMARCH_CUBE_TILE=2 -DMARCH_TILE_REGS=168 -DMARCH_TILE_STAGES=2"
+  [tile4s2]="-DMARCH_CUBE_TILE=4 -DMARCH_TILE_STAGES=2"
+  [tile4s2np]="-DMARCH_CUBE_TILE=4 -DMARCH_TILE_STAGES=2 -DMARCH_TILE_NOPAD"
+)
+names=("$@"); [ ${#names[@]} -eq 0 ] && names=("${!FLAGS[@]}")
+for n in "${names[@]}"; do
+  [ -z "${FLAGS[$n]:-}" ] && { echo "unknown variant $n"; exit 1; }
+  ( BRICKS_EXP_NAME=$n BRICKS_EXP_FLAGS="${FLAGS[$n]}" python bricklib_b200/build.py >/dev/null && echo "built $n" ) &
+done
 wait
