@@ -74,7 +74,7 @@ struct MarchParams {
   const unsigned *adj;
   const FieldDev *fields;
   unsigned gd0, gd1;
-  double c[10];
+  double c[27];
 };
 
 /* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane

@@ -108,9 +108,12 @@ struct StageLayout {
   static constexpr int IL = 2 * P * C_PL, IR = IL + P * I_PL;
   static constexpr int JL0 = IR + P * I_PL, JL1 = JL0 + P * J_PL, JH0 = JL1 + P * J_PL,
                        JH1 = JH0 + P * J_PL;
-  static constexpr int XLL = JH1 + P * J_PL, XRL = XLL + P * X_PL, XLH = XRL + P * X_PL,
-                       XRH = XLH + P * X_PL;
-  static constexpr int RAW = CUBE ? XRH + P * X_PL : XLL;
+  /* a TMA destination must be 128-byte aligned: the 2x1 corner pieces of the 27-point cube are
+   * only 16 bytes per plane */
+  static constexpr int X_STRIDE = P * X_PL < 128 ? 128 : P * X_PL;
+  static constexpr int XLL = JH1 + P * J_PL, XRL = XLL + X_STRIDE, XLH = XRL + X_STRIDE,
+                       XRH = XLH + X_STRIDE;
+  static constexpr int RAW = CUBE ? XRH + X_STRIDE : XLL;
   static constexpr int BYTES = (RAW + 511) / 512 * 512;
   static constexpr int NPIECE_MAIN = CUBE ? 12 : 8;
   static constexpr int NPIECE_ROLL = CUBE ? 12 : 2;

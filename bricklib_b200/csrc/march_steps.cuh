@@ -129,6 +129,53 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
     for (int m = 0; m < 4; ++m) carry[a][m] = acc[NZ + a][m];
 }
 
+/* ------------------------------------------------------------------ 27-point cube, 27 coefficients
+ * d3pt27 (stencils/3axis.cpp:165-247).  w[(dk+1)*9 + (dj+1)*3 + (di+1)] is the weight of
+ * in(k+dk, j+dj, i+di); an input plane z feeds output plane z-1 with the dk = +1 block, z with the
+ * dk = 0 block and z+1 with the dk = -1 block: 27 FMAs per point. */
+template <int P, int NZ, int MODE>
+__device__ __forceinline__ void cube27_step(const char *st, const LaneK<1, true, P> &lk,
+                                            const double *__restrict__ w, double (&carry)[2][4],
+                                            const OutPtrs &o, int zbase) {
+  constexpr int R = 1, HW = 2;
+  double acc[NZ + 2][4];
+#pragma unroll
+  for (int a = 0; a < NZ + 2; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) acc[a][m] = a < 2 ? carry[a][m] : 0.0;
+
+#pragma unroll
+  for (int z = 0; z < NZ; ++z) {
+    double e[3][6]; /* rows j-1, j, j+1; columns i-1 .. i+4 of the lane's quad */
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      double x[4], h[HW];
+      ld_quad(st, lk.row0[a] + z * lk.rpitch[a], lk.row1[a] + z * lk.rpitch[a], x);
+      ld_halo<HW>(st, lk.hrow[a] + z * lk.hpitch[a], lk.halo, h);
+      gather_i<R, HW>(x, h, lk.halo, lk.bb, lk.srcL, lk.srcR, e[a]);
+    }
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+#pragma unroll
+      for (int blk = 0; blk < 3; ++blk) {
+        /* block blk = dk + 1 goes to output plane z - dk, i.e. acc[z + 2 - blk] */
+        if ((MODE == 0 && blk != 0) || (MODE == 2 && blk != 2)) continue;
+        double s = blk == 0 ? 0.0 : acc[z + 2 - blk][m];
+#pragma unroll
+        for (int dj = 0; dj < 3; ++dj)
+#pragma unroll
+          for (int di = 0; di < 3; ++di) s = fma(w[blk * 9 + dj * 3 + di], e[dj][m + di], s);
+        acc[z + 2 - blk][m] = s;
+      }
+    }
+    store_done<R, MODE>(o, zbase, z, acc[z]);
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int m = 0; m < 4; ++m) carry[a][m] = acc[NZ + a][m];
+}
+
 /* One input plane of the cube: e[b][0..7] = v_b over the lane's quad and two columns either side.
  * Adds the plane's contributions to the five output planes it feeds (acc[z..z+4]). */
 template <int NZ, int MODE>

@@ -65,6 +65,7 @@ unsigned column_length(int stencil_id) {
    * amortise the pre-/post-roll planes (arithmetic-bound cube) */
   switch (stencil_id) {
     case BRICKS_ST_125PT: return 17;
+    case BRICKS_ST_27PT_COEFF: return 11;
     case BRICKS_ST_25PT: return 10;
     case BRICKS_ST_13PT: return 9;
     default: return 7;

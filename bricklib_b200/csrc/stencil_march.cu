@@ -140,7 +140,14 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
         o.curv = (lk.bb == 0) || (it.valid1 != 0);
       }
     }
-    if constexpr (CUBE) {
+    if constexpr (CUBE && R == 1) {
+      if (mode == 1)
+        dev::cube27_step<P, P, 1>(st, lk, prm.c, carry, o, zbase);
+      else if (mode == 0)
+        dev::cube27_step<P, R, 0>(st, lk, prm.c, carry, o, zbase);
+      else
+        dev::cube27_step<P, R, 2>(st, lk, prm.c, carry, o, zbase);
+    } else if constexpr (CUBE) {
       if (mode == 1)
         dev::cube_step<P, P, 1>(st, lk, prm.c, carry, o, zbase);
       else if (mode == 0)
@@ -179,7 +186,7 @@ int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfield
   prm.fields = fields;
   prm.gd0 = plan->gdims[0];
   prm.gd1 = plan->gdims[1];
-  for (int i = 0; i < 10; ++i) prm.c[i] = c[i];
+  for (int i = 0; i < 27; ++i) prm.c[i] = c[i];
   kern<<<dim3(nitems, nfields), 32, smem, s>>>(prm);
   BRK_CUDA(cudaGetLastError());
   ++bricks::g_launches;
@@ -213,7 +220,7 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
     return 0;
   }
   const int R = stencil_id == 13 || stencil_id == 125 ? 2 : (stencil_id == 25 ? 4 : 1);
-  const bool cube = stencil_id == 125;
+  const bool cube = stencil_id == 125 || stencil_id == BRICKS_ST_27PT_COEFF;
   const int HW = R > 2 ? 4 : 2;
   std::vector<FieldDev> host(nfields);
   for (int f = 0; f < nfields; ++f) {
@@ -263,13 +270,21 @@ extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, co
   const FieldDev *fields = nullptr;
   int rc = get_fields(plan, stencil_id, P, nfields, in, out, in_step, out_step, s, &fields);
   if (rc) return rc;
-  double c[10] = {0};
+  double c[27] = {0};
   switch (stencil_id) {
     case BRICKS_ST_7PT_COEFF:
       BRK_ARG(coeff_host);
       for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
       return P == 8 ? launch<1, false, 1, 8>(plan, stencil_id, fields, nfields, c, s)
                     : launch<1, false, 1, 4>(plan, stencil_id, fields, nfields, c, s);
+    case BRICKS_ST_27PT_COEFF: /* d3pt27 (stencils/3axis.cpp:165-247) */
+      BRK_ARG(coeff_host);
+      for (int i = 0; i < 27; ++i) c[i] = coeff_host[i];
+      /* the reference reads term 16 at (k+1, j+1, i), the place of term 25, not at (k, j+1, i) */
+      c[25] += c[16];
+      c[16] = 0.0;
+      return P == 8 ? launch<1, true, 1, 8>(plan, stencil_id, fields, nfields, c, s)
+                    : launch<1, true, 1, 4>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_7PT: /* MPI_ALPHA, MPI_BETA (stencils/fake.h:11-12) */
       c[0] = 0.4, c[1] = 0.1;
       return P == 8 ? launch<1, false, 0, 8>(plan, stencil_id, fields, nfields, c, s)

@@ -51,6 +51,10 @@ int build_points(int id, const double *coeff, int *off, double *cf) {
     if (!coeff) return -1;
     add(0, 0, 0, coeff[0]), add(1, 0, 0, coeff[1]), add(-1, 0, 0, coeff[2]);
     add(0, 1, 0, coeff[3]), add(0, -1, 0, coeff[4]), add(0, 0, 1, coeff[5]), add(0, 0, -1, coeff[6]);
+  } else if (id == BRICKS_ST_27PT_COEFF) {
+    if (!coeff) return -1;
+    /* stencils/3axis.cpp:186-231, including term 16 read at [k+1][j+1][i] as the reference has it */
+    for (int t = 0; t < 27; ++t) add(t % 3 - 1, (t / 3) % 3 - 1, t == 16 ? 1 : t / 9 - 1, coeff[t]);
   } else if (id == BRICKS_ST_7PT) {
     const double a[] = {0.4, 0.1};
     star(1, a);

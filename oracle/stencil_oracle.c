@@ -16,6 +16,10 @@
  *     adjacency slot (dk*3 + dj)*3 + di, element dat[adj[b][slot]*step + k*64 + j*8 + i]
  *     (row-major in-brick order = fold <8> / <4,8>, include/brick.h:235-245)
  *   - array form: stencils/fake.h:41-352 (ST_CPU), stencils/3axis.cpp:32-37
+ *   - d3pt27 (27 runtime coefficients): stencils/3axis.cpp:165-247; no compiled-reference golden
+ *     exists for it (the reference function draws its own random field and prints timings only), so
+ *     this one stencil is PARITY UNPINNED: restated from the source text, checked array form vs
+ *     brick form like the reference's own compareBrick (3axis.cpp:236-237)
  * Terms are summed one at a time, left to right, in the DSL's order of coefficient classes,
  * without fused multiply-add (built with -ffp-contract=off).
  */
@@ -65,7 +69,7 @@ static int cls125(int a, int b, int c) {
   return tab[a][b][c];
 }
 
-/* which: 0 = 7pt.py (coeff_in[0..6]), 7/13/25/125 = mpi*pt.py constants */
+/* which: 0 = 7pt.py (coeff_in[0..6]), 27 = d3pt27 (coeff_in[0..26]), 7/13/25/125 = mpi*pt.py constants */
 int oracle_points(int which, const double *coeff_in, int *off_out, double *c_out) {
   points_t p;
   p.n = 0;
@@ -94,6 +98,16 @@ int oracle_points(int which, const double *coeff_in, int *off_out, double *c_out
         for (int dj = -2; dj <= 2; ++dj)
           for (int di = -2; di <= 2; ++di)
             if (cls125(di, dj, dk) == cl) add_pt(&p, di, dj, dk, C[cl]);
+  } else if (which == 27) {
+    /* d3pt27 (stencils/3axis.cpp:186-200 array form, :209-231 brick form): term t multiplies
+     * in[k + t/9 - 1][j + (t/3)%3 - 1][i + t%3 - 1] by coeff[t] -- except term 16, which BOTH forms
+     * of the reference read at [k+1][j+1][i] instead of [k][j+1][i].  Restated as written. */
+    const double *c = coeff_in;
+    for (int t = 0; t < 27; ++t) {
+      int dk = t / 9 - 1, dj = (t / 3) % 3 - 1, di = t % 3 - 1;
+      if (t == 16) dk = 1;
+      add_pt(&p, di, dj, dk, c[t]);
+    }
   } else {
     return -1;
   }

@@ -5,7 +5,7 @@ Timing: 20 ping-pong sweeps between CUDA events.  Experiment tooling; results ar
 import os, sys, zlib
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 import numpy as np
-from bricklib_b200 import capi
+from bricklib_b200 import capi, synth
 
 
 def main():
@@ -18,20 +18,21 @@ def main():
     d_a, d_b, d_c = ctx.upload(f), ctx.malloc(nb * 4096), ctx.malloc(nb * 4096)
     plan = capi.Plan(ctx, dec.grid, dec.adj)
     for w in which:
+        cf = synth.coefficients()[:27] if w in (0, 27) else None
         ctx.memset(d_b, 0, nb * 4096)
         ctx.memset(d_c, 0, nb * 4096)
-        plan.stencil(w, d_a, d_b)
-        plan.stencil_naive(w, d_a, d_c)
+        plan.stencil(w, d_a, d_b, coeff=cf)
+        plan.stencil_naive(w, d_a, d_c, coeff=cf)
         ctx.sync()
         got = ctx.download(d_b, nb * 512)
         exp = ctx.download(d_c, nb * 512)
         err = float(np.max(np.abs(got - exp) / np.maximum(np.abs(exp), 1e-300)))
         crc = zlib.crc32(got.tobytes())
         for _ in range(2):
-            plan.stencil(w, d_a, d_b); plan.stencil(w, d_b, d_c)
+            plan.stencil(w, d_a, d_b, coeff=cf); plan.stencil(w, d_b, d_c, coeff=cf)
         ctx.timer_start(0)
         for _ in range(10):
-            plan.stencil(w, d_a, d_b); plan.stencil(w, d_b, d_c)
+            plan.stencil(w, d_a, d_b, coeff=cf); plan.stencil(w, d_b, d_c, coeff=cf)
         ctx.timer_stop(0)
         ms = ctx.timer_ms(0) / 20
         print("VCHECK variant=%s maxcol=%s stencil=%d maxrel=%.2e crc=%08x ms=%.4f GB/s=%.0f" % (
