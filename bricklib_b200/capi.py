@@ -13,11 +13,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIBPATH = os.environ.get("BRICKS_LIB") or os.path.join(HERE, "lib", "libbricks_b200.so")
 
 ST_7PT_COEFF, ST_7PT, ST_13PT, ST_25PT, ST_125PT = 0, 7, 13, 25, 125
+ST_COND = 1  # stencils/cond.py (d3cond): 7pt.py's coefficients on max(x, 0), |sum|
 ST_27PT_COEFF = 27  # d3pt27 (stencils/3axis.cpp:165-247): 27 runtime coefficients
 STREAM_COMPUTE, STREAM_COMM, STREAM_H2D, STREAM_D2H = 0, 1, 2, 3
 #: ghost-zone sweeps per exchange, stencils/fake.h:39-344 (ST_ITER) -- GZ / radius
 ST_ITER = {ST_7PT: 8, ST_13PT: 4, ST_25PT: 2, ST_125PT: 4, ST_7PT_COEFF: 8}
-RADIUS = {ST_7PT: 1, ST_13PT: 2, ST_25PT: 4, ST_125PT: 2, ST_7PT_COEFF: 1, ST_27PT_COEFF: 1}
+RADIUS = {ST_7PT: 1, ST_13PT: 2, ST_25PT: 4, ST_125PT: 2, ST_7PT_COEFF: 1, ST_27PT_COEFF: 1, ST_COND: 1}
 
 
 class BricksError(RuntimeError):

@@ -62,7 +62,15 @@ __device__ __forceinline__ void ld_halo(const char *st, int off, bool /*halo*/, 
   }
 }
 
-/* ------------------------------------------------------------------ star stencils */
+template <int N>
+__device__ __forceinline__ void relu(double (&v)[N]) {
+#pragma unroll
+  for (int m = 0; m < N; ++m) v[m] = fmax(v[m], 0.0);
+}
+
+/* ------------------------------------------------------------------ star stencils
+ * VAR 0: one coefficient per distance (mpi*pt.py); 1: 7pt.py's seven coefficients; 2: cond.py, the
+ * same seven on max(x, 0) inputs with |.| on the result (stencils/cond.py:23-30). */
 template <int R, int VAR, int P, int NZ, int MODE>
 __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, P> &lk,
                                           const double *__restrict__ c, double (&carry)[2 * R][4],
@@ -78,9 +86,11 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
   for (int z = 0; z < NZ; ++z) {
     double x[4];
     ld_quad(st, lk.row0[R] + z * lk.rpitch[R], lk.row1[R] + z * lk.rpitch[R], x);
+    if (VAR == 2) relu(x); /* cond.py: every input through max(x, 0) */
     if (MODE == 1) {
       double h[HW], e[4 + 2 * R];
       ld_halo<HW>(st, lk.hrow[R] + z * lk.hpitch[R], lk.halo, h);
+      if (VAR == 2) relu(h);
       gather_i<R, HW>(x, h, lk.halo, lk.bb, lk.srcL, lk.srcR, e);
       double s[4];
 #pragma unroll
@@ -90,6 +100,7 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
         double up[4], dn[4];
         ld_quad(st, lk.row0[R + r] + z * lk.rpitch[R + r], lk.row1[R + r] + z * lk.rpitch[R + r], up);
         ld_quad(st, lk.row0[R - r] + z * lk.rpitch[R - r], lk.row1[R - r] + z * lk.rpitch[R - r], dn);
+        if (VAR == 2) relu(up), relu(dn);
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
           if (VAR) {
@@ -121,7 +132,14 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
             acc[z + R + r][m] = fma(VAR ? c[6] : c[r], x[m], acc[z + R + r][m]);
         }
       }
-    store_done<R, MODE>(o, zbase, z, acc[z]);
+    if (VAR == 2) { /* cond.py: If(calc > 0, calc, -calc) */
+      double v[4];
+#pragma unroll
+      for (int m = 0; m < 4; ++m) v[m] = fabs(acc[z][m]);
+      store_done<R, MODE>(o, zbase, z, v);
+    } else {
+      store_done<R, MODE>(o, zbase, z, acc[z]);
+    }
   }
 #pragma unroll
   for (int a = 0; a < 2 * R; ++a)

@@ -277,6 +277,11 @@ extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, co
       for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
       return P == 8 ? launch<1, false, 1, 8>(plan, stencil_id, fields, nfields, c, s)
                     : launch<1, false, 1, 4>(plan, stencil_id, fields, nfields, c, s);
+    case BRICKS_ST_COND: /* cond.py (d3cond, stencils/3axis.cpp:94-163): coeff[0..6] as 7pt.py */
+      BRK_ARG(coeff_host);
+      for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
+      return P == 8 ? launch<1, false, 2, 8>(plan, stencil_id, fields, nfields, c, s)
+                    : launch<1, false, 2, 4>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_27PT_COEFF: /* d3pt27 (stencils/3axis.cpp:165-247) */
       BRK_ARG(coeff_host);
       for (int i = 0; i < 27; ++i) c[i] = coeff_host[i];

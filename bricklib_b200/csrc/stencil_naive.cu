@@ -14,6 +14,7 @@ struct NaiveParams {
   double *out;
   unsigned long long in_step, out_step;
   int npts;
+  int cond; /* cond.py: max(in, 0) per term, |sum| */
 };
 
 __constant__ int c_off[125 * 3];
@@ -27,10 +28,11 @@ __global__ void __launch_bounds__(512) naive_kernel(NaiveParams p) {
   for (int t = 0; t < p.npts; ++t) {
     const int ii = i + c_off[3 * t] + 8, jj = j + c_off[3 * t + 1] + 8, kk = k + c_off[3 * t + 2] + 8;
     const unsigned nb = row[((kk >> 3) * 3 + (jj >> 3)) * 3 + (ii >> 3)];
-    const double v = p.in[(size_t)nb * p.in_step + (kk & 7) * 64 + (jj & 7) * 8 + (ii & 7)];
+    double v = p.in[(size_t)nb * p.in_step + (kk & 7) * 64 + (jj & 7) * 8 + (ii & 7)];
+    if (p.cond) v = fmax(v, 0.0);
     acc = t ? acc + c_coef[t] * v : c_coef[t] * v;
   }
-  p.out[(size_t)b * p.out_step + threadIdx.x] = acc;
+  p.out[(size_t)b * p.out_step + threadIdx.x] = p.cond ? fabs(acc) : acc;
 }
 
 int build_points(int id, const double *coeff, int *off, double *cf) {
@@ -47,7 +49,7 @@ int build_points(int id, const double *coeff, int *off, double *cf) {
       add(0, 0, r, a[r]), add(0, 0, -r, a[r]);
     }
   };
-  if (id == BRICKS_ST_7PT_COEFF) {
+  if (id == BRICKS_ST_7PT_COEFF || id == BRICKS_ST_COND) {
     if (!coeff) return -1;
     add(0, 0, 0, coeff[0]), add(1, 0, 0, coeff[1]), add(-1, 0, 0, coeff[2]);
     add(0, 1, 0, coeff[3]), add(0, -1, 0, coeff[4]), add(0, 0, 1, coeff[5]), add(0, 0, -1, coeff[6]);
@@ -105,6 +107,7 @@ extern "C" int bricks_stencil_naive(bricks_plan *plan, int stencil_id, int nfiel
     p.in_step = in_step;
     p.out_step = out_step;
     p.npts = n;
+    p.cond = stencil_id == BRICKS_ST_COND;
     naive_kernel<<<(unsigned)plan->nlist, 512, 0, s>>>(p);
     BRK_CUDA(cudaGetLastError());
     ++bricks::g_launches;

@@ -9,6 +9,7 @@
 //   single [-d N] [-S 7|13|25|125|0 (0 = all)] [-I launches per timing]
 #include <unistd.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <iostream>
@@ -55,12 +56,12 @@ int main(int argc, char **argv) {
       case 'S': which = std::stoi(optarg); break;
       case 'I': reps = std::stoi(optarg); break;
       default:
-        printf("usage: %s [-d N] [-S 0|7|13|25|27|125] [-I reps]\n", argv[0]);
+        printf("usage: %s [-d N] [-S 0|1|7|13|25|27|125] [-I reps]\n", argv[0]);
         return c == 'h' ? 0 : 1;
     }
   }
-  if (N % TILE || N < 2 * TILE || (which && which != 27 && !drv::stencil_known(which))) {
-    printf("N must be a multiple of %ld (>= %ld); stencil one of 7, 13, 25, 27, 125\n", TILE, 2 * TILE);
+  if (N % TILE || N < 2 * TILE || (which && which != 1 && which != 27 && !drv::stencil_known(which))) {
+    printf("N must be a multiple of %ld (>= %ld); stencil one of 1 (cond), 7, 13, 25, 27, 125\n", TILE, 2 * TILE);
     return 1;
   }
   for (int i = 0; i < 129; ++i) coeff[i] = bricks_detail::uniform01(42 ^ 0x5EED, i);
@@ -123,6 +124,38 @@ int main(int argc, char **argv) {
       check("d3pt7", back, out_ptr);
     }
 
+    if (which == 0 || which == 1) {
+      // ---- the reference's d3cond / d3condcu test (stencils/3axis.cpp:94-163, cond.py): max(in, 0) per
+      // term, |sum| as the result; on the reference's U[0,1) field and coefficients both are no-ops
+      auto arr_func = [&]() {
+        const long s1 = STRIDE, s2 = STRIDE * STRIDE, o = GZ + PADDING;
+#pragma omp parallel for collapse(2)
+        for (long k = o; k < o + N; ++k)
+          for (long j = o; j < o + N; ++j) {
+            const bElem *a = in_ptr + k * s2 + j * s1;
+            bElem *r = out_ptr + k * s2 + j * s1;
+#pragma omp simd
+            for (long i = o; i < o + N; ++i) {
+              const bElem partial = coeff[5] * std::max(a[i + s2], 0.0) + coeff[6] * std::max(a[i - s2], 0.0) +
+                                    coeff[3] * std::max(a[i + s1], 0.0) + coeff[4] * std::max(a[i - s1], 0.0) +
+                                    coeff[1] * std::max(a[i + 1], 0.0) + coeff[2] * std::max(a[i - 1], 0.0) +
+                                    coeff[0] * std::max(a[i], 0.0);
+              r[i] = partial > 0 ? partial : -partial;
+            }
+          }
+      };
+      auto brick_func = [&]() { plan.run(BRICKS_ST_COND, bIn_dev, bOut_dev, coeff); };
+      std::cout << "cond" << std::endl;
+      const double t_arr = time_host(arr_func, 3);
+      std::cout << "Arr: " << t_arr << std::endl;
+      const double t_bri = cutime_func(rk.ctx, brick_func, reps);
+      std::cout << "Bri: " << t_bri << std::endl;
+      std::cout << "  | Arr (host OpenMP) " << pts / t_arr * 1e-9 << " GStencil/s, Bri (B200) " << pts / t_bri * 1e-9
+                << " GStencil/s, " << 16.0 * pts / t_bri * 1e-9 << " GB/s" << std::endl;
+      BrickStorage back = movBrickStorage(bStorage_dev, gpuMemcpyDeviceToHost);
+      check("cond", back, out_ptr);
+    }
+
     if (which == 0 || which == 27) {
       // ---- the reference's d3pt27 test (stencils/3axis.cpp:165-247): 27 coefficients; term 16 is read
       // at [k+1][j+1][i] in both of its forms, and so it is here
@@ -155,7 +188,7 @@ int main(int argc, char **argv) {
 
     // ---- fixed-coefficient stencils of the MPI drivers on the same grid, vs the naive kernel
     for (int w : {7, 13, 25, 125}) {
-      if (which && which != w) continue;  // -S 27 runs d3pt27 only
+      if (which && which != w) continue;  // -S 1 / -S 27 run cond / d3pt27 only
       BrickStorage twin = movBrickStorage(bStorage, gpuMemcpyHostToDevice);
       const double *i2[1] = {twin.dat.get()};
       double *o2[1] = {twin.dat.get() + bSize};

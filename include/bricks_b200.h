@@ -39,6 +39,8 @@ typedef struct bricks_exchange bricks_exchange; /* a halo-exchange plan */
  * mpi125pt.py with the constants of stencils/fake.h:11-33. */
 enum {
   BRICKS_ST_7PT_COEFF = 0,
+  BRICKS_ST_COND = 1, /* stencils/cond.py:23-30 (d3cond / d3condcu): 7pt.py's point set and coeff[0..6] on
+                         max(in, 0), result |sum| */
   BRICKS_ST_27PT_COEFF = 27, /* d3pt27, stencils/3axis.cpp:165-247: 27 runtime coefficients coeff[0..26],
                                 term t at (k + t/9 - 1, j + (t/3)%3 - 1, i + t%3 - 1) except term 16, which
                                 the reference reads at (k+1, j+1, i); reproduced as written */
@@ -100,7 +102,7 @@ int bricks_plan_device_tables(const bricks_plan *plan, const unsigned **adj_dev,
  * storage pairs that share the plan's grid/adjacency (strong scaling: one pair per
  * subdomain).  in/out are DEVICE field pointers (already offset to the field inside an
  * interleaved storage); steps in elements.  coeff_host: BRICKS_ST_7PT_COEFF reads 7 doubles,
- * BRICKS_ST_27PT_COEFF 27, others ignore it.  Asynchronous on `stream`. */
+ * BRICKS_ST_COND reads 7 too, BRICKS_ST_27PT_COEFF 27, others ignore it.  Asynchronous on `stream`. */
 int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, const double *const *in,
                    double *const *out, size_t in_step, size_t out_step, const double *coeff_host,
                    int stream);

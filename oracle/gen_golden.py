@@ -5,7 +5,7 @@ oracle/Makefile (BrickDecomp::initialize / populate of include/brick-mpi.h, the 
 brick kernels of stencils/*.py and the ST_CPU array forms of stencils/fake.h).  Run it in
 the build container, where /root/reference exists:
 
-    make -C oracle all && python oracle/gen_golden.py
+    make -C oracle all && python oracle/gen_golden.py && python oracle/gen_golden.py cond
 
 The fixtures pin the oracle (tests/test_oracle_golden.py) and, through it, the CUDA path.
 Inputs are not stored: they are a pure function of the element index
@@ -88,8 +88,42 @@ def stencil_fixture(dims):
     return out
 
 
+def cond_inputs(nelem):
+    """Field and coefficients with both signs, so that max(x, 0) and |sum| of cond.py matter."""
+    return synth.uniform(nelem, seed=13) - 0.5, synth.coefficients()[:7] - 0.5
+
+
+def cond_fixture(dims):
+    """cond.py (d3cond, stencils/3axis.cpp:94-163) through the reference's codegen brick kernel and
+    its array form, on a decomposed subdomain; same layout as stencil_fixture."""
+    ref = R.RefDecomp(dims, 8)
+    nb = ref.nbricks
+    inp, coeff = cond_inputs(nb * 512)
+    t = ref.grid.shape
+    interior = ref.grid[1:-1, 1:-1, 1:-1].reshape(-1)
+    arr = np.zeros((t[0] * 8, t[1] * 8, t[2] * 8))
+    field = inp.reshape(nb, 8, 8, 8)
+    for bk in range(t[0]):
+        for bj in range(t[1]):
+            for bi in range(t[2]):
+                arr[bk * 8:bk * 8 + 8, bj * 8:bj * 8 + 8, bi * 8:bi * 8 + 8] = field[ref.grid[bk, bj, bi]]
+    res = np.zeros(nb * 512)
+    R.brick_sweep_rm(1, ref.adj, ref.grid.reshape(-1), inp, res, 512, coeff)
+    aout = np.zeros_like(arr)
+    R.array_sweep(1, arr, aout, (8, arr.shape[0] - 8, 8, arr.shape[1] - 8, 8, arr.shape[2] - 8), coeff)
+    out = {"dims": np.array(dims), "interior_bricks": interior.astype(np.uint32),
+           "brick_1": res.reshape(nb, 512)[interior].copy(), "array_1": aout[8:-8, 8:-8, 8:-8].copy()}
+    ref.close()
+    return out
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if "cond" in sys.argv[1:]:  # only the cond.py fixtures (added after the others were frozen)
+        for d in STENCIL_DIMS:
+            np.savez(os.path.join(GOLDEN, "cond_%dx%dx%d.npz" % d), **cond_fixture(d))
+            print("cond_%dx%dx%d.npz" % d)
+        return
     recs = [decomp_record(d) for d in DECOMP_DIMS]
     meta = {"generator": "oracle/gen_golden.py", "source": "oracle/_ref/libref_%s.so" % R.host_isa(),
             "vsvec": R.vsvec(), "decomp": recs}

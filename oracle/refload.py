@@ -20,7 +20,7 @@ _u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
 _i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
 _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
 
-STENCILS = (0, 7, 13, 25, 125)  # 0 = stencils/7pt.py with coeff[]; others = mpi<N>pt.py
+STENCILS = (0, 1, 7, 13, 25, 125)  # 0 = stencils/7pt.py with coeff[], 1 = cond.py (same coeff[]); others = mpi<N>pt.py
 
 
 def host_isa():

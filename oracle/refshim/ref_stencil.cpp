@@ -8,10 +8,12 @@
  * (7-pt-with-coefficients: stencils/3axis.cpp:32-37).  oracle/Makefile runs the
  * reference code generator on this file and compiles it once per stencil
  * (-DREF_WHICH=7|13|25|125 for the MPI_* constant-coefficient stencils,
- * -DREF_WHICH=0 for stencils/7pt.py with the runtime `coeff[]` array) into
+ * -DREF_WHICH=0 for stencils/7pt.py with the runtime `coeff[]` array, -DREF_WHICH=1 for
+ * stencils/cond.py, the max/abs stencil of d3cond, stencils/3axis.cpp:94-163) into
  * oracle/_ref/.  Used by tests, oracle/gen_golden.py and bench.py's CPU baseline.
  */
 #include <omp.h>
+#include <algorithm>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -36,8 +38,11 @@ typedef Brick<Dim<REF_BDIM>, Dim<VFOLD>> Brick3D;
 #define REF_CAT(a, b) REF_CAT2(a, b)
 #define REFSYM(name) REF_CAT(REF_CAT(ref, REF_WHICH), _##name)
 
-#if REF_WHICH == 0
-bElem *coeff = nullptr; /* the free identifier stencils/7pt.py names */
+#if REF_WHICH == 0 || REF_WHICH == 1
+static bElem *coeff = nullptr; /* the free identifier stencils/7pt.py and cond.py name (one per translation unit) */
+#endif
+#if REF_WHICH == 1
+using std::max; /* cond.py calls max(); stencils/3axis.cpp:12 */
 #endif
 
 namespace {
@@ -80,7 +85,7 @@ void fold_table(unsigned *tab) {
 extern "C" {
 
 int REFSYM(st_iter)() {
-#if REF_WHICH == 0
+#if REF_WHICH == 0 || REF_WHICH == 1
   return 1;
 #else
   return ST_ITER;
@@ -97,7 +102,7 @@ void REFSYM(brick_sweep)(const unsigned *adj, unsigned nbricks, const unsigned *
                          double *in_dat, double *out_dat, long step, const double *coeff_in) {
   InfoView iv(adj, nbricks);
   BrickStorage sin = wrap(in_dat, nbricks, step), sout = wrap(out_dat, nbricks, step);
-#if REF_WHICH == 0
+#if REF_WHICH == 0 || REF_WHICH == 1
   coeff = const_cast<double *>(coeff_in);
   Brick3D bIn(&iv.info, sin, 0), bOut(&iv.info, sout, 0);
 #else
@@ -166,7 +171,7 @@ void REFSYM(array_sweep)(const double *in_ptr, double *out_ptr, long s0, long s1
   (void)s2;
   auto arrIn = (const bElem(*)[s1][s0])in_ptr;
   auto arrOut = (bElem(*)[s1][s0])out_ptr;
-#if REF_WHICH == 0
+#if REF_WHICH == 0 || REF_WHICH == 1
   const double *c = coeff_in;
 #else
   (void)coeff_in;
@@ -176,7 +181,16 @@ void REFSYM(array_sweep)(const double *in_ptr, double *out_ptr, long s0, long s1
     for (long j = j0; j < j1; ++j)
 #pragma omp simd
       for (long i = i0; i < i1; ++i)
-#if REF_WHICH == 0
+#if REF_WHICH == 1
+      {
+        /* d3cond's array form, stencils/3axis.cpp:112-121: k+1, k-1, j+1, j-1, i+1, i-1, centre */
+        const bElem partial = c[5] * max(arrIn[k + 1][j][i], 0.0) + c[6] * max(arrIn[k - 1][j][i], 0.0) +
+                              c[3] * max(arrIn[k][j + 1][i], 0.0) + c[4] * max(arrIn[k][j - 1][i], 0.0) +
+                              c[1] * max(arrIn[k][j][i + 1], 0.0) + c[2] * max(arrIn[k][j][i - 1], 0.0) +
+                              c[0] * max(arrIn[k][j][i], 0.0);
+        arrOut[k][j][i] = partial > 0 ? partial : -partial;
+      }
+#elif REF_WHICH == 0
         /* stencils/7pt.py:19-26 term order: centre, i+1, i-1, j+1, j-1, k+1, k-1 */
         arrOut[k][j][i] = c[0] * arrIn[k][j][i] + c[1] * arrIn[k][j][i + 1] +
                           c[2] * arrIn[k][j][i - 1] + c[3] * arrIn[k][j + 1][i] +

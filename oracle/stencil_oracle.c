@@ -69,11 +69,11 @@ static int cls125(int a, int b, int c) {
   return tab[a][b][c];
 }
 
-/* which: 0 = 7pt.py (coeff_in[0..6]), 27 = d3pt27 (coeff_in[0..26]), 7/13/25/125 = mpi*pt.py constants */
+/* which: 0 = 7pt.py (coeff_in[0..6]), 1 = cond.py (same, max/abs), 27 = d3pt27 (coeff_in[0..26]), 7/13/25/125 = mpi*pt.py constants */
 int oracle_points(int which, const double *coeff_in, int *off_out, double *c_out) {
   points_t p;
   p.n = 0;
-  if (which == 0) {
+  if (which == 0 || which == 1) { /* 1 = cond.py: same point set, see oracle_is_cond */
     const double *c = coeff_in;
     add_pt(&p, 0, 0, 0, c[0]);
     add_pt(&p, 1, 0, 0, c[1]);
@@ -122,6 +122,12 @@ int oracle_points(int which, const double *coeff_in, int *off_out, double *c_out
   return p.n;
 }
 
+/* stencils/cond.py:23-30 (d3cond, stencils/3axis.cpp:94-163): every input goes through max(x, 0)
+ * and the sum through If(calc > 0, calc, -calc) */
+static inline int oracle_is_cond(int which) { return which == 1; }
+static inline double cond_in(int cond, double v) { return cond && !(v > 0.0) ? 0.0 : v; }
+static inline double cond_out(int cond, double v) { return cond && !(v > 0.0) ? -v : v; }
+
 static inline double brick_at(const unsigned *adj, const double *dat, long step, unsigned b, int k,
                               int j, int i) {
   int dk = (k + 8) / 8, dj = (j + 8) / 8, di = (i + 8) / 8;
@@ -139,17 +145,18 @@ int oracle_brick_sweep(int which, const unsigned *adj, const unsigned *blist, lo
   static double c[MAXPTS];
   int np = oracle_points(which, coeff_in, off, c);
   if (np < 0) return -1;
+  const int cond = oracle_is_cond(which);
 #pragma omp parallel for schedule(static)
   for (long n = 0; n < nlist; ++n) {
     unsigned b = blist[n];
     for (int k = 0; k < 8; ++k)
       for (int j = 0; j < 8; ++j)
         for (int i = 0; i < 8; ++i) {
-          double acc = c[0] * brick_at(adj, in, in_step, b, k + off[2], j + off[1], i + off[0]);
+          double acc = c[0] * cond_in(cond, brick_at(adj, in, in_step, b, k + off[2], j + off[1], i + off[0]));
           for (int t = 1; t < np; ++t)
-            acc = acc + c[t] * brick_at(adj, in, in_step, b, k + off[3 * t + 2], j + off[3 * t + 1],
-                                        i + off[3 * t + 0]);
-          out[(size_t)b * out_step + k * 64 + j * 8 + i] = acc;
+            acc = acc + c[t] * cond_in(cond, brick_at(adj, in, in_step, b, k + off[3 * t + 2], j + off[3 * t + 1],
+                                                      i + off[3 * t + 0]));
+          out[(size_t)b * out_step + k * 64 + j * 8 + i] = cond_out(cond, acc);
         }
   }
   return 0;
@@ -163,16 +170,17 @@ int oracle_array_sweep(int which, const double *in, double *out, long s0, long s
   (void)s2;
   int np = oracle_points(which, coeff_in, off, c);
   if (np < 0) return -1;
+  const int cond = oracle_is_cond(which);
 #pragma omp parallel for schedule(static)
   for (long k = k0; k < k1; ++k)
     for (long j = j0; j < j1; ++j)
       for (long i = i0; i < i1; ++i) {
         double acc = 0.0;
         for (int t = 0; t < np; ++t) {
-          double v = in[((k + off[3 * t + 2]) * s1 + (j + off[3 * t + 1])) * s0 + i + off[3 * t]];
+          double v = cond_in(cond, in[((k + off[3 * t + 2]) * s1 + (j + off[3 * t + 1])) * s0 + i + off[3 * t]]);
           acc = t ? acc + c[t] * v : c[t] * v;
         }
-        out[(k * s1 + j) * s0 + i] = acc;
+        out[(k * s1 + j) * s0 + i] = cond_out(cond, acc);
       }
   return 0;
 }

@@ -53,7 +53,7 @@ def _perf(out):
 def test_single_driver_validates(drivers):
     rc, out = _run(os.path.join(drivers, "single"), "-d", "64", "-I", "3")
     assert rc == 0, out
-    assert "d3pt7" in out and "d3pt27" in out and "Arr: " in out and "Bri: " in out and "mismatch" not in out
+    assert "d3pt7" in out and "cond" in out and "d3pt27" in out and "Arr: " in out and "Bri: " in out and "mismatch" not in out
     for w in (7, 13, 25, 125):
         assert "mpi%dpt" % w in out
 

@@ -18,7 +18,7 @@ def main():
     d_a, d_b, d_c = ctx.upload(f), ctx.malloc(nb * 4096), ctx.malloc(nb * 4096)
     plan = capi.Plan(ctx, dec.grid, dec.adj)
     for w in which:
-        cf = synth.coefficients()[:27] if w in (0, 27) else None
+        cf = synth.coefficients()[:27] if w in (0, 1, 27) else None
         ctx.memset(d_b, 0, nb * 4096)
         ctx.memset(d_c, 0, nb * 4096)
         plan.stencil(w, d_a, d_b, coeff=cf)
