@@ -61,6 +61,7 @@ _SIGS = {
     "bricks_links_upload": (C.c_int, [_vp, _vp, C.c_int, _vpp]),
     "bricks_copy_regions": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
     "bricks_copy_array": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_int]),
+    "bricks_array_stencil7": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "bricks_comm_unique_id": (C.c_int, [_vp]),
     "bricks_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
     "bricks_comm_destroy": (C.c_int, [_vp]),
@@ -469,6 +470,13 @@ def copy_array_dev(ctx, to_brick, dimlist, padding, ghost, arr_dev, grid_dev, br
     d, p, g = (np.ascontiguousarray(x, np.int64) for x in (dimlist, padding, ghost))
     check(lib().bricks_copy_array(ctx._h, 1 if to_brick else 0, _np_ptr(d), _np_ptr(p), _np_ptr(g), arr_dev,
                                   grid_dev, bricks_dev, step, stream))
+
+
+def array_stencil7(ctx, in_dev, out_dev, ext, lo, hi, coeff, stream=STREAM_COMPUTE):
+    """Array-layout 7-point baseline on the device (d3pt7_arr of stencils/3axis.cu:39-49)."""
+    e, l, h = (np.ascontiguousarray(x, np.int64) for x in (ext, lo, hi))
+    c = np.ascontiguousarray(coeff, np.float64)
+    check(lib().bricks_array_stencil7(ctx._h, in_dev, out_dev, _np_ptr(e), _np_ptr(l), _np_ptr(h), _np_ptr(c), stream))
 
 
 def compare_brick(dimlist, padding, ghost, arr, grid, bdat, adj, step=512):

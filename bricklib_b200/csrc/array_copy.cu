@@ -101,3 +101,71 @@ extern "C" int bricks_copy_array(bricks_ctx *ctx, int to_brick, const long dimli
   ++bricks::g_launches;
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+//   bricks_array_stencil7   the array-layout baseline of the reference's single-GPU driver:
+//                           d3pt7_arr / d3pt7_arr_warp (stencils/3axis.cu:39-60), the 7-point stencil
+//                           with seven coefficients on a conventional padded array, for an on-box
+//                           brick-vs-array comparison.  NOT the product path; it exists so that the
+//                           "Arr" line of d3pt7cu has a B200 counterpart.
+// A block owns a 32 (i) x 8 (j) column and marches it along k: the k-1 / k / k+1 values of a thread's
+// point stay in registers, so every element is fetched from global memory once as a centre and is an
+// L1 hit for its four in-plane neighbours.
+namespace {
+
+struct Array7Params {
+  const double *in;
+  double *out;
+  long s1, s2;          /* strides of j and k in elements */
+  long lo[3], n[3];     /* box origin and extent, i first */
+  double c[7];
+  int kchunk;
+};
+
+__global__ void __launch_bounds__(256) array7_kernel(const Array7Params p) {
+  const long i = (long)blockIdx.x * 32 + threadIdx.x, j = (long)blockIdx.y * 8 + threadIdx.y;
+  if (i >= p.n[0] || j >= p.n[1]) return;
+  const long k0 = (long)blockIdx.z * p.kchunk;
+  const long k1 = k0 + p.kchunk < p.n[2] ? k0 + p.kchunk : p.n[2];
+  const double *a = p.in + (p.lo[2] + k0) * p.s2 + (p.lo[1] + j) * p.s1 + p.lo[0] + i;
+  double *o = p.out + (p.lo[2] + k0) * p.s2 + (p.lo[1] + j) * p.s1 + p.lo[0] + i;
+  double below = a[-p.s2], here = a[0];
+  for (long k = k0; k < k1; ++k) {
+    const double above = a[p.s2];
+    /* term order of the reference: k+1, k-1, j+1, j-1, i+1, i-1, centre (3axis.cu:44-47) */
+    const double r = p.c[5] * above + p.c[6] * below + p.c[3] * a[p.s1] + p.c[4] * a[-p.s1] + p.c[1] * a[1] +
+                     p.c[2] * a[-1] + p.c[0] * here;
+    __stcs(o, r);
+    below = here;
+    here = above;
+    a += p.s2;
+    o += p.s2;
+  }
+}
+
+}  // namespace
+
+extern "C" int bricks_array_stencil7(bricks_ctx *ctx, const double *in_dev, double *out_dev, const long ext[3],
+                                     const long lo[3], const long hi[3], const double *coeff_host, int stream) {
+  BRK_ARG(ctx && in_dev && out_dev && ext && lo && hi && coeff_host && in_dev != out_dev);
+  BRK_ARG(stream >= 0 && stream < bricks::kNumStreams);
+  Array7Params p;
+  for (int d = 0; d < 3; ++d) {
+    BRK_ARG(lo[d] >= 1 && hi[d] > lo[d] && hi[d] <= ext[d] - 1); /* one element of halo inside the array */
+    p.lo[d] = lo[d];
+    p.n[d] = hi[d] - lo[d];
+  }
+  p.in = in_dev;
+  p.out = out_dev;
+  p.s1 = ext[0];
+  p.s2 = ext[0] * ext[1];
+  for (int t = 0; t < 7; ++t) p.c[t] = coeff_host[t];
+  p.kchunk = 32;
+  BRK_ARG((p.n[1] + 7) / 8 < 65536 && (p.n[2] + p.kchunk - 1) / p.kchunk < 65536);
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  const dim3 grid((unsigned)((p.n[0] + 31) / 32), (unsigned)((p.n[1] + 7) / 8), (unsigned)((p.n[2] + p.kchunk - 1) / p.kchunk));
+  array7_kernel<<<grid, dim3(32, 8), 0, ctx->streams[stream]>>>(p);
+  BRK_CUDA(cudaGetLastError());
+  ++bricks::g_launches;
+  return 0;
+}

@@ -122,6 +122,32 @@ int main(int argc, char **argv) {
                 << " GStencil/s, " << 16.0 * pts / t_bri * 1e-9 << " GB/s" << std::endl;
       BrickStorage back = movBrickStorage(bStorage_dev, gpuMemcpyDeviceToHost);
       check("d3pt7", back, out_ptr);
+      // ---- the array layout on the device: the "Arr" line of d3pt7cu (stencils/3axis.cu:39-60,173-174),
+      // compared with the host array result element by element
+      {
+        const size_t abytes = (size_t)STRIDE * STRIDE * STRIDE * sizeof(bElem);
+        bElem *ain_dev = nullptr, *aout_dev = nullptr;
+        gpuCheck(gpuMalloc(&ain_dev, abytes));
+        gpuCheck(gpuMalloc(&aout_dev, abytes));
+        gpuCheck(gpuMemcpy(ain_dev, in_ptr, abytes, gpuMemcpyHostToDevice));
+        gpuCheck(bricks_memset(rk.ctx, aout_dev, 0, abytes));
+        const long ext[3] = {STRIDE, STRIDE, STRIDE}, o = GZ + PADDING, lo[3] = {o, o, o}, hi[3] = {o + N, o + N, o + N};
+        auto cuarr_func = [&]() {
+          gpuCheck(bricks_array_stencil7(rk.ctx, ain_dev, aout_dev, ext, lo, hi, coeff, BRICKS_STREAM_COMPUTE));
+        };
+        const double t_cuarr = cutime_func(rk.ctx, cuarr_func, reps);
+        std::cout << "Arr (B200): " << t_cuarr << std::endl;
+        std::cout << "  | " << pts / t_cuarr * 1e-9 << " GStencil/s, " << 16.0 * pts / t_cuarr * 1e-9
+                  << " GB/s; brick layout / array layout = " << t_cuarr / t_bri << "x" << std::endl;
+        std::vector<bElem> got((size_t)STRIDE * STRIDE * STRIDE);
+        gpuCheck(gpuMemcpy(got.data(), aout_dev, abytes, gpuMemcpyDeviceToHost));
+        if (!compareArray({STRIDE, STRIDE, STRIDE}, got.data(), out_ptr)) {  // both are zero outside the box
+          std::cout << "d3pt7 array kernel: result mismatch!" << std::endl;
+          ++failures;
+        }
+        gpuCheck(gpuFree(ain_dev));
+        gpuCheck(gpuFree(aout_dev));
+      }
     }
 
     if (which == 0 || which == 1) {

@@ -135,6 +135,14 @@ int bricks_copy_array(bricks_ctx *ctx, int to_brick, const long dimlist[3], cons
                       const long ghost[3], double *arr_dev, const unsigned *grid_dev,
                       double *bricks_dev, size_t step, int stream);
 
+/* ---- array-layout baseline (NOT the product path): the 7-point stencil with seven coefficients on a
+ * conventional padded device array, the counterpart of d3pt7_arr / d3pt7_arr_warp
+ * (stencils/3axis.cu:39-60) for an on-box brick-vs-array comparison.  ext = array extents in elements
+ * (i first), [lo, hi) the box of points to compute (at least one element inside the array on every
+ * side); coeff_host[0..6] = centre, i+1, i-1, j+1, j-1, k+1, k-1.  Asynchronous on `stream`. */
+int bricks_array_stencil7(bricks_ctx *ctx, const double *in_dev, double *out_dev, const long ext[3],
+                          const long lo[3], const long hi[3], const double *coeff_host, int stream);
+
 /* ---- halo exchange: replaces BrickDecomp::exchange(BrickStorage&) (brick-mpi.h:466-495),
  * ExchangeView::exchange (brick-mpi.h:96-123) and the D2H / MPI / H2D staging of
  * weak/main.cu:251-275.  Region i: receive nbytes[i] at recv_off[i] of the storage from

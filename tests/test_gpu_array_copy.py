@@ -75,3 +75,22 @@ def test_full_size_round_trip(ctx, built):
     for p in (d_arr, d_back, d_br):
         ctx.free(p)
     plan.close()
+
+
+def test_array_layout_baseline_kernel(ctx, built, oracle):
+    """bricks_array_stencil7, the device counterpart of d3pt7_arr (stencils/3axis.cu:39-49), against the
+    oracle's array form of 7pt.py on a padded array; ragged box sizes, points outside the box untouched."""
+    from bricklib_b200 import synth
+    from conftest import REL_TOL, relerr
+    coeff = synth.coefficients()[:7]
+    for ext, lo, hi in [((40, 24, 48), (8, 8, 8), (32, 16, 40)), ((50, 21, 37), (1, 2, 3), (49, 20, 36))]:
+        arr = synth.uniform(ext[0] * ext[1] * ext[2], seed=6).reshape(ext[2], ext[1], ext[0])
+        d_in, d_out = ctx.upload(arr), ctx.upload(np.full(arr.size, -2.0))
+        built.array_stencil7(ctx, d_in, d_out, ext, lo, hi, coeff)
+        ctx.sync()
+        got = ctx.download(d_out, arr.size).reshape(arr.shape)
+        exp = np.full(arr.shape, -2.0)
+        oracle.array_sweep(0, arr, exp, (lo[2], hi[2], lo[1], hi[1], lo[0], hi[0]), coeff)
+        assert relerr(got, exp) <= REL_TOL
+        ctx.free(d_in)
+        ctx.free(d_out)
