@@ -17,6 +17,9 @@
 /* Register caps.  The register file is 4 x 16 Ki, one quarter per scheduler, so a one-warp CTA fits
  * floor(16384 / (32 * regs)) times per scheduler: <= 128 registers -> 16 warps per SM, <= 168 ->
  * 12, more -> 8 (ncu launch__occupancy_limit_registers).  7-point: 128; 13-point and cube: 168. */
+#ifndef MARCH_STAR4_REGS /* 25-point star: 216-230 registers as compiled, 8 warps per SM */
+#define MARCH_STAR4_REGS 255
+#endif
 #ifndef MARCH_CUBE_REGS
 #define MARCH_CUBE_REGS 168
 #endif
@@ -26,7 +29,7 @@ namespace {
 
 template <int R, bool CUBE, int VAR, int P>
 /* register cap for the cube: measured best on B200 (profiles/r01_maxnreg_sweep.txt) */
-__global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R == 1 ? 128 : (R == 2 ? 168 : 255))) march_kernel(const __grid_constant__ MarchParams prm) {
+__global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R == 1 ? 128 : (R == 2 ? 168 : MARCH_STAR4_REGS))) march_kernel(const __grid_constant__ MarchParams prm) {
   using L = dev::StageLayout<R, CUBE, P>;
   constexpr int H = 8 / P;
   extern __shared__ __align__(1024) char smem[];
