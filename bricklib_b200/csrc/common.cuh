@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <nccl.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -16,7 +17,7 @@
 namespace bricks {
 
 void set_error(const char *fmt, ...);
-extern unsigned long long g_launches;
+extern std::atomic<unsigned long long> g_launches; /* host threads drive one device each */
 
 #define BRK_CUDA(expr)                                                                  \
   do {                                                                                  \

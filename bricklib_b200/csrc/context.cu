@@ -5,7 +5,7 @@
 
 namespace bricks {
 static thread_local char g_err[1024] = "";
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 
 void set_error(const char *fmt, ...) {
   va_list ap;
@@ -181,7 +181,7 @@ int bricks_timer_elapsed_ms(bricks_ctx *c, int slot, float *ms) {
 
 int bricks_launch_count(unsigned long long *count) {
   BRK_ARG(count);
-  *count = g_launches;
+  *count = g_launches.load();
   return 0;
 }
 

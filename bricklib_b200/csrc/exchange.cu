@@ -8,6 +8,7 @@
 //                        by construction of the layout, so nothing is packed); regions whose
 //                        peer is this rank become on-device copies.
 #include <cstring>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -83,6 +84,24 @@ int upload_links(bricks_ctx *ctx, const bricks_region_link *host, int n, void **
 /* The device blob returned by bricks_links_upload carries its own chunk table after the links;
  * the count of chunks is kept host side, keyed by the blob pointer. */
 static std::map<const void *, std::pair<int, unsigned>> g_link_meta;
+static std::mutex g_link_mutex; /* one host thread per device may be inside the library at once */
+
+static void meta_put(const void *blob, int n, unsigned nchunks) {
+  std::lock_guard<std::mutex> lock(g_link_mutex);
+  g_link_meta[blob] = std::make_pair(n, nchunks);
+}
+static bool meta_get(const void *blob, int *n, unsigned *nchunks) {
+  std::lock_guard<std::mutex> lock(g_link_mutex);
+  auto it = g_link_meta.find(blob);
+  if (it == g_link_meta.end()) return false;
+  *n = it->second.first;
+  *nchunks = it->second.second;
+  return true;
+}
+static void meta_erase(const void *blob) {
+  std::lock_guard<std::mutex> lock(g_link_mutex);
+  g_link_meta.erase(blob);
+}
 
 extern "C" {
 
@@ -97,19 +116,20 @@ int bricks_links_upload(bricks_ctx *ctx, const bricks_region_link *links_host, i
   unsigned nchunks = 0;
   int rc = upload_links(ctx, links_host, n, &blob, &nchunks);
   if (rc) return rc;
-  g_link_meta[blob] = std::make_pair(n, nchunks);
+  meta_put(blob, n, nchunks);
   *links_dev = (bricks_region_link *)blob;
   return 0;
 }
 
 int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, int n, int stream) {
   BRK_ARG(ctx && links_dev && stream >= 0 && stream < bricks::kNumStreams);
-  auto it = g_link_meta.find(links_dev);
-  BRK_ARG(it != g_link_meta.end() && it->second.first == n);
-  if (it->second.second == 0) return 0;
+  int have = 0;
+  unsigned nchunks = 0;
+  BRK_ARG(meta_get(links_dev, &have, &nchunks) && have == n);
+  if (nchunks == 0) return 0;
   BRK_CUDA(cudaSetDevice(ctx->device));
   const unsigned *first = (const unsigned *)((const char *)links_dev + sizeof(bricks_region_link) * n);
-  copy_regions_kernel<<<it->second.second, kCopyThreads, 0, ctx->streams[stream]>>>(links_dev, first, n,
+  copy_regions_kernel<<<nchunks, kCopyThreads, 0, ctx->streams[stream]>>>(links_dev, first, n,
                                                                                   nullptr);
   BRK_CUDA(cudaGetLastError());
   ++bricks::g_launches;
@@ -184,7 +204,7 @@ int bricks_exchange_create_v(bricks_ctx *ctx, int rank, int nregions, const size
       delete ex;
       return rc;
     }
-    g_link_meta[blob] = std::make_pair(ex->nself, nchunks);
+    meta_put(blob, ex->nself, nchunks);
     ex->self_links_dev = (bricks_region_link *)blob;
   }
   *out = ex;
@@ -201,7 +221,7 @@ int bricks_exchange_destroy(bricks_exchange *ex) {
   if (!ex) return 0;
   cudaSetDevice(ex->ctx->device);
   if (ex->self_links_dev) {
-    g_link_meta.erase(ex->self_links_dev);
+    meta_erase(ex->self_links_dev);
     cudaFree(ex->self_links_dev);
   }
   delete ex;
@@ -233,10 +253,15 @@ int bricks_exchange_run(bricks_exchange *ex, double *storage, int stream) {
     BRK_NCCL(ncclGroupEnd());
   }
   if (ex->nself) {
-    auto it = g_link_meta.find(ex->self_links_dev);
+    int have = 0;
+    unsigned nchunks = 0;
+    if (!meta_get(ex->self_links_dev, &have, &nchunks)) {
+      bricks::set_error("exchange: the table of self links is gone");
+      return -5;
+    }
     const unsigned *first =
         (const unsigned *)((const char *)ex->self_links_dev + sizeof(bricks_region_link) * ex->nself);
-    copy_regions_kernel<<<it->second.second, kCopyThreads, 0, s>>>(ex->self_links_dev, first, ex->nself,
+    copy_regions_kernel<<<nchunks, kCopyThreads, 0, s>>>(ex->self_links_dev, first, ex->nself,
                                                                   base);
     BRK_CUDA(cudaGetLastError());
     ++bricks::g_launches;
