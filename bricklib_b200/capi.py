@@ -60,6 +60,7 @@ _SIGS = {
     "bricks_launch_count": (C.c_int, [C.POINTER(C.c_ulonglong)]),
     "bricks_links_upload": (C.c_int, [_vp, _vp, C.c_int, _vpp]),
     "bricks_copy_regions": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "bricks_links_free": (C.c_int, [_vp, _vp]),
     "bricks_copy_array": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_int]),
     "bricks_array_stencil7": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "bricks_comm_unique_id": (C.c_int, [_vp]),
@@ -305,7 +306,8 @@ def copy_regions(ctx, links, stream=STREAM_COMPUTE):
     dev = C.c_void_p()
     check(lib().bricks_links_upload(ctx._h, arr, len(links), C.byref(dev)))
     check(lib().bricks_copy_regions(ctx._h, dev, len(links), stream))
-    return dev.value
+    ctx.sync(stream)  # the table is read by the kernel; free it once the copies are done
+    check(lib().bricks_links_free(ctx._h, dev))
 
 
 # probes ---------------------------------------------------------------------
@@ -604,6 +606,11 @@ class LinkTable(object):
     def run(self, stream=STREAM_COMPUTE):
         if self.n:
             check(lib().bricks_copy_regions(self.ctx._h, self._dev, self.n, stream))
+
+    def close(self):
+        if self._dev:
+            lib().bricks_links_free(self.ctx._h, self._dev)
+            self._dev = C.c_void_p()
 
 
 class ExchangeV(Exchange):

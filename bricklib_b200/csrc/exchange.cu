@@ -121,6 +121,18 @@ int bricks_links_upload(bricks_ctx *ctx, const bricks_region_link *links_host, i
   return 0;
 }
 
+int bricks_links_free(bricks_ctx *ctx, bricks_region_link *links_dev) {
+  BRK_ARG(ctx);
+  if (!links_dev) return 0;
+  int n = 0;
+  unsigned nchunks = 0;
+  BRK_ARG(meta_get(links_dev, &n, &nchunks)); /* only tables made by bricks_links_upload */
+  meta_erase(links_dev);
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  BRK_CUDA(cudaFree(links_dev));
+  return 0;
+}
+
 int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, int n, int stream) {
   BRK_ARG(ctx && links_dev && stream >= 0 && stream < bricks::kNumStreams);
   int have = 0;

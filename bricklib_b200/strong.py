@@ -139,6 +139,8 @@ class StrongDomain(object):
             p.close()
         if self.exchange is not None:
             self.exchange.close()
+        for t in (self.local, self.pack, self.unpack):
+            t.close()
         for d in (self.d_a, self.d_b, self.arena):
             self.ctx.free(d)
         self.plan.close()

@@ -52,7 +52,7 @@ struct Links {
     if (n) gpuCheck(bricks_copy_regions(ctx, dev, n, stream));
   }
   ~Links() {
-    if (dev) bricks_free(ctx, dev);
+    if (dev) bricks_links_free(ctx, dev);
   }
 };
 

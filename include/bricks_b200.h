@@ -123,6 +123,8 @@ typedef struct {
 int bricks_links_upload(bricks_ctx *ctx, const bricks_region_link *links_host, int n,
                         bricks_region_link **links_dev);
 int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, int n, int stream);
+/* release a table made by bricks_links_upload (after the copies that use it have completed) */
+int bricks_links_free(bricks_ctx *ctx, bricks_region_link *links_dev);
 
 /* ---- array <-> brick copies on the device: replaces copyToBrick<3> / copyFromBrick<3>
  * (include/bricksetup.h:172-221; cell range and strides of iter_grid, :139-160) for arrays that
