@@ -27,18 +27,7 @@ int bricks_device_count(int *count) {
   return 0;
 }
 
-int bricks_ctx_create(int device, bricks_ctx **out) {
-  BRK_ARG(out);
-  BRK_CUDA(cudaSetDevice(device));
-  cudaDeviceProp prop;
-  BRK_CUDA(cudaGetDeviceProperties(&prop, device));
-  if (prop.major != 10) {
-    set_error("bricks_b200 is built for sm_100a only; device %d is sm_%d%d", device, prop.major,
-              prop.minor);
-    return -2;
-  }
-  bricks_ctx *c = new bricks_ctx;
-  c->device = device;
+static int ctx_init(bricks_ctx *c, const cudaDeviceProp &prop) {
   c->sm_count = prop.multiProcessorCount;
   /* the communication stream outranks the compute stream, so exchange kernels (NCCL, region
    * copies) get the next free SM slots while a stencil sweep is in flight */
@@ -51,6 +40,27 @@ int bricks_ctx_create(int device, bricks_ctx **out) {
   for (int t = 0; t < kNumTimers; ++t) {
     BRK_CUDA(cudaEventCreate(&c->t0[t]));
     BRK_CUDA(cudaEventCreate(&c->t1[t]));
+  }
+  return 0;
+}
+
+int bricks_ctx_create(int device, bricks_ctx **out) {
+  BRK_ARG(out);
+  *out = nullptr;
+  BRK_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  BRK_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("bricks_b200 is built for sm_100a only; device %d is sm_%d%d", device, prop.major,
+              prop.minor);
+    return -2;
+  }
+  bricks_ctx *c = new bricks_ctx;
+  c->device = device;
+  const int rc = ctx_init(c, prop);
+  if (rc) { /* keep the error text of the failing call; release what was created */
+    bricks_ctx_destroy(c);
+    return rc;
   }
   *out = c;
   return 0;

@@ -137,7 +137,12 @@ int bricks_plan_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigne
     for (int d = 0; d < 3; ++d) BRK_ARG(boxes[6 * b + 3 + d] <= gdims[d]);
   BRK_ARG(gdims[0] < 65536 && gdims[1] < 65536 && gdims[2] < 65536);
   BRK_CUDA(cudaSetDevice(ctx->device));
-  bricks_plan *p = new bricks_plan;
+  /* released on every early return below; handed to the caller at the end */
+  struct Guard {
+    bricks_plan *p;
+    ~Guard() { bricks_plan_destroy(p); }
+  } guard{new bricks_plan};
+  bricks_plan *p = guard.p;
   p->ctx = ctx;
   p->nbricks = nbricks;
   size_t ncell = 1;
@@ -146,6 +151,9 @@ int bricks_plan_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigne
     ncell *= gdims[d];
   }
   for (size_t c = 0; c < ncell; ++c) BRK_ARG(grid_host[c] < nbricks);
+  /* every neighbour a kernel may follow names a brick of the storage (the BrickDecomp sentinel is
+   * brick 0, include/brick-mpi.h:353) */
+  for (size_t n = 0; n < (size_t)nbricks * 27; ++n) BRK_ARG(adj_host[n] < nbricks);
   std::vector<MarchItem> items;
   std::vector<unsigned> cells;
   build_items(gdims, nboxes, boxes, 11, items, &cells);
@@ -165,6 +173,7 @@ int bricks_plan_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigne
                            cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaStreamSynchronize(s)); /* host vectors die here */
   p->nlist = (long)blist.size();
+  guard.p = nullptr;
   *out = p;
   return 0;
 }

@@ -267,6 +267,13 @@ extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, co
     BRK_ARG(in[f] && out[f] && in[f] != out[f]);
     BRK_ARG(((uintptr_t)in[f] & 15) == 0 && ((uintptr_t)out[f] & 31) == 0);
   }
+  switch (stencil_id) { /* before anything is built or cached for it */
+    case BRICKS_ST_7PT: case BRICKS_ST_13PT: case BRICKS_ST_25PT: case BRICKS_ST_125PT: break;
+    case BRICKS_ST_7PT_COEFF: case BRICKS_ST_COND: case BRICKS_ST_27PT_COEFF: BRK_ARG(coeff_host); break;
+    default:
+      bricks::set_error("unknown stencil id %d", stencil_id);
+      return -1;
+  }
   BRK_CUDA(cudaSetDevice(plan->ctx->device));
   cudaStream_t s = plan->ctx->streams[stream];
   const int P = planes_per_stage();
