@@ -46,6 +46,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+/* true in exactly one lane of the (converged) warp; the compiler knows it, so warp-uniform
+ * instructions behind it (UTMALDG) need no loop over the active lanes */
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 /* one box of the [brick][k][j][i] field tensor -> dense box in shared memory */
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, int ci, int cj,
                                             int ck, int cb, uint32_t bar) {

@@ -83,6 +83,42 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   };
   auto issue = [&](int s, unsigned nb) {
     const bool roll = (s == 0) || (s == nsteps - 1);
+#ifdef MARCH_UNI_ISSUE
+    /* experiment (tools/build_variants.sh uni): every operand of a copy is warp-uniform BY
+     * CONSTRUCTION -- the neighbour brick of piece m comes out of a warp reduction (CREDUX writes a
+     * uniform register), the rest is compile-time per piece -- and the issuing lane is picked by
+     * elect.sync, so the copies are straight-line UTMALDG instead of the compiler's
+     * ELECT / R2UR.BROADCAST / BRA.U.ANY loop over the lanes' operands (15 % of the warp's time in
+     * profiles/r02_ncu_full_march125.txt) */
+    {
+      const uint32_t bar = bar0 + 8 * (s & 1);
+      const uint32_t dst0 = smem0 + (s & 1) * L::BYTES;
+      const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
+      constexpr int NP = L::NPIECE_MAIN;
+      unsigned nbm[NP];
+#pragma unroll
+      for (int m = 0; m < NP; ++m) nbm[m] = __reduce_max_sync(0xffffffffu, lane == m ? nb : 0u);
+      if (dev::elect_one()) {
+        dev::mbar_expect_tx(bar, roll ? R * ROLL_PLANE_BYTES : P * MAIN_PLANE_BYTES);
+        const CUtensorMap *maps = roll ? fd.maps.roll : fd.maps.main;
+#pragma unroll
+        for (int m = 0; m < NP; ++m) {
+          if (m >= L::NPIECE_ROLL && roll) break;
+          const dev::PieceK q = dev::piece_of<R, CUBE, P>(m);
+          const bool pairable = (m < 2 || (m >= 4 && m < 8));
+          if (pairable && !(m & 1)) {
+            if (!roll && nbm[m + 1] == nbm[m] + 1) {
+              dev::tma_load_4d(dst0 + q.off, &fd.maps.pair[m < 2 ? 0 : 1], q.ci, q.cj, ck, (int)nbm[m], bar);
+              ++m; /* the odd piece came with it */
+              continue;
+            }
+          }
+          dev::tma_load_4d(dst0 + q.off, &maps[q.map], q.ci, q.cj, ck, (int)nbm[m], bar);
+        }
+      }
+      return;
+    }
+#endif
     const uint32_t bar = bar0 + 8 * (s & 1);
     const uint32_t dst = smem0 + (s & 1) * L::BYTES + pk.off;
     const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);

@@ -4,6 +4,7 @@
 #        VARIANT=<name> BRICKS_LIB=$PWD/bricklib_b200/lib/libbricks_b200_<name>.so python tools/variant_check.py 125
 cd "$(dirname "$0")/.."
 declare -A FLAGS=(
+  [uni]="-DMARCH_UNI_ISSUE"
   [win4]="-DMARCH_CUBE_WINDOW=4"
   [win2r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128"
   [win2s3r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128 -DMARCH_WINDOW_STAGES=3"
