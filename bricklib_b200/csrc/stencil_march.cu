@@ -148,6 +148,12 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   o.cur = o.prev = nullptr;
   o.curv = o.prevv = false;
   const int lane_off = lk.j * 8 + lk.ih * 4;
+  /* read once: behind the asm memory clobbers of the pipeline the compiler would re-read
+   * fd.out / fd.out_step from global memory every layer (LDG.128 + a long-scoreboard wait in front
+   * of the first store: 125-point 0.575 -> 0.562 ms, 25-point 0.629 -> 0.613 ms, the other kernels
+   * unchanged; profiles/r02_experiments/variants_h_*, variants_i_*) */
+  double *const out_base = fd.out;
+  const unsigned long long out_stride = fd.out_step;
 
   unsigned nbn = load_nb(0);
   issue(0, nbn);
@@ -175,7 +181,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
         const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
         o.prev = o.cur;
         o.prevv = o.curv && layer > 0;
-        o.cur = fd.out + (size_t)(lk.bb ? b1 : b0) * fd.out_step + lane_off;
+        o.cur = out_base + (size_t)(lk.bb ? b1 : b0) * out_stride + lane_off;
         o.curv = (lk.bb == 0) || (it.valid1 != 0);
       }
     }
