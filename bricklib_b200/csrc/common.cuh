@@ -76,6 +76,12 @@ struct MarchParams {
   const FieldDev *fields;
   unsigned gd0, gd1;
   double c[27];
+#ifdef MARCH_NB_TABLE
+  /* experiment (tools/build_variants.sh nbtab): per-item neighbour rows built with the plan, see
+   * plan.cu build_nbtab */
+  const unsigned *nbtab;
+  unsigned nbtab_stride; /* unsigned per item */
+#endif
 };
 
 /* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane
@@ -121,7 +127,14 @@ struct bricks_plan {
   struct ItemList {
     MarchItem *dev = nullptr;
     int n = 0;
+#ifdef MARCH_NB_TABLE
+    unsigned *nbtab_dev = nullptr;
+    unsigned nbtab_stride = 0;
+#endif
   };
+#ifdef MARCH_NB_TABLE
+  std::vector<unsigned> grid_host, adj_host; /* kept to build neighbour tables lazily */
+#endif
   std::map<unsigned, ItemList> items;
   std::vector<unsigned> boxes; /* kept to build further item lists */
   unsigned *blist_dev = nullptr; /* flat list of every brick in the boxes (naive kernel) */
@@ -148,6 +161,9 @@ unsigned column_length(int stencil_id);
 /* the plan's item list for that column length (built and uploaded on first use); fj = bricks per
  * footprint along j (1: brick pairs, 2: 2x2 bricks) */
 int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems, int fj = 1);
+#ifdef MARCH_NB_TABLE
+int plan_nbtab(bricks_plan *plan, unsigned maxcol, const unsigned **tab_dev, unsigned *stride);
+#endif
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
                unsigned bj, unsigned bk, bool swizzle64, unsigned bb = 1);
 }

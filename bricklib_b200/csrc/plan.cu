@@ -104,6 +104,61 @@ static void build_items(const unsigned gdims[3], int nboxes, const unsigned *box
   }
 }
 
+#ifdef MARCH_NB_TABLE
+/* Experiment: everything a warp looks up through grid[] and adj[] while it marches its column,
+ * resolved at plan time into one row of 16 unsigned per stage source:
+ *   row 0        pre-roll  (pieces cut from the -k neighbours of layer 0)
+ *   row 1 + l    layer l   (same-layer neighbours; both half-stages of the layer use it)
+ *   row nk + 1   post-roll (the +k neighbours of layer nk-1)
+ * entries 0..11 = neighbour brick of piece p (march_dev.cuh piece_of: p&1 picks the brick of the
+ * pair, p>>1 = centre, i-face, -j face, +j face, -j corners, +j corners), 12/13 = the pair's own
+ * bricks, 14 = pairing flags of the main stages (bit p: piece p arrives with piece p-1's two-brick
+ * copy; bit 16+p: piece p is that two-brick copy).  The kernel reads a row as ONE coalesced 64-byte
+ * load, any number of stages ahead, instead of chasing items -> grid -> adj -> adj. */
+static void build_nbtab(const bricks_plan *p, const std::vector<MarchItem> &items, unsigned maxcol,
+                        std::vector<unsigned> &tab, unsigned &stride) {
+  stride = (maxcol + 2) * 16;
+  tab.assign((size_t)items.size() * stride, 0u);
+  const unsigned *grid = p->grid_host.data(), *adj = p->adj_host.data();
+  for (size_t n = 0; n < items.size(); ++n) {
+    const MarchItem &it = items[n];
+    unsigned *base = tab.data() + n * stride;
+    for (unsigned row = 0; row < (unsigned)it.nk + 2; ++row) {
+      const int dk = row == 0 ? -1 : (row == (unsigned)it.nk + 1 ? +1 : 0);
+      const unsigned layer = row == 0 ? 0 : (row == (unsigned)it.nk + 1 ? it.nk - 1 : row - 1);
+      const size_t cell = ((size_t)(it.gk0 + layer) * p->gdims[1] + it.gj) * p->gdims[0] + it.gi;
+      const unsigned b0 = grid[cell];
+      const unsigned b1 = it.valid1 ? grid[cell + 1] : adj[(size_t)b0 * 27 + 14];
+      unsigned *r = base + row * 16;
+      for (int piece = 0; piece < 12; ++piece) {
+        const int useb1 = piece & 1, grp = piece >> 1, side = useb1 ? +1 : -1;
+        const int di = (grp == 1 || grp >= 4) ? side : 0;
+        const int dj = (grp == 2 || grp == 4) ? -1 : ((grp == 3 || grp == 5) ? +1 : 0);
+        r[piece] = adj[(size_t)(useb1 ? b1 : b0) * 27 + (dk + 1) * 9 + (dj + 1) * 3 + (di + 1)];
+      }
+      r[12] = b0;
+      r[13] = b1;
+      unsigned flags = 0;
+      if (dk == 0)
+        for (int piece : {0, 4, 6})
+          if (r[piece + 1] == r[piece] + 1) flags |= (1u << (piece + 1)) | (1u << (16 + piece));
+      r[14] = flags;
+    }
+  }
+}
+
+int plan_nbtab(bricks_plan *p, unsigned maxcol, const unsigned **tab_dev, unsigned *stride) {
+  auto it = p->items.find(maxcol);
+  if (it == p->items.end()) {
+    set_error("plan_nbtab: no item list for column length %u", maxcol);
+    return -1;
+  }
+  *tab_dev = it->second.nbtab_dev;
+  *stride = it->second.nbtab_stride;
+  return 0;
+}
+#endif
+
 int plan_items(bricks_plan *p, unsigned maxcol, const MarchItem **items_dev, int *nitems, int fj) {
   const unsigned key = maxcol | (fj > 1 ? 0x100u : 0u);
   auto it = p->items.find(key);
@@ -116,6 +171,14 @@ int plan_items(bricks_plan *p, unsigned maxcol, const MarchItem **items_dev, int
     BRK_CUDA(cudaMalloc(&l.dev, items.size() * sizeof(MarchItem)));
     BRK_CUDA(cudaMemcpyAsync(l.dev, items.data(), items.size() * sizeof(MarchItem), cudaMemcpyHostToDevice, s));
     BRK_CUDA(cudaStreamSynchronize(s)); /* `items` dies here */
+#ifdef MARCH_NB_TABLE
+    if (fj <= 1) {
+      std::vector<unsigned> tab;
+      build_nbtab(p, items, maxcol, tab, l.nbtab_stride);
+      BRK_CUDA(cudaMalloc(&l.nbtab_dev, tab.size() * sizeof(unsigned)));
+      BRK_CUDA(cudaMemcpy(l.nbtab_dev, tab.data(), tab.size() * sizeof(unsigned), cudaMemcpyHostToDevice));
+    }
+#endif
     it = p->items.emplace(key, l).first;
   }
   *items_dev = it->second.dev;
@@ -173,6 +236,10 @@ int bricks_plan_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigne
                            cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaStreamSynchronize(s)); /* host vectors die here */
   p->nlist = (long)blist.size();
+#ifdef MARCH_NB_TABLE
+  p->grid_host.assign(grid_host, grid_host + ncell);
+  p->adj_host.assign(adj_host, adj_host + (size_t)nbricks * 27);
+#endif
   guard.p = nullptr;
   *out = p;
   return 0;
@@ -183,7 +250,12 @@ int bricks_plan_destroy(bricks_plan *p) {
   cudaSetDevice(p->ctx->device);
   cudaFree(p->grid_dev);
   cudaFree(p->adj_dev);
-  for (auto &kv : p->items) cudaFree(kv.second.dev);
+  for (auto &kv : p->items) {
+    cudaFree(kv.second.dev);
+#ifdef MARCH_NB_TABLE
+    cudaFree(kv.second.nbtab_dev);
+#endif
+  }
   cudaFree(p->blist_dev);
   for (auto &kv : p->fields) cudaFree(kv.second);
   delete p;

@@ -49,6 +49,11 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   }
   __syncwarp();
 
+#ifdef MARCH_NB_TABLE
+  /* experiment (tools/build_variants.sh nbtab): the neighbour rows of this item, resolved at plan
+   * time (plan.cu build_nbtab) -- no grid[] / adj[] lookups in the kernel */
+  const unsigned *nbt = prm.nbtab + (size_t)blockIdx.x * prm.nbtab_stride;
+#else
   /* brick ids of the column: lane t holds layer t */
   unsigned col0 = 0, col1 = 0;
   if (lane < nk) {
@@ -56,6 +61,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     col0 = prm.grid[cell];
     col1 = it.valid1 ? prm.grid[cell + 1] : prm.adj[(size_t)col0 * 27 + 14];
   }
+#endif
 
   dev::LaneK<R, CUBE, P> lk;
   lk.init(lane);
@@ -72,6 +78,11 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   };
   /* neighbour brick that lane's piece of stage s is cut from */
   auto load_nb = [&](int s) -> unsigned {
+#ifdef MARCH_NB_TABLE
+    /* lanes 0..11: neighbour brick of the lane's piece; 12, 13: the pair's own bricks; 14: flags */
+    const int row = s == 0 ? 0 : (s == nsteps - 1 ? nk + 1 : 1 + (s - 1) / H);
+    return lane < 16 ? __ldg(nbt + row * 16 + lane) : 0u;
+#else
     int dk;
     const int layer = step_layer(s, dk);
     const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
@@ -80,6 +91,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     unsigned nb = 0;
     if (lane < 12) nb = prm.adj[(size_t)rowb * 27 + (dk + 1) * 9 + (pk.dj + 1) * 3 + (pk.di + 1)];
     return nb;
+#endif
   };
   auto issue = [&](int s, unsigned nb) {
     const bool roll = (s == 0) || (s == nsteps - 1);
@@ -128,10 +140,16 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
      * bricks are consecutive in storage -- the rule inside a BrickDecomp region -- the even lane
      * fills both with one two-brick copy and the odd lane stays idle (9 instead of 12 copies per
      * cube stage: +1-2 %; going further down to 5 changed nothing, profiles/r02_experiments/). */
+#ifdef MARCH_NB_TABLE
+    const unsigned flags = __shfl_sync(0xffffffffu, nb, 14); /* 0 in the roll rows */
+    const bool lead = lane < 12 && ((flags >> (16 + (lane & 15))) & 1u);
+    const bool follow = lane < 12 && ((flags >> (lane & 15)) & 1u);
+#else
     const unsigned nb_up = __shfl_down_sync(0xffffffffu, nb, 1), nb_dn = __shfl_up_sync(0xffffffffu, nb, 1);
     const bool pairable = !roll && (lane < 2 || (lane >= 4 && lane < 8));
     const bool lead = pairable && !(lane & 1) && nb_up == nb + 1;
     const bool follow = pairable && (lane & 1) && nb == nb_dn + 1;
+#endif
     if (lane < np && !follow) {
       const CUtensorMap *map = roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[lane < 2 ? 0 : 1] : &fd.maps.main[pk.map]);
       dev::tma_load_4d(dst, map, pk.ci, pk.cj, ck, (int)nb, bar);
@@ -158,12 +176,32 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   unsigned nbn = load_nb(0);
   issue(0, nbn);
   nbn = load_nb(1);
+#ifdef MARCH_NB_AHEAD
+  /* experiment (tools/build_variants.sh nbahead): adjacency rows fetched TWO stages ahead.  The ncu
+   * source view shows ~150 cycles per stage of long-scoreboard wait on the row fetched one stage
+   * (3.5 us) earlier: a first-touch adjacency row is a DRAM miss under a loaded memory system */
+  unsigned nbn2 = nsteps > 2 ? load_nb(2) : 0u;
+#endif
 
+#ifdef MARCH_NB_TABLE
+  unsigned bcur = 0, bnext = 0; /* the lane's own brick in the layer of stage s / s+1 */
+#endif
   for (int s = 0; s < nsteps; ++s) {
+#ifdef MARCH_NB_TABLE
+    bcur = bnext;
+#endif
     if (s + 1 < nsteps) {
       dev::fence_proxy_async();
       issue(s + 1, nbn);
+#ifdef MARCH_NB_TABLE
+      bnext = __shfl_sync(0xffffffffu, nbn, 12 + lk.bb);
+#endif
+#ifdef MARCH_NB_AHEAD
+      nbn = nbn2;
+      if (s + 3 < nsteps) nbn2 = load_nb(s + 3);
+#else
       if (s + 2 < nsteps) nbn = load_nb(s + 2);
+#endif
     }
     dev::mbar_wait(bar0 + 8 * (s & 1), (s >> 1) & 1);
     const char *st = smem + (s & 1) * L::BYTES;
@@ -177,11 +215,15 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
       const int layer = (s - 1) / H, half = (s - 1) % H;
       zbase = half * P;
       if (half == 0) {
-        const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
-        const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
         o.prev = o.cur;
         o.prevv = o.curv && layer > 0;
+#ifdef MARCH_NB_TABLE
+        o.cur = out_base + (size_t)bcur * out_stride + lane_off;
+#else
+        const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
+        const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
         o.cur = out_base + (size_t)(lk.bb ? b1 : b0) * out_stride + lane_off;
+#endif
         o.curv = (lk.bb == 0) || (it.valid1 != 0);
       }
     }
@@ -232,6 +274,9 @@ int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfield
   prm.gd0 = plan->gdims[0];
   prm.gd1 = plan->gdims[1];
   for (int i = 0; i < 27; ++i) prm.c[i] = c[i];
+#ifdef MARCH_NB_TABLE
+  if (int rc = bricks::plan_nbtab(plan, bricks::column_length(stencil_id), &prm.nbtab, &prm.nbtab_stride)) return rc;
+#endif
   kern<<<dim3(nitems, nfields), 32, smem, s>>>(prm);
   BRK_CUDA(cudaGetLastError());
   ++bricks::g_launches;

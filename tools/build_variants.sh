@@ -5,6 +5,9 @@
 cd "$(dirname "$0")/.."
 declare -A FLAGS=(
   [uni]="-DMARCH_UNI_ISSUE"
+  [nbahead]="-DMARCH_NB_AHEAD"
+  [nbtab]="-DMARCH_NB_TABLE"
+  [nbtabahead]="-DMARCH_NB_TABLE -DMARCH_NB_AHEAD"
   [win4]="-DMARCH_CUBE_WINDOW=4"
   [win2r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128"
   [win2s3r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128 -DMARCH_WINDOW_STAGES=3"
