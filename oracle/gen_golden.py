@@ -117,8 +117,44 @@ def cond_fixture(dims):
     return out
 
 
+def d3pt27_fixture():
+    """Runs the reference's own d3pt27() (stencils/3axis.cpp:165-247, N = 256, its own random field)
+    through oracle/refshim/ref_3axis.cpp (`make -C oracle golden27`) and cuts one 16^3 block of its
+    output together with the 18^3 block of its input that the block depends on.  d3pt27() throws
+    when its brick form and its array form disagree, so the block stands for both."""
+    import ctypes as C
+    import subprocess
+    from bricklib_b200 import synth
+    subprocess.check_call(["make", "-C", HERE, "golden27"], stdout=subprocess.DEVNULL)
+    lib = C.CDLL(os.path.join(HERE, "_ref", "libref3axis.so"))
+    n, stride, first = C.c_long(), C.c_long(), C.c_long()
+    lib.ref3axis_geometry(C.byref(n), C.byref(stride), C.byref(first))
+    coeff = np.ascontiguousarray(synth.coefficients()[:27] - 0.5)  # both signs
+    pin, pout = C.POINTER(C.c_double)(), C.POINTER(C.c_double)()
+    rc = lib.ref3axis_d3pt27(coeff.ctypes.data_as(C.POINTER(C.c_double)), C.byref(pin), C.byref(pout))
+    if rc:
+        raise RuntimeError("reference d3pt27 failed: %d" % rc)
+    s, f = stride.value, first.value
+    arr = np.ctypeslib.as_array(pin, shape=(s, s, s))
+    out = np.ctypeslib.as_array(pout, shape=(s, s, s))
+    assert out[0, 0, 0] == 0.0 and out[f, f, f] != 0.0  # zeroArray outside the computed box
+    k0, j0, i0 = f + 40, f + 8, f + 100  # a block off every symmetry plane, inside the domain
+    fx = {"coeff": coeff, "origin": np.array([k0, j0, i0]), "n": np.array([n.value]),
+          "in_block": arr[k0 - 1:k0 + 17, j0 - 1:j0 + 17, i0 - 1:i0 + 17].copy(),
+          "out_block": out[k0:k0 + 16, j0:j0 + 16, i0:i0 + 16].copy(),
+          # first computed corner: its halo lies in the ghost zone of the reference's array
+          "in_corner": arr[f - 1:f + 9, f - 1:f + 9, f - 1:f + 9].copy(),
+          "out_corner": out[f:f + 8, f:f + 8, f:f + 8].copy()}
+    lib.ref3axis_release()
+    return fx
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if "d3pt27" in sys.argv[1:]:  # the 27-point block (one ~20 s run of the reference's d3pt27())
+        np.savez(os.path.join(GOLDEN, "d3pt27_block.npz"), **d3pt27_fixture())
+        print("d3pt27_block.npz", os.path.getsize(os.path.join(GOLDEN, "d3pt27_block.npz")))
+        return
     if "cond" in sys.argv[1:]:  # only the cond.py fixtures (added after the others were frozen)
         for d in STENCIL_DIMS:
             np.savez(os.path.join(GOLDEN, "cond_%dx%dx%d.npz" % d), **cond_fixture(d))

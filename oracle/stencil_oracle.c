@@ -16,10 +16,9 @@
  *     adjacency slot (dk*3 + dj)*3 + di, element dat[adj[b][slot]*step + k*64 + j*8 + i]
  *     (row-major in-brick order = fold <8> / <4,8>, include/brick.h:235-245)
  *   - array form: stencils/fake.h:41-352 (ST_CPU), stencils/3axis.cpp:32-37
- *   - d3pt27 (27 runtime coefficients): stencils/3axis.cpp:165-247; no compiled-reference golden
- *     exists for it (the reference function draws its own random field and prints timings only), so
- *     this one stencil is PARITY UNPINNED: restated from the source text, checked array form vs
- *     brick form like the reference's own compareBrick (3axis.cpp:236-237)
+ *   - d3pt27 (27 runtime coefficients): stencils/3axis.cpp:165-247; pinned against a block of the
+ *     output of the reference's own d3pt27() run (oracle/refshim/ref_3axis.cpp,
+ *     tests/golden/d3pt27_block.npz), term 16 read at (k+1, j+1, i) as the source has it
  * Terms are summed one at a time, left to right, in the DSL's order of coefficient classes,
  * without fused multiply-add (built with -ffp-contract=off).
  */
