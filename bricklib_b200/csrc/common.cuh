@@ -82,6 +82,10 @@ struct MarchParams {
   const unsigned *nbtab;
   unsigned nbtab_stride; /* unsigned per item */
 #endif
+#ifdef MARCH_PERSIST
+  unsigned *counter; /* next item per field (march_persist.cuh), zeroed before every launch */
+  unsigned nitems;
+#endif
 };
 
 /* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane
@@ -134,6 +138,8 @@ struct bricks_plan {
   };
 #ifdef MARCH_NB_TABLE
   std::vector<unsigned> grid_host, adj_host; /* kept to build neighbour tables lazily */
+  unsigned *counter_dev = nullptr;           /* item counters of the persistent kernel, one per field */
+  int ncounters = 0;
 #endif
   std::map<unsigned, ItemList> items;
   std::vector<unsigned> boxes; /* kept to build further item lists */

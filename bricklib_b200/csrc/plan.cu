@@ -113,7 +113,7 @@ static void build_items(const unsigned gdims[3], int nboxes, const unsigned *box
  * entries 0..11 = neighbour brick of piece p (march_dev.cuh piece_of: p&1 picks the brick of the
  * pair, p>>1 = centre, i-face, -j face, +j face, -j corners, +j corners), 12/13 = the pair's own
  * bricks, 14 = pairing flags of the main stages (bit p: piece p arrives with piece p-1's two-brick
- * copy; bit 16+p: piece p is that two-brick copy).  The kernel reads a row as ONE coalesced 64-byte
+ * copy; bit 16+p: piece p is that two-brick copy), 15 of row 0 = nk | valid1 << 8.  The kernel reads a row as ONE coalesced 64-byte
  * load, any number of stages ahead, instead of chasing items -> grid -> adj -> adj. */
 static void build_nbtab(const bricks_plan *p, const std::vector<MarchItem> &items, unsigned maxcol,
                         std::vector<unsigned> &tab, unsigned &stride) {
@@ -143,6 +143,7 @@ static void build_nbtab(const bricks_plan *p, const std::vector<MarchItem> &item
         for (int piece : {0, 4, 6})
           if (r[piece + 1] == r[piece] + 1) flags |= (1u << (piece + 1)) | (1u << (16 + piece));
       r[14] = flags;
+      if (row == 0) r[15] = (unsigned)it.nk | (it.valid1 ? 0x100u : 0u); /* item header (march_persist.cuh) */
     }
   }
 }
@@ -257,6 +258,9 @@ int bricks_plan_destroy(bricks_plan *p) {
 #endif
   }
   cudaFree(p->blist_dev);
+#ifdef MARCH_NB_TABLE
+  cudaFree(p->counter_dev);
+#endif
   for (auto &kv : p->fields) cudaFree(kv.second);
   delete p;
   return 0;

@@ -24,6 +24,10 @@
 #define MARCH_CUBE_REGS 168
 #endif
 
+#ifdef MARCH_PERSIST
+#include "march_persist.cuh"
+#endif
+
 namespace {
 
 
@@ -255,6 +259,9 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
 
 template <int R, bool CUBE, int VAR, int P>
 int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
+#ifdef MARCH_PERSIST
+  return launch_persist<R, CUBE, VAR, P>(plan, stencil_id, fields, nfields, c, s);
+#endif
   using L = dev::StageLayout<R, CUBE, P>;
   const int smem = 2 * L::BYTES + 64;
   auto kern = march_kernel<R, CUBE, VAR, P>;
