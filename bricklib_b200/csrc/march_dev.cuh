@@ -33,6 +33,27 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
 }
+#ifdef MARCH_WAIT_TRAP
+/* experiment builds (tools/build_variants.sh adds the flag): a stage that never arrives -- a
+ * bookkeeping bug in a new pipeline -- ends in a trap after ~1 s instead of hanging the GPU */
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (clock64() - t0 > 2000000000ll) __trap();
+  }
+}
+#else
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
@@ -46,6 +67,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+#endif
 /* true in exactly one lane of the (converged) warp; the compiler knows it, so warp-uniform
  * instructions behind it (UTMALDG) need no loop over the active lanes */
 __device__ __forceinline__ bool elect_one() {
