@@ -94,9 +94,15 @@ struct MarchParams {
  * consecutive in storage (main stages only): the two pieces of a pair sit back to back in the
  * stage, so one copy fills both. */
 struct alignas(64) MapSet {
+#ifdef MARCH_JL_SWIZZLE /* [4] / pair[2]: the swizzled four-row -j face box (march_dev.cuh) */
+  CUtensorMap main[5];
+  CUtensorMap roll[5];
+  CUtensorMap pair[3];
+#else
   CUtensorMap main[4];
   CUtensorMap roll[4];
   CUtensorMap pair[2]; /* [0]=centres of bricks b, b+1; [1]=j-face rows of bricks b, b+1 */
+#endif
 };
 
 struct alignas(64) FieldDev {

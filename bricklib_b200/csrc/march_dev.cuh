@@ -139,10 +139,24 @@ template <int R, bool CUBE, int P>
 struct StageLayout {
   static constexpr int HW = R > 2 ? 4 : 2;      /* i-face width in elements (16-byte multiple) */
   static constexpr int C_PL = 512, I_PL = 64 * HW, J_PL = 64 * R, X_PL = 8 * R * HW; /* B/plane */
+  /* experiment -DMARCH_JL_SWIZZLE (cube only): the -j face box is four rows (4..7 of the neighbour)
+   * copied with SWIZZLE_64B, which stores rows 6 and 7 with their 16-byte chunks XORed by 1 (even
+   * planes) or 3 (odd planes): the rows land on the ODD 16-byte granules, the class the centre
+   * image's own swizzle would give rows -2 and -1, and the two-way bank conflicts between those
+   * rows and centre rows 0..1 (19 % of the LDS wavefronts) are gone.  Costs 1 KB per stage. */
+#ifdef MARCH_JL_SWIZZLE
+  static constexpr bool JLX = CUBE && R == 2;
+#else
+  static constexpr bool JLX = false;
+#endif
+  static constexpr int JL_ROWS = JLX ? 4 : R, JL_PL = 64 * JL_ROWS;
+  static constexpr int JSUM_PL = 2 * J_PL + 2 * JL_PL; /* the four j-face pieces, bytes per plane */
   static constexpr int C0 = 0, C1 = P * C_PL;
   static constexpr int IL = 2 * P * C_PL, IR = IL + P * I_PL;
-  static constexpr int JL0 = IR + P * I_PL, JL1 = JL0 + P * J_PL, JH0 = JL1 + P * J_PL,
+  static constexpr int JL0 = IR + P * I_PL, JL1 = JL0 + P * JL_PL, JH0 = JL1 + P * JL_PL,
                        JH1 = JH0 + P * J_PL;
+  static_assert(!JLX || (JL0 % 512 == 0 && (P * JL_PL) % 512 == 0 && (R * JL_PL) % 512 == 0),
+                "swizzled -j face pieces must keep the 512-byte phase of the swizzle pattern");
   /* a TMA destination must be 128-byte aligned: the 2x1 corner pieces of the 27-point cube are
    * only 16 bytes per plane */
   static constexpr int X_STRIDE = P * X_PL < 128 ? 128 : P * X_PL;
@@ -156,7 +170,7 @@ struct StageLayout {
 
 /* what lane p (< 12) copies: piece p of the stage */
 struct PieceK {
-  int useb1, di, dj, map, ci, cj, off, plane_bytes;
+  int useb1, di, dj, map, ci, cj, off, plane_bytes, pairmap;
 };
 
 template <int R, bool CUBE, int P>
@@ -169,9 +183,16 @@ __device__ __forceinline__ PieceK piece_of(int p) {
   k.di = (grp == 1 || grp >= 4) ? side : 0;
   k.dj = (grp == 2 || grp == 4) ? -1 : ((grp == 3 || grp == 5) ? +1 : 0);
   k.map = grp == 0 ? 0 : (grp == 1 ? 1 : (grp <= 3 ? 2 : 3));
+  k.pairmap = grp == 0 ? 0 : 1;
   k.ci = (k.di < 0) ? 8 - L::HW : 0;
   k.cj = (k.dj < 0) ? 8 - R : 0;
   k.plane_bytes = grp == 0 ? L::C_PL : (grp == 1 ? L::I_PL : (grp <= 3 ? L::J_PL : L::X_PL));
+  if (L::JLX && grp == 2) { /* the swizzled four-row -j face box has its own maps */
+    k.map = 4;
+    k.pairmap = 2;
+    k.cj = 8 - L::JL_ROWS;
+    k.plane_bytes = L::JL_PL;
+  }
   const int offs[12] = {L::C0,  L::C1,  L::IL,  L::IR,  L::JL0, L::JL1,
                         L::JH0, L::JH1, L::XLL, L::XRL, L::XLH, L::XRH};
   k.off = offs[p < 12 ? p : 0];
@@ -191,6 +212,9 @@ struct LaneK {
   int rpitch[2 * R + 1]; /* bytes per plane for that row */
   int hrow[2 * R + 1];   /* halo: byte offset of the HW-wide row j+d, plane 0 */
   int hpitch[2 * R + 1];
+#ifdef MARCH_JL_SWIZZLE
+  int jx[R]; /* XOR for the quad offsets of row j+d (d < 0) in ODD planes: 0x20 when it is a -j face row */
+#endif
 
   __device__ __forceinline__ void init(int lane) {
     bb = lane >> 4;
@@ -202,6 +226,22 @@ struct LaneK {
 #pragma unroll
     for (int d = -R; d <= R; ++d) {
       const int jj = j + d, a = d + R;
+#ifdef MARCH_JL_SWIZZLE
+      if (d < 0) jx[a] = 0;
+      if (L::JLX && jj < 0) {
+        /* row jj of the brick = row rr of the four-row box; SWIZZLE_64B XORs the 16-byte chunk index
+         * with bits 7..8 of the shared-memory address: (rr >> 1) + 2 * plane for a 512-aligned piece */
+        const int rr = jj + L::JL_ROWS;
+        const int base = (bb ? L::JL1 : L::JL0) + rr * 64, x0 = (rr >> 1) & 3;
+        row0[a] = base + (((2 * ih) ^ x0) << 4);
+        row1[a] = base + (((2 * ih + 1) ^ x0) << 4);
+        rpitch[a] = L::JL_PL;
+        jx[a] = 0x20; /* odd planes: chunk ^ (x0 ^ 2) */
+        hrow[a] = (bb ? L::XRL : L::XLL) + (jj + R) * L::HW * 8;
+        hpitch[a] = L::X_PL;
+        continue;
+      }
+#endif
       if (jj >= 0 && jj < 8) {
         const int base = (bb ? L::C1 : L::C0) + jj * 64, sw = (jj >> 1) & 3;
         row0[a] = base + (((2 * ih) ^ sw) << 4);

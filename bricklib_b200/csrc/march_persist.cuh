@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(32)
   dev::LaneK<R, CUBE, P> lk;
   lk.init(lane);
   const dev::PieceK pk = dev::piece_of<R, CUBE, P>(lane < 12 ? lane : 0);
-  constexpr int MAIN_PLANE_BYTES = 2 * L::C_PL + 2 * L::I_PL + 4 * L::J_PL + (CUBE ? 4 * L::X_PL : 0);
+  constexpr int MAIN_PLANE_BYTES = 2 * L::C_PL + 2 * L::I_PL + L::JSUM_PL + (CUBE ? 4 * L::X_PL : 0);
   constexpr int ROLL_PLANE_BYTES = CUBE ? MAIN_PLANE_BYTES : 2 * L::C_PL;
   const int lane_off = lk.j * 8 + lk.ih * 4;
 
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(32)
     const bool follow = lane < 12 && ((flags >> (lane & 15)) & 1u);
     if (lane < np && !follow) {
       const CUtensorMap *map =
-          roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[lane < 2 ? 0 : 1] : &fd.maps.main[pk.map]);
+          roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[pk.pairmap] : &fd.maps.main[pk.map]);
       dev::tma_load_4d(dst, map, pk.ci, pk.cj, ck, (int)nb, bar);
     }
   };

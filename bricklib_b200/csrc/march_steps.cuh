@@ -269,6 +269,11 @@ __device__ __forceinline__ void cube_step(const char *st, const LaneK<2, true, P
       double xr[5][4], hr[5][HW];
 #pragma unroll
       for (int a = 0; a < 5; ++a) {
+#ifdef MARCH_JL_SWIZZLE
+        if (a < R && (z & 1)) /* swizzled -j face rows: odd planes flip chunk bit 1 (march_dev.cuh) */
+          ld_quad(st, (lk.row0[a] + z * lk.rpitch[a]) ^ lk.jx[a], (lk.row1[a] + z * lk.rpitch[a]) ^ lk.jx[a], xr[a]);
+        else
+#endif
         ld_quad(st, lk.row0[a] + z * lk.rpitch[a], lk.row1[a] + z * lk.rpitch[a], xr[a]);
         ld_halo<HW>(st, lk.hrow[a] + z * lk.hpitch[a], lk.halo, hr[a]);
       }

@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   lk.init(lane);
   const dev::PieceK pk = dev::piece_of<R, CUBE, P>(lane < 12 ? lane : 0);
   constexpr int MAIN_PLANE_BYTES =
-      2 * L::C_PL + 2 * L::I_PL + 4 * L::J_PL + (CUBE ? 4 * L::X_PL : 0);
+      2 * L::C_PL + 2 * L::I_PL + L::JSUM_PL + (CUBE ? 4 * L::X_PL : 0);
   constexpr int ROLL_PLANE_BYTES = CUBE ? MAIN_PLANE_BYTES : 2 * L::C_PL;
 
   auto step_layer = [&](int s, int &dk) -> int {
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
           const bool pairable = (m < 2 || (m >= 4 && m < 8));
           if (pairable && !(m & 1)) {
             if (!roll && nbm[m + 1] == nbm[m] + 1) {
-              dev::tma_load_4d(dst0 + q.off, &fd.maps.pair[m < 2 ? 0 : 1], q.ci, q.cj, ck, (int)nbm[m], bar);
+              dev::tma_load_4d(dst0 + q.off, &fd.maps.pair[q.pairmap], q.ci, q.cj, ck, (int)nbm[m], bar);
               ++m; /* the odd piece came with it */
               continue;
             }
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     const bool follow = pairable && (lane & 1) && nb == nb_dn + 1;
 #endif
     if (lane < np && !follow) {
-      const CUtensorMap *map = roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[lane < 2 ? 0 : 1] : &fd.maps.main[pk.map]);
+      const CUtensorMap *map = roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[pk.pairmap] : &fd.maps.main[pk.map]);
       dev::tma_load_4d(dst, map, pk.ci, pk.cj, ck, (int)nb, bar);
     }
   };
@@ -334,10 +334,16 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
       if (!rc) rc = bricks::encode_map(&m[1], in[f], plan->nbricks, in_step, HW, 8, pk, false);
       if (!rc) rc = bricks::encode_map(&m[2], in[f], plan->nbricks, in_step, 8, R, pk, false);
       if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false);
+#ifdef MARCH_JL_SWIZZLE
+      if (!rc && cube && R == 2) rc = bricks::encode_map(&m[4], in[f], plan->nbricks, in_step, 8, 4, pk, true);
+#endif
       if (rc) return rc;
     }
     int rc = bricks::encode_map(&fd.maps.pair[0], in[f], plan->nbricks, in_step, 8, 8, P, true, 2);
     if (!rc) rc = bricks::encode_map(&fd.maps.pair[1], in[f], plan->nbricks, in_step, 8, R, P, false, 2);
+#ifdef MARCH_JL_SWIZZLE
+    if (!rc && cube && R == 2) rc = bricks::encode_map(&fd.maps.pair[2], in[f], plan->nbricks, in_step, 8, 4, P, true, 2);
+#endif
     if (rc) return rc;
   }
   FieldDev *d = nullptr;

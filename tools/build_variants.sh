@@ -9,6 +9,8 @@ declare -A FLAGS=(
   [nbtab]="-DMARCH_NB_TABLE"
   [nbtabahead]="-DMARCH_NB_TABLE -DMARCH_NB_AHEAD"
   [persist]="-DMARCH_NB_TABLE -DMARCH_PERSIST"
+  [jlswz]="-DMARCH_JL_SWIZZLE"
+  [jlswzpersist]="-DMARCH_JL_SWIZZLE -DMARCH_NB_TABLE -DMARCH_PERSIST"
   [win4]="-DMARCH_CUBE_WINDOW=4"
   [win2r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128"
   [win2s3r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128 -DMARCH_WINDOW_STAGES=3"
