@@ -139,22 +139,25 @@ template <int R, bool CUBE, int P>
 struct StageLayout {
   static constexpr int HW = R > 2 ? 4 : 2;      /* i-face width in elements (16-byte multiple) */
   static constexpr int C_PL = 512, I_PL = 64 * HW, J_PL = 64 * R, X_PL = 8 * R * HW; /* B/plane */
-  /* experiment -DMARCH_JL_SWIZZLE (cube only): the -j face box is four rows (4..7 of the neighbour)
+  /* experiment -DMARCH_JL_SWIZZLE (125-point cube, 25-point star): the -j face box is four rows (4..7 of the neighbour)
    * copied with SWIZZLE_64B, which stores rows 6 and 7 with their 16-byte chunks XORed by 1 (even
    * planes) or 3 (odd planes): the rows land on the ODD 16-byte granules, the class the centre
    * image's own swizzle would give rows -2 and -1, and the two-way bank conflicts between those
    * rows and centre rows 0..1 (19 % of the LDS wavefronts) are gone.  Costs 1 KB per stage. */
 #ifdef MARCH_JL_SWIZZLE
-  static constexpr bool JLX = CUBE && R == 2;
+  static constexpr bool JLX = (CUBE && R == 2) || (!CUBE && R == 4); /* the 25-point star's -j face IS four rows */
 #else
   static constexpr bool JLX = false;
 #endif
+  /* with R = 4 the +j face is four rows as well: swizzled, its rows 8..11 continue the centre pattern */
+  static constexpr bool JHX = JLX && !CUBE && R == 4;
   static constexpr int JL_ROWS = JLX ? 4 : R, JL_PL = 64 * JL_ROWS;
   static constexpr int JSUM_PL = 2 * J_PL + 2 * JL_PL; /* the four j-face pieces, bytes per plane */
   static constexpr int C0 = 0, C1 = P * C_PL;
   static constexpr int IL = 2 * P * C_PL, IR = IL + P * I_PL;
   static constexpr int JL0 = IR + P * I_PL, JL1 = JL0 + P * JL_PL, JH0 = JL1 + P * JL_PL,
                        JH1 = JH0 + P * J_PL;
+  static_assert(!JHX || (JH0 % 512 == 0 && (P * J_PL) % 512 == 0), "swizzled +j face pieces: 512-byte phase");
   static_assert(!JLX || (JL0 % 512 == 0 && (P * JL_PL) % 512 == 0 && (R * JL_PL) % 512 == 0),
                 "swizzled -j face pieces must keep the 512-byte phase of the swizzle pattern");
   /* a TMA destination must be 128-byte aligned: the 2x1 corner pieces of the 27-point cube are
@@ -187,6 +190,10 @@ __device__ __forceinline__ PieceK piece_of(int p) {
   k.ci = (k.di < 0) ? 8 - L::HW : 0;
   k.cj = (k.dj < 0) ? 8 - R : 0;
   k.plane_bytes = grp == 0 ? L::C_PL : (grp == 1 ? L::I_PL : (grp <= 3 ? L::J_PL : L::X_PL));
+  if (L::JHX && grp == 3) { /* same box shape at rows 0..3 of the +j neighbour */
+    k.map = 4;
+    k.pairmap = 2;
+  }
   if (L::JLX && grp == 2) { /* the swizzled four-row -j face box has its own maps */
     k.map = 4;
     k.pairmap = 2;
@@ -213,7 +220,7 @@ struct LaneK {
   int hrow[2 * R + 1];   /* halo: byte offset of the HW-wide row j+d, plane 0 */
   int hpitch[2 * R + 1];
 #ifdef MARCH_JL_SWIZZLE
-  int jx[R]; /* XOR for the quad offsets of row j+d (d < 0) in ODD planes: 0x20 when it is a -j face row */
+  int jx[2 * R + 1]; /* XOR for the quad offsets of row j+d in ODD planes: 0x20 when it is a swizzled face row */
 #endif
 
   __device__ __forceinline__ void init(int lane) {
@@ -227,7 +234,18 @@ struct LaneK {
     for (int d = -R; d <= R; ++d) {
       const int jj = j + d, a = d + R;
 #ifdef MARCH_JL_SWIZZLE
-      if (d < 0) jx[a] = 0;
+      jx[a] = 0;
+      if (L::JHX && jj > 7) {
+        const int rr = jj - 8;
+        const int base = (bb ? L::JH1 : L::JH0) + rr * 64, x0 = (rr >> 1) & 3;
+        row0[a] = base + (((2 * ih) ^ x0) << 4);
+        row1[a] = base + (((2 * ih + 1) ^ x0) << 4);
+        rpitch[a] = L::J_PL;
+        jx[a] = 0x20;
+        hrow[a] = (bb ? L::XRH : L::XLH) + rr * L::HW * 8;
+        hpitch[a] = L::X_PL;
+        continue;
+      }
       if (L::JLX && jj < 0) {
         /* row jj of the brick = row rr of the four-row box; SWIZZLE_64B XORs the 16-byte chunk index
          * with bits 7..8 of the shared-memory address: (rr >> 1) + 2 * plane for a 512-aligned piece */

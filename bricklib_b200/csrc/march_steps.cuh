@@ -98,7 +98,19 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
 #pragma unroll
       for (int r = 1; r <= R; ++r) {
         double up[4], dn[4];
+#ifdef MARCH_JL_SWIZZLE
+        if (StageLayout<R, false, P>::JHX && (z & 1))
+          ld_quad(st, (lk.row0[R + r] + z * lk.rpitch[R + r]) ^ lk.jx[R + r],
+                  (lk.row1[R + r] + z * lk.rpitch[R + r]) ^ lk.jx[R + r], up);
+        else
+#endif
         ld_quad(st, lk.row0[R + r] + z * lk.rpitch[R + r], lk.row1[R + r] + z * lk.rpitch[R + r], up);
+#ifdef MARCH_JL_SWIZZLE
+        if (StageLayout<R, false, P>::JLX && (z & 1)) /* swizzled -j face rows, odd planes (march_dev.cuh) */
+          ld_quad(st, (lk.row0[R - r] + z * lk.rpitch[R - r]) ^ lk.jx[R - r],
+                  (lk.row1[R - r] + z * lk.rpitch[R - r]) ^ lk.jx[R - r], dn);
+        else
+#endif
         ld_quad(st, lk.row0[R - r] + z * lk.rpitch[R - r], lk.row1[R - r] + z * lk.rpitch[R - r], dn);
         if (VAR == 2) relu(up), relu(dn);
 #pragma unroll

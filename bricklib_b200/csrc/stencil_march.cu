@@ -335,14 +335,16 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
       if (!rc) rc = bricks::encode_map(&m[2], in[f], plan->nbricks, in_step, 8, R, pk, false);
       if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false);
 #ifdef MARCH_JL_SWIZZLE
-      if (!rc && cube && R == 2) rc = bricks::encode_map(&m[4], in[f], plan->nbricks, in_step, 8, 4, pk, true);
+      if (!rc && ((cube && R == 2) || (!cube && R == 4)))
+        rc = bricks::encode_map(&m[4], in[f], plan->nbricks, in_step, 8, 4, pk, true);
 #endif
       if (rc) return rc;
     }
     int rc = bricks::encode_map(&fd.maps.pair[0], in[f], plan->nbricks, in_step, 8, 8, P, true, 2);
     if (!rc) rc = bricks::encode_map(&fd.maps.pair[1], in[f], plan->nbricks, in_step, 8, R, P, false, 2);
 #ifdef MARCH_JL_SWIZZLE
-    if (!rc && cube && R == 2) rc = bricks::encode_map(&fd.maps.pair[2], in[f], plan->nbricks, in_step, 8, 4, P, true, 2);
+    if (!rc && ((cube && R == 2) || (!cube && R == 4)))
+      rc = bricks::encode_map(&fd.maps.pair[2], in[f], plan->nbricks, in_step, 8, 4, P, true, 2);
 #endif
     if (rc) return rc;
   }

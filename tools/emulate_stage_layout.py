@@ -2,11 +2,11 @@
 the StageLayout of march_dev.cuh, then every lane's shared-memory quad loads (LaneK) -- checks that
 each lane reads the elements it should and counts LDS.128 bank conflicts per 8-lane phase.
 Mirrors the C++ formulas by hand; used to check layout experiments (-DMARCH_JL_SWIZZLE) without a GPU.
-usage: python tools/emulate_stage_layout.py [P]"""
+usage: python tools/emulate_stage_layout.py [P] [R]   (R = 2: 125-point cube, R = 4: 25-point star)"""
 import sys
 import numpy as np
 
-R, HW = 2, 2
+R, HW = 2, 2  # set by main()
 
 
 def layout(P, jlx):
@@ -53,6 +53,11 @@ def lanek(L, lane, jlx):
             base, x0 = (L["JL1"] if bb else L["JL0"]) + rr * 64, (rr >> 1) & 3
             row0[a], row1[a] = base + (((2 * ih) ^ x0) << 4), base + (((2 * ih + 1) ^ x0) << 4)
             pitch[a], jx[a] = L["JL_PL"], 0x20
+        elif jlx and R == 4 and jj > 7:  # JHX: the +j face of the 25-point star, swizzled as well
+            rr = jj - 8
+            base, x0 = (L["JH1"] if bb else L["JH0"]) + rr * 64, (rr >> 1) & 3
+            row0[a], row1[a] = base + (((2 * ih) ^ x0) << 4), base + (((2 * ih + 1) ^ x0) << 4)
+            pitch[a], jx[a] = L["J_PL"], 0x20
         elif 0 <= jj < 8:
             base, sw = (L["C1"] if bb else L["C0"]) + jj * 64, (jj >> 1) & 3
             row0[a], row1[a] = base + (((2 * ih) ^ sw) << 4), base + (((2 * ih + 1) ^ sw) << 4)
@@ -76,7 +81,7 @@ def run(P, jlx):
         tma(smem, L["JL0"], src, (8, 4, P, 2), (0, 4, ck, 2), True)
     else:
         tma(smem, L["JL0"], src, (8, R, P, 2), (0, 8 - R, ck, 2), False)
-    tma(smem, L["JH0"], src, (8, R, P, 2), (0, 0, ck, 4), False)
+    tma(smem, L["JH0"], src, (8, R, P, 2), (0, 0, ck, 4), jlx and R == 4)
     wrong = conflicts = loads = 0
     for z in range(P):
         for a in range(2 * R + 1):
@@ -85,7 +90,7 @@ def run(P, jlx):
                 for lane in range(32):
                     bb, j, ih, row0, row1, pitch, jx = lanek(L, lane, jlx)
                     off = (row1 if q else row0)[a] + z * pitch[a]
-                    if jlx and a < R and (z & 1):
+                    if jlx and (a < R or R == 4) and (z & 1):
                         off ^= jx[a]
                     addrs.append(off)
                     jj = j + a - R
@@ -102,6 +107,8 @@ def run(P, jlx):
 
 if __name__ == "__main__":
     P = int(sys.argv[1]) if len(sys.argv) > 1 else 4
+    R = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+    HW = 4 if R > 2 else 2
     for jlx in (False, True):
         w, c, n, b = run(P, jlx)
         print("P=%d swizzled -j face %-5s: wrong quads %d, conflicting lanes %d over %d LDS.128 (%d wavefronts ideal), "
