@@ -224,12 +224,27 @@ struct LaneK {
 #endif
 
   __device__ __forceinline__ void init(int lane) {
+#ifdef MARCH_EDGE_HI
+    /* experiment: the 16 lanes on the footprint edge (the only ones that use the i-face values) are
+     * lanes 16..31, so a PREDICATED i-face load touches two quarter-warps instead of four:
+     * lane = edge * 16 + j * 2 + bb, with ih = bb on the edge and 1 - bb inside */
+    bb = lane & 1;
+    j = (lane >> 1) & 7;
+    halo = (lane >> 4) != 0;
+    ih = halo ? bb : 1 - bb;
+    {
+      auto lane_of = [](int b, int jj, int i) { return (i == b ? 16 : 0) + jj * 2 + b; };
+      srcL = ih ? lane_of(bb, j, 0) : (bb ? lane_of(0, j, 1) : lane);
+      srcR = ih ? (bb ? lane : lane_of(1, j, 0)) : lane_of(bb, j, 1);
+    }
+#else
     bb = lane >> 4;
     j = (lane >> 1) & 7;
     ih = lane & 1;
     halo = (ih == bb);
     srcL = ih ? lane - 1 : (bb ? lane - 15 : lane);
     srcR = ih ? (bb ? lane : lane + 15) : lane + 1;
+#endif
 #pragma unroll
     for (int d = -R; d <= R; ++d) {
       const int jj = j + d, a = d + R;

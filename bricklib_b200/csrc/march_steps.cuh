@@ -53,7 +53,29 @@ __device__ __forceinline__ void gather_i(const double (&x)[4], const double (&h)
  * bytes (a broadcast, no extra wavefront), so the load needs neither a predicate nor a zero fill;
  * only the lane on the footprint edge uses the value (gather_i). */
 template <int HW>
+#ifdef MARCH_EDGE_HI
+/* edge lanes are lanes 16..31 (LaneK::init): the load is predicated, the other half-warp issues nothing */
+__device__ __forceinline__ void ld_halo(const char *st, int off, bool halo, double (&h)[HW]) {
+#pragma unroll
+  for (int q = 0; q < HW / 2; ++q) {
+    double a = 0.0, b = 0.0;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %3, 0;\n"
+        "@p ld.shared.v2.f64 {%0, %1}, [%2];\n"
+        "}\n"
+        : "+d"(a), "+d"(b)
+        : "r"(smem_u32(st + off + 16 * q)), "r"((int)halo));
+    h[2 * q] = a;
+    h[2 * q + 1] = b;
+  }
+}
+template <int HW>
+__device__ __forceinline__ void ld_halo_unused(const char *st, int off, bool /*halo*/, double (&h)[HW]) {
+#else
 __device__ __forceinline__ void ld_halo(const char *st, int off, bool /*halo*/, double (&h)[HW]) {
+#endif
 #pragma unroll
   for (int q = 0; q < HW / 2; ++q) {
     const double2 v = *reinterpret_cast<const double2 *>(st + off + 16 * q);

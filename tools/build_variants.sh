@@ -10,6 +10,8 @@ declare -A FLAGS=(
   [nbtabahead]="-DMARCH_NB_TABLE -DMARCH_NB_AHEAD"
   [persist]="-DMARCH_NB_TABLE -DMARCH_PERSIST"
   [jlswz]="-DMARCH_JL_SWIZZLE"
+  [edgehi]="-DMARCH_EDGE_HI"
+  [jlswzedge]="-DMARCH_JL_SWIZZLE -DMARCH_EDGE_HI"
   [jlswzpersist]="-DMARCH_JL_SWIZZLE -DMARCH_NB_TABLE -DMARCH_PERSIST"
   [win4]="-DMARCH_CUBE_WINDOW=4"
   [win2r128]="-DMARCH_CUBE_WINDOW=2 -DMARCH_WINDOW_REGS=128"

@@ -2,7 +2,8 @@
 the StageLayout of march_dev.cuh, then every lane's shared-memory quad loads (LaneK) -- checks that
 each lane reads the elements it should and counts LDS.128 bank conflicts per 8-lane phase.
 Mirrors the C++ formulas by hand; used to check layout experiments (-DMARCH_JL_SWIZZLE) without a GPU.
-usage: python tools/emulate_stage_layout.py [P] [R]   (R = 2: 125-point cube, R = 4: 25-point star)"""
+usage: python tools/emulate_stage_layout.py [P] [R]   (R = 2: 125-point cube, R = 4: 25-point star)
+       python tools/emulate_stage_layout.py edge      (the -DMARCH_EDGE_HI lane numbering)"""
 import sys
 import numpy as np
 
@@ -42,8 +43,53 @@ def tma(smem, dst, src, box, coord, swizzle):
                     smem[a // 8] = src[cb + b, ck + k, cj + j, ci + i]
 
 
+EDGE_HI = False  # -DMARCH_EDGE_HI: lane = edge * 16 + j * 2 + bb
+
+
+def lane_fields(lane):
+    if EDGE_HI:
+        bb, j, edge = lane & 1, (lane >> 1) & 7, lane >> 4
+        return bb, j, (bb if edge else 1 - bb)
+    return lane >> 4, (lane >> 1) & 7, lane & 1
+
+
+def lane_of(bb, j, ih):
+    if EDGE_HI:
+        return (16 if ih == bb else 0) + j * 2 + bb
+    return bb * 16 + j * 2 + ih
+
+
+def shuffle_sources(lane):
+    """(srcL, srcR) as LaneK::init computes them"""
+    bb, j, ih = lane_fields(lane)
+    if EDGE_HI:
+        src_l = lane_of(bb, j, 0) if ih else (lane_of(0, j, 1) if bb else lane)
+        src_r = (lane if bb else lane_of(1, j, 0)) if ih else lane_of(bb, j, 1)
+    else:
+        src_l = lane - 1 if ih else (lane - 15 if bb else lane)
+        src_r = (lane if bb else lane + 15) if ih else lane + 1
+    return src_l, src_r
+
+
+def check_shuffles():
+    """the left / right source lane owns the quad next to this lane's in the 16-wide row, or is the
+    lane itself on the footprint edge (where the i-face value is used instead)"""
+    bad = 0
+    for lane in range(32):
+        bb, j, ih = lane_fields(lane)
+        pos = bb * 2 + ih  # quad index 0..3 along i
+        for src, want in zip(shuffle_sources(lane), (pos - 1, pos + 1)):
+            sb, sj, si = lane_fields(src)
+            if 0 <= want <= 3:
+                bad += int((sj, sb * 2 + si) != (j, want))
+            else:
+                bad += int(src != lane)
+    edge = [lane for lane in range(32) if lane_fields(lane)[2] == lane_fields(lane)[0]]
+    return bad, edge
+
+
 def lanek(L, lane, jlx):
-    bb, j, ih = lane >> 4, (lane >> 1) & 7, lane & 1
+    bb, j, ih = lane_fields(lane)
     row0, row1, pitch, jx = {}, {}, {}, {}
     for d in range(-R, R + 1):
         jj, a = j + d, d + R
@@ -105,7 +151,22 @@ def run(P, jlx):
     return wrong, conflicts, loads, L["BYTES"]
 
 
+def main_edge():
+    global EDGE_HI
+    for flag in (False, True):
+        EDGE_HI = flag
+        bad, edge = check_shuffles()
+        w, c, n, _ = run(4, False)
+        quarters = sorted(set(x >> 3 for x in edge))
+        print("edge lanes high %-5s: wrong shuffle sources %d, wrong quads %d, conflicting lanes %d over %d LDS.128, "
+              "edge lanes sit in quarter-warps %s" % (flag, bad, w, c, n, quarters))
+    EDGE_HI = False
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "edge":
+        main_edge()
+        sys.exit(0)
     P = int(sys.argv[1]) if len(sys.argv) > 1 else 4
     R = int(sys.argv[2]) if len(sys.argv) > 2 else 2
     HW = 4 if R > 2 else 2
