@@ -139,13 +139,13 @@ template <int R, bool CUBE, int P>
 struct StageLayout {
   static constexpr int HW = R > 2 ? 4 : 2;      /* i-face width in elements (16-byte multiple) */
   static constexpr int C_PL = 512, I_PL = 64 * HW, J_PL = 64 * R, X_PL = 8 * R * HW; /* B/plane */
-  /* experiment -DMARCH_JL_SWIZZLE (125-point cube, 25-point star): the -j face box is four rows (4..7 of the neighbour)
+  /* experiment -DMARCH_JL_SWIZZLE (125-point cube, 13- and 25-point stars): the -j face box is four rows (4..7 of the neighbour)
    * copied with SWIZZLE_64B, which stores rows 6 and 7 with their 16-byte chunks XORed by 1 (even
    * planes) or 3 (odd planes): the rows land on the ODD 16-byte granules, the class the centre
    * image's own swizzle would give rows -2 and -1, and the two-way bank conflicts between those
    * rows and centre rows 0..1 (19 % of the LDS wavefronts) are gone.  Costs 1 KB per stage. */
 #ifdef MARCH_JL_SWIZZLE
-  static constexpr bool JLX = (CUBE && R == 2) || (!CUBE && R == 4); /* the 25-point star's -j face IS four rows */
+  static constexpr bool JLX = R == 2 || (!CUBE && R == 4); /* cube, 13-point star; the 25-point star's -j face IS four rows */
 #else
   static constexpr bool JLX = false;
 #endif

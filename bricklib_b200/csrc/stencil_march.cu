@@ -335,7 +335,7 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
       if (!rc) rc = bricks::encode_map(&m[2], in[f], plan->nbricks, in_step, 8, R, pk, false);
       if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false);
 #ifdef MARCH_JL_SWIZZLE
-      if (!rc && ((cube && R == 2) || (!cube && R == 4)))
+      if (!rc && (R == 2 || (!cube && R == 4)))
         rc = bricks::encode_map(&m[4], in[f], plan->nbricks, in_step, 8, 4, pk, true);
 #endif
       if (rc) return rc;
@@ -343,7 +343,7 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
     int rc = bricks::encode_map(&fd.maps.pair[0], in[f], plan->nbricks, in_step, 8, 8, P, true, 2);
     if (!rc) rc = bricks::encode_map(&fd.maps.pair[1], in[f], plan->nbricks, in_step, 8, R, P, false, 2);
 #ifdef MARCH_JL_SWIZZLE
-    if (!rc && ((cube && R == 2) || (!cube && R == 4)))
+    if (!rc && (R == 2 || (!cube && R == 4)))
       rc = bricks::encode_map(&fd.maps.pair[2], in[f], plan->nbricks, in_step, 8, 4, P, true, 2);
 #endif
     if (rc) return rc;
