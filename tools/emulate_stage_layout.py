@@ -146,7 +146,7 @@ def run(P, jlx):
                     wrong += int(not np.array_equal(exp, got))
                 for ph in range(4):
                     g = [(x >> 4) & 7 for x in addrs[8 * ph: 8 * ph + 8]]
-                    conflicts += 8 - len(set(g))
+                    conflicts += max(g.count(v) for v in set(g)) - 1  # extra wavefronts of this phase
                 loads += 1
     return wrong, conflicts, loads, L["BYTES"]
 
@@ -158,7 +158,7 @@ def main_edge():
         bad, edge = check_shuffles()
         w, c, n, _ = run(4, False)
         quarters = sorted(set(x >> 3 for x in edge))
-        print("edge lanes high %-5s: wrong shuffle sources %d, wrong quads %d, conflicting lanes %d over %d LDS.128, "
+        print("edge lanes high %-5s: wrong shuffle sources %d, wrong quads %d, %d extra wavefronts over %d LDS.128, "
               "edge lanes sit in quarter-warps %s" % (flag, bad, w, c, n, quarters))
     EDGE_HI = False
 
@@ -172,5 +172,5 @@ if __name__ == "__main__":
     HW = 4 if R > 2 else 2
     for jlx in (False, True):
         w, c, n, b = run(P, jlx)
-        print("P=%d swizzled -j face %-5s: wrong quads %d, conflicting lanes %d over %d LDS.128 (%d wavefronts ideal), "
+        print("P=%d swizzled -j face %-5s: wrong quads %d, %d extra wavefronts over %d LDS.128 (%d wavefronts ideal), "
               "stage %d bytes" % (P, jlx, w, c, n, 4 * n, b))
