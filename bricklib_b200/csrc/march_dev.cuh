@@ -226,14 +226,25 @@ struct LaneK {
   __device__ __forceinline__ void init(int lane) {
 #ifdef MARCH_EDGE_HI
     /* experiment: the 16 lanes on the footprint edge (the only ones that use the i-face values) are
-     * lanes 16..31, so a PREDICATED i-face load touches two quarter-warps instead of four:
-     * lane = edge * 16 + j * 2 + bb, with ih = bb on the edge and 1 - bb inside */
-    bb = lane & 1;
-    j = (lane >> 1) & 7;
+     * lanes 16..31, one quarter-warp per brick (lane = 16 + bb * 8 + j, ih = bb): a PREDICATED i-face
+     * load then touches two quarter-warps, each reading the eight rows of one i-face piece (one
+     * wavefront).  The inner lanes keep the product's phase shape, four rows x two bricks
+     * (lane = (j >> 2) * 8 + (j & 3) * 2 + bb, ih = 1 - bb).  Grouping found with the stage model
+     * (tools/emulate_stage_layout.py edge). */
     halo = (lane >> 4) != 0;
-    ih = halo ? bb : 1 - bb;
+    if (halo) {
+      bb = (lane >> 3) & 1;
+      j = lane & 7;
+      ih = bb;
+    } else {
+      bb = lane & 1;
+      j = ((lane >> 3) & 1) * 4 + ((lane >> 1) & 3);
+      ih = 1 - bb;
+    }
     {
-      auto lane_of = [](int b, int jj, int i) { return (i == b ? 16 : 0) + jj * 2 + b; };
+      auto lane_of = [](int b, int jj, int i) {
+        return i == b ? 16 + b * 8 + jj : (jj >> 2) * 8 + (jj & 3) * 2 + b;
+      };
       srcL = ih ? lane_of(bb, j, 0) : (bb ? lane_of(0, j, 1) : lane);
       srcR = ih ? (bb ? lane : lane_of(1, j, 0)) : lane_of(bb, j, 1);
     }

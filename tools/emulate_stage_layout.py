@@ -43,19 +43,22 @@ def tma(smem, dst, src, box, coord, swizzle):
                     smem[a // 8] = src[cb + b, ck + k, cj + j, ci + i]
 
 
-EDGE_HI = False  # -DMARCH_EDGE_HI: lane = edge * 16 + j * 2 + bb
+EDGE_HI = False  # -DMARCH_EDGE_HI: edge lanes 16 + bb * 8 + j, inner lanes (j >> 2) * 8 + (j & 3) * 2 + bb
 
 
 def lane_fields(lane):
     if EDGE_HI:
-        bb, j, edge = lane & 1, (lane >> 1) & 7, lane >> 4
-        return bb, j, (bb if edge else 1 - bb)
+        if lane >> 4:
+            bb = (lane >> 3) & 1
+            return bb, lane & 7, bb
+        bb = lane & 1
+        return bb, ((lane >> 3) & 1) * 4 + ((lane >> 1) & 3), 1 - bb
     return lane >> 4, (lane >> 1) & 7, lane & 1
 
 
 def lane_of(bb, j, ih):
     if EDGE_HI:
-        return (16 if ih == bb else 0) + j * 2 + bb
+        return 16 + bb * 8 + j if ih == bb else (j >> 2) * 8 + (j & 3) * 2 + bb
     return bb * 16 + j * 2 + ih
 
 
@@ -151,13 +154,45 @@ def run(P, jlx):
     return wrong, conflicts, loads, L["BYTES"]
 
 
+def halo_wavefronts(P=4):
+    """wavefronts of the five i-face LDS.128 of one cube plane: per 8-lane phase, the largest number of
+    DISTINCT 16-byte addresses that fall on one granule; a phase without an active lane costs nothing.
+    Product numbering: every lane loads (pairs broadcast); EDGE_HI: only the edge lanes do."""
+    L = layout(P, False)
+    total = 0
+    for d in range(-R, R + 1):
+        addrs = []
+        for lane in range(32):
+            bb, j, ih = lane_fields(lane)
+            if EDGE_HI and ih != bb:
+                addrs.append(None)
+                continue
+            jj = j + d
+            if 0 <= jj < 8:
+                a = (L["IR"] if bb else L["IL"]) + jj * HW * 8
+            elif jj < 0:
+                a = (L["XRL"] if bb else L["XLL"]) + (jj + R) * HW * 8
+            else:
+                a = (L["XRH"] if bb else L["XLH"]) + (jj - 8) * HW * 8
+            addrs.append(a)
+        for ph in range(4):
+            act = set(x >> 4 for x in addrs[8 * ph: 8 * ph + 8] if x is not None)
+            if act:
+                g = [x & 7 for x in act]
+                total += max(g.count(v) for v in set(g))
+    return total
+
+
 def main_edge():
     global EDGE_HI
     for flag in (False, True):
         EDGE_HI = flag
         bad, edge = check_shuffles()
-        w, c, n, _ = run(4, False)
         quarters = sorted(set(x >> 3 for x in edge))
+        print("   i-face loads: %d wavefronts per plane" % halo_wavefronts())
+        w, c, n, _ = run(4, True)
+        print("   with the swizzled -j face: wrong quads %d, %d extra wavefronts over %d LDS.128" % (w, c, n))
+        w, c, n, _ = run(4, False)
         print("edge lanes high %-5s: wrong shuffle sources %d, wrong quads %d, %d extra wavefronts over %d LDS.128, "
               "edge lanes sit in quarter-warps %s" % (flag, bad, w, c, n, quarters))
     EDGE_HI = False
