@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- fp64 GStencil/s of the brick stencil hot path on N B200s (one rank per GPU).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload weak125|weak7|weak13|weak25]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload weak125|weak7|weak13|weak25|strong125|strong7]
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference ...      # the reference's own CPU path (oracle/_ref)
 
@@ -9,8 +9,24 @@ One "step" is the hot loop of the reference's weak driver (weak/main.cu:246-287)
 exchange of the 512^3 subdomain each GPU owns, then ST_ITER stencil sweeps (4 for the 125-point
 cube, 8 for the 7-point star).  value = interior points x sweeps x ranks / time, in GStencil/s
 (weak/main.cu:315-317).  Prints ONE JSON line (rank 0).
+
+What the line carries beyond the contract keys:
+  parity     before anything is timed, at EVERY N: one bare halo exchange and two weak steps (7- and
+             125-point) on a small subdomain per rank through the same WeakSubdomain code the timed
+             loop uses, gathered to rank 0 and compared with the oracle's BrickDecomp::exchange
+             restatement (bit-exact) and with the global periodic array computation (<= 1e-12).
+             The oracle is used here as the checker only.  A failure exits non-zero.
+  roofline   the dominant kernel (one sweep over the 66^3-brick grid): `frac` counts the bytes the
+             launch really moves (ghost bricks included, = DRAM utilisation, cross-checked by ncu
+             dram bytes), `frac_interior` counts only the 512^3 interior points SURVEY.md 8(d)
+             calls algorithmic (ghost-brick recompute is overhead).
+  kernels    the same two fractions for every stencil of the path (7/13/25/125-point).
+  strong     BASELINE.json configs[4] at this N: 1024^3 in 128^3 subdomains, 125-point, a few steps.
+  cpu_baseline  N = 1 only: the reference's codegen brick kernel (oracle/_ref) on all host cores,
+             full 512^3 sweeps.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -27,6 +43,9 @@ WORKLOADS = {"weak125": 125, "weak7": 7, "weak13": 13, "weak25": 25, "strong125"
 SUBDOMAIN = (512, 512, 512)
 STRONG_DOM, STRONG_SDOM = 1024, 128  # BASELINE.json configs[4]: 1024^3 global grid in 128^3 subdomains
 BYTES_PER_POINT = 16.0  # one 8-byte read + one 8-byte write per point per sweep
+ST_ITER = {125: 4, 7: 8, 13: 4, 25: 2}  # stencils/fake.h:39-344 (GZ / radius)
+REL_TOL = 1e-12  # BASELINE.json north_star: stencil output vs the reference CPU path
+PARITY_DIMS = (64, 64, 64)
 
 
 def measured_peak():
@@ -36,6 +55,47 @@ def measured_peak():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:  # noqa: BLE001
         return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def kernel_source_hash():
+    """sha1 over the CUDA sources of the sweep kernels: ties profiles/traffic.json (ncu dram bytes)
+    to the kernel version that is actually benchmarked."""
+    h = hashlib.sha1()
+    d = os.path.join(ROOT, "bricklib_b200", "csrc")
+    for name in ("march_dev.cuh", "march_steps.cuh", "stencil_march.cu"):
+        with open(os.path.join(d, name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic(which):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
+    capture of THIS kernel version, else None (a capture of another version is not reported)."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(tpath) as f:
+            t = json.load(f)
+    except Exception:  # noqa: BLE001
+        return None, "no profiles/traffic.json"
+    if t.get("kernel_source_hash") != kernel_source_hash():
+        return None, "profiles/traffic.json was captured from another kernel version (%s)" % t.get("kernel_source_hash")
+    return t.get(str(which)), t.get("source")
+
+
+def dims_create(nnodes, ndims=3):
+    """MPI_Dims_create for the process counts of one box (weak/args.cpp:105-130): 8 -> 2x2x2,
+    4 -> 2x2x1, 2 -> 2x1x1.  Pure Python so that the reference arm needs nothing of the product."""
+    dims = [1] * ndims
+    n, f = nnodes, 2
+    factors = []
+    while n > 1:
+        while n % f == 0:
+            factors.append(f)
+            n //= f
+        f += 1
+    for p in sorted(factors, reverse=True):
+        dims[dims.index(min(dims))] *= p
+    return sorted(dims, reverse=True)
 
 
 class ClockSampler(threading.Thread):
@@ -71,50 +131,76 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
-def cpu_reference_rate(which, budget_s=15.0, dims=(256, 256, 256)):
+# ------------------------------------------------------------------------------------------
+# CPU legs: the reference's own code (oracle/_ref).  Nothing of bricklib_b200's library is loaded.
+
+def use_all_host_threads():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to every rank; the CPU legs must use the
+    host's cores whatever the launcher exported.  Sets the OpenMP thread count of THIS thread's
+    parallel regions to the size of the process's affinity mask (libgomp is the runtime
+    oracle/_ref links) and returns it."""
+    import ctypes
+    n = len(os.sched_getaffinity(0))
+    os.environ["OMP_NUM_THREADS"] = str(n)  # for a runtime that has not started yet
+    ctypes.CDLL("libgomp.so.1", mode=ctypes.RTLD_GLOBAL).omp_set_num_threads(n)
+    return n
+
+
+def synth_uniform(n, seed):
+    """bricklib_b200/synth.py is pure numpy (the counter-based U[0,1) generator of
+    include/bricks/multiarray.h); importing it does not load the CUDA library."""
+    from bricklib_b200 import synth
+    return synth.uniform(n, seed=seed)
+
+
+def cpu_reference_rate(which, budget_s=15.0, dims=SUBDOMAIN):
     """The reference's own CPU brick kernel (codegen, OpenMP, all host threads; oracle/_ref) on a
     bounded sample of the workload: full sweeps over a `dims` subdomain incl. ghost bricks."""
     from oracle import oracle as O
     from oracle import refload as R
     if not R.available():
         raise RuntimeError("oracle/_ref is not built for this host")
+    threads = use_all_host_threads()
+    if R.max_threads() != threads:
+        raise RuntimeError("OpenMP runs %d threads, the affinity mask has %d" % (R.max_threads(), threads))
     dec = O.Decomp(dims, 8)
     n = dec.nbricks * 512
     a, b = R.aligned_empty(n), R.aligned_empty(n)
-    from bricklib_b200 import synth
-    a[:] = synth.uniform(n, seed=1)
+    a[:] = synth_uniform(n, 1)
     b[:] = 0.0
     blist = dec.grid.reshape(-1)
-    t1 = R.brick_sweep_timed(which, dec.adj, blist, a, b, 512, None, 1)
+    t1 = R.brick_sweep_timed(which, dec.adj, blist, a, b, 512, None, 2)
     reps = int(max(2, min(400, budget_s / max(t1, 1e-4))))
     reps += reps & 1
     t = R.brick_sweep_timed(which, dec.adj, blist, a, b, 512, None, reps)
     pts = float(np.prod(dims))
-    return {"value": pts / t * 1e-9, "unit": "GStencil/s", "cores": R.max_threads(), "kind": "reference",
+    return {"value": pts / t * 1e-9, "unit": "GStencil/s", "cores": threads, "kind": "reference",
+            "subdomain": list(dims),
             "sample": "%d sweeps of the %d-point stencil over one %dx%dx%d subdomain (+ghost bricks), "
-                      "reference codegen brick kernel (%s), %.1f ms/sweep" % (reps, which if which else 7, dims[0], dims[1],
-                                                                               dims[2], R.vsvec(), t * 1e3)}
+                      "reference codegen brick kernel (%s) under OpenMP with %d threads, %.1f ms/sweep"
+                      % (reps, which if which else 7, dims[0], dims[1], dims[2], R.vsvec(), threads, t * 1e3)}
 
 
 def run_reference(args, which):
     """--impl reference: the reference's own CPU implementation of the path (oracle/_ref: its
-    codegen brick kernel under OpenMP, all host threads) on this arm's metric/config; each step
-    is a bounded sample (a 256^3 subdomain) of the workload.  Rank 0 only."""
+    codegen brick kernel under OpenMP, all host threads) on this arm's metric/config.  A step is
+    what one rank of the workload does: one periodic self exchange + ST_ITER sweeps over the
+    512^3 subdomain (strong: over one 128^3 subdomain).  Rank 0 only; maps no product library."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     from oracle import oracle as O
     from oracle import refload as R
-    from bricklib_b200 import capi, synth
-    st_iter = capi.ST_ITER[which]
+    threads = use_all_host_threads()
+    st_iter = ST_ITER[which]
     strong = args.workload.startswith("strong")
     # strong: a step of the sample = one subdomain of the decomposition (its 26 periodic neighbours
     # are copies of itself, as in strong/main.cu on one rank with one subdomain)
-    dims = (args.sdom,) * 3 if strong else (256, 256, 256)
+    dims = (args.sdom,) * 3 if strong else SUBDOMAIN
     dec = O.Decomp(dims, 8)
     n = dec.nbricks * 512
     a, b = R.aligned_empty(n), R.aligned_empty(n)
-    a[:] = synth.uniform(n, seed=1)
+    a[:] = synth_uniform(n, 1)
     b[:] = 0.0
     blist = np.ascontiguousarray(dec.grid.reshape(-1), np.uint32)
     adjf = np.ascontiguousarray(dec.adj.reshape(-1), np.uint32)
@@ -137,14 +223,17 @@ def run_reference(args, which):
         step()
     dt = (time.perf_counter() - t0) / args.steps
     val = float(np.prod(dims)) * st_iter / dt * 1e-9
+    sample = ("%d steps x (periodic self exchange + %d sweeps) over one %d^3 subdomain (+ghost bricks): what one rank "
+              "of the workload does per step; codegen brick kernel %s under OpenMP with %d threads (affinity mask %d, "
+              "launcher exported OMP_NUM_THREADS=%s)"
+              % (args.steps, st_iter, dims[0], R.vsvec(), R.max_threads(), threads, args.launcher_omp))
     line = {"impl": "reference", "metric": "fp64 GStencil/s", "value": val, "unit": "GStencil/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
             "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": make_config(which, args.gpus, (args.dom, args.sdom) if strong else None),
             "cpu_baseline": {"value": val, "unit": "GStencil/s", "cores": R.max_threads(), "kind": "reference",
-                             "sample": "%d steps x (self exchange + %d sweeps) over a %d^3 subdomain, codegen brick "
-                                       "kernel %s under OpenMP" % (args.steps, st_iter, dims[0], R.vsvec())},
+                             "subdomain": list(dims), "sample": sample},
             "e2e": {"value": val, "unit": "GStencil/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -152,41 +241,56 @@ def run_reference(args, which):
 
 
 def make_config(which, ngpus, strong=None):
-    from bricklib_b200 import capi
     if strong:
         dom, sdom = strong
         g = sdom // 8 + 2
         return {"workload": ("strong-scaling step: %d-point %s stencil, fp64, %d^3 global periodic grid in %d^3 subdomains "
                              "(Z-Morton ids, contiguous ranges per GPU), 8x8x8 bricks, 1 halo exchange + %d sweeps per step"
-                             % (which, "cube" if which == 125 else "star", dom, sdom, capi.ST_ITER[which])),
+                             % (which, "cube" if which == 125 else "star", dom, sdom, ST_ITER[which])),
                 "global_grid": [dom] * 3, "subdomain": [sdom] * 3, "subdomains": (dom // sdom) ** 3, "brick": [8, 8, 8],
-                "ghost_depth": 8, "st_iter": capi.ST_ITER[which],
+                "ghost_depth": 8, "st_iter": ST_ITER[which],
                 "l2_policy": "working set %.2f GB per sweep over all GPUs >> 126 MB L2 (inputs larger than L2)"
                              % ((dom // sdom) ** 3 * g ** 3 * 4096 * 2 / 1e9)}
     return {"workload": workload_name(which), "subdomain_per_gpu": list(SUBDOMAIN), "brick": [8, 8, 8],
-            "ghost_depth": 8, "st_iter": capi.ST_ITER[which], "process_grid": capi.cart_dims(ngpus),
+            "ghost_depth": 8, "st_iter": ST_ITER[which], "process_grid": dims_create(ngpus),
             "l2_policy": "working set 2.36 GB per GPU per sweep >> 126 MB L2 (inputs larger than L2)"}
 
 
 def workload_name(which):
     return ("weak-scaling step: %d-point %s stencil, fp64, 512^3 subdomain per GPU in 8x8x8 bricks "
             "(BrickDecomp layout), 1 periodic halo exchange + %d sweeps per step"
-            % (which, "cube" if which == 125 else "star", {125: 4, 7: 8, 13: 4, 25: 2}[which]))
+            % (which, "cube" if which == 125 else "star", ST_ITER[which]))
 
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
 
 def kernel_probe(ctx, sub, which, reps=10):
     """Average duration of the dominant kernel (one full-grid sweep, 66^3 bricks), CUDA events on
     the stream it is launched on, back to back ping-pong launches."""
-    from bricklib_b200 import capi
     for _ in range(2):
-        sub.plan_full.stencil(which, sub.d_a, sub.d_b, 512, 512)
-        sub.plan_full.stencil(which, sub.d_b, sub.d_a, 512, 512)
+        sub.sweep_full(which, sub.d_a, sub.d_b)
+        sub.sweep_full(which, sub.d_b, sub.d_a)
     ctx.timer_start(1)
     for _ in range(reps):
-        sub.plan_full.stencil(which, sub.d_a, sub.d_b, 512, 512)
-        sub.plan_full.stencil(which, sub.d_b, sub.d_a, 512, 512)
+        sub.sweep_full(which, sub.d_a, sub.d_b)
+        sub.sweep_full(which, sub.d_b, sub.d_a)
     ctx.timer_stop(1)
     return ctx.timer_ms(1) / (2 * reps)
+
+
+def kernel_fractions(ms, gdims, dims, peak):
+    """The two ways of charging a sweep against the HBM roof (module docstring)."""
+    launch_pts = float(gdims[0] * gdims[1] * gdims[2] * 512)
+    interior = float(np.prod(dims))
+    achieved = launch_pts * BYTES_PER_POINT / (ms * 1e-3) * 1e-9
+    achieved_int = interior * BYTES_PER_POINT / (ms * 1e-3) * 1e-9
+    return {"achieved": achieved, "frac": achieved / peak, "achieved_interior": achieved_int,
+            "frac_interior": achieved_int / peak, "frac_of_8TBps_nominal": achieved / 8000.0,
+            "frac_interior_of_8TBps_nominal": achieved_int / 8000.0,
+            "interior_gstencil_per_s_kernel_only": interior / (ms * 1e-3) * 1e-9,
+            "algorithmic_bytes_per_launch": launch_pts * BYTES_PER_POINT,
+            "algorithmic_bytes_interior": interior * BYTES_PER_POINT}
 
 
 def init_ranks(args):
@@ -228,26 +332,134 @@ def init_ranks(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    return ctx, rank, world, local, dist, barrier, max_over_ranks
+    def gather(arr):
+        """every rank's numpy array (same shape on all ranks) on every rank"""
+        if world == 1:
+            return [arr]
+        t = torch.from_numpy(np.ascontiguousarray(arr)).cuda()
+        outs = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(outs, t)
+        return [o.cpu().numpy() for o in outs]
+
+    return ctx, rank, world, local, dist, barrier, max_over_ranks, gather
+
+
+def parity_block(ctx, rank, world, gather, overlap, early, shift):
+    """Correctness evidence inside the run the driver times (module docstring).  Same code path as
+    the timed loop -- WeakSubdomain over the C ABI, NCCL between the ranks -- on PARITY_DIMS per
+    rank.  Checked on rank 0 against (1) the oracle's restatement of BrickDecomp::exchange
+    (include/brick-mpi.h:466-495) on `world` virtual ranks, bit for bit, and (2) the stencil applied
+    to the assembled GLOBAL periodic array (what weak/main.cu:321-323 checks per rank)."""
+    from bricklib_b200 import capi, weak
+    dims = PARITY_DIMS
+    procdims = capi.cart_dims(world)
+    out = {"nranks": world, "subdomain_per_rank": list(dims), "process_grid": list(procdims), "tolerance": REL_TOL,
+           "schedule": {"overlap": overlap, "early_exchange": early, "shift_exchange": shift},
+           "checker": "oracle/oracle.py exchange() (bit-exact) and the global periodic array through the oracle's "
+                      "array stencil"}
+    ok = True
+    O = odec = None
+    if rank == 0:
+        from oracle import oracle as O  # the checker; never on the measured path
+        odec = O.Decomp(dims, 8)
+
+    # (1) one bare exchange of a random storage
+    sub = weak.WeakSubdomain(ctx, dims, 7, rank=rank, procdims=procdims, shift=shift)
+    nb = sub.dec.nbricks
+    f = capi.uniform(nb * 512, seed=9000 + rank)
+    sub.upload(f)
+    sub.exchange_only()
+    ctx.sync()
+    got = gather(sub.download())
+    fields = gather(f)
+    sub.close()
+    if rank == 0:
+        exp = O.exchange([x.copy() for x in fields], odec, procdims)
+        bit = all(np.array_equal(g.view(np.uint64), e.view(np.uint64)) for g, e in zip(got, exp))
+        changed = int(sum(np.count_nonzero(g.view(np.uint64) != x.view(np.uint64)) for g, x in zip(got, fields)))
+        out["exchange_bitexact"] = bool(bit)
+        out["exchange_words_moved"] = changed
+        ok = ok and bit and changed > 0
+
+    # (2) two steps of the 7- and the 125-point stencil == periodic sweeps of the global array
+    t = [x // 8 + 2 for x in dims]
+    ext = [t[0] * 8, t[1] * 8, t[2] * 8]
+    pk, pj, pi = procdims
+
+    def where(r):  # physical block of rank r: populate() puts the "+d" neighbour at coordinate - 1
+        c = capi.cart_coords(r, procdims)
+        return [(-c[a]) % procdims[a] for a in range(3)]
+
+    errs = {}
+    nsteps = 2
+    for which in (7, 125):
+        sub = weak.WeakSubdomain(ctx, dims, which, rank=rank, procdims=procdims, shift=shift)
+        f0 = sub.host_field()
+        sub.upload(f0)
+        for _ in range(nsteps):
+            sub.step(overlap=overlap, early=early)
+        ctx.sync()
+        res = gather(sub.download())
+        f0s = gather(f0)
+        sub.close()
+        if rank == 0:
+            def interior_of(field):
+                a = np.zeros((ext[2], ext[1], ext[0]))
+                O.copy_brick(False, ext, [0, 0, 0], [0, 0, 0], a, odec.grid, field)
+                return a[8:-8, 8:-8, 8:-8]
+            d2, d1, d0 = dims[2], dims[1], dims[0]
+            glob = np.zeros((d2 * pk, d1 * pj, d0 * pi))
+            for r in range(world):
+                ck, cj, ci = where(r)
+                glob[d2 * ck:d2 * (ck + 1), d1 * cj:d1 * (cj + 1), d0 * ci:d0 * (ci + 1)] = interior_of(f0s[r])
+            cur = glob
+            for _ in range(nsteps * ST_ITER[which]):
+                pad = np.pad(cur, 8, mode="wrap")
+                o = np.zeros_like(pad)
+                O.array_sweep(which, pad, o, (8, 8 + cur.shape[0], 8, 8 + cur.shape[1], 8, 8 + cur.shape[2]))
+                cur = o[8:-8, 8:-8, 8:-8].copy()
+            worst = 0.0
+            for r in range(world):
+                ck, cj, ci = where(r)
+                e = cur[d2 * ck:d2 * (ck + 1), d1 * cj:d1 * (cj + 1), d0 * ci:d0 * (ci + 1)]
+                g = interior_of(res[r])
+                worst = max(worst, float(np.max(np.abs(g - e) / np.maximum(np.abs(e), 1e-300))))
+            errs[str(which)] = worst
+            ok = ok and worst <= REL_TOL
+    if rank == 0:
+        out["step_max_rel_err"] = errs
+        out["steps_checked"] = nsteps
+        out["ok"] = bool(ok)
+    return out
 
 
 def run_gpu(args, which):
     from bricklib_b200 import capi, weak
-    ctx, rank, world, local, dist, barrier, max_over_ranks = init_ranks(args)
+    ctx, rank, world, local, dist, barrier, max_over_ranks, gather = init_ranks(args)
 
     procdims = capi.cart_dims(world)
     st_iter = capi.ST_ITER[which]
+    # start the next step's exchange behind the last sweep's skin bricks: pays off when the
+    # exchange crosses NVLink (N > 1); on one GPU the plain schedule is faster (measured)
+    overlap = not args.no_overlap
+    early = (not args.no_early) and world > 1 and overlap
+
+    parity = None
+    if not args.no_parity:
+        parity = parity_block(ctx, rank, world, gather, overlap, early, args.shift_exchange)
+        bad = 0.0 if (rank != 0 or parity["ok"]) else 1.0
+        if max_over_ranks(bad) > 0:
+            if rank == 0:
+                print(json.dumps({"error": "parity check failed", "parity": parity}), flush=True)
+            return 3
+
     sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims, shift=args.shift_exchange)
-    nb = sub.dec.nbricks
     field = sub.host_field()
     sub.upload(field)
 
     # ---- device-resident timing: W warm-up steps, then exactly K steps
-    # start the next step's exchange behind the last sweep's skin bricks: pays off when the
-    # exchange crosses NVLink (N > 1); on one GPU the plain schedule is faster (measured)
-    early = (not args.no_early) and world > 1
     for _ in range(max(args.warmup, 3)):
-        sub.step(overlap=not args.no_overlap, early=early)
+        sub.step(overlap=overlap, early=early)
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
@@ -255,7 +467,7 @@ def run_gpu(args, which):
     n0 = capi.launch_count()
     ctx.timer_start(0)
     for _ in range(args.steps):
-        sub.step(overlap=not args.no_overlap, early=early)
+        sub.step(overlap=overlap, early=early)
     ctx.stream_wait(capi.STREAM_COMPUTE, capi.STREAM_COMM)  # nothing of the K steps is left in flight
     ctx.timer_stop(0)
     ms = ctx.timer_ms(0)
@@ -269,28 +481,34 @@ def run_gpu(args, which):
     # ---- dominant kernel: one full-grid sweep
     sub.upload(field)
     k_ms = kernel_probe(ctx, sub, which)
-    g = sub.gdims
-    launch_pts = float(g[0] * g[1] * g[2] * 512)
-    achieved = launch_pts * BYTES_PER_POINT / (k_ms * 1e-3) * 1e-9
     peak, peak_src = measured_peak()
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        try:
-            traffic = json.load(open(tpath)).get(str(which))
-        except Exception:  # noqa: BLE001
-            traffic = None
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "march_kernel (one sweep over 66^3 bricks)",
-                "kernel_ms": k_ms, "algorithmic_bytes_per_launch": launch_pts * BYTES_PER_POINT,
-                "interior_gstencil_per_s_kernel_only": float(np.prod(SUBDOMAIN)) / (k_ms * 1e-3) * 1e-9,
-                "frac_of_8TBps_nominal": achieved / 8000.0}
+    traffic, traffic_src = ncu_traffic(which)
+    roofline = {"bound": "hbm", "peak": peak, "unit": "GB/s", "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": peak_src, "kernel": "march_kernel (one sweep over 66^3 bricks)", "kernel_ms": k_ms,
+                "kernel_source_hash": kernel_source_hash(),
+                "definition": "frac = 16 B x every point the launch updates (66^3 bricks, ghost bricks included) / "
+                              "kernel_ms / peak = DRAM utilisation; frac_interior = 16 B x 512^3 interior points / "
+                              "kernel_ms / peak (SURVEY.md 8d: ghost-brick recompute is overhead, not counted)"}
+    roofline.update(kernel_fractions(k_ms, sub.gdims, SUBDOMAIN, peak))
 
     # ---- end to end through the C ABI with HOST buffers: H2D of the step's input field from
     # pinned memory, exchange + ST_ITER sweeps, D2H of the step's result
     e2e = end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step)
-    # the sampler ran through every timed region (device-resident steps, kernel probe, e2e steps)
+    kernels = None
+    if not args.no_all_stencils:
+        kernels = all_stencils(ctx, sub, peak)
+    # the sampler ran through every timed region (device-resident steps, kernel probes, e2e steps)
     clocks = sampler.summary() if sampler else None
+    exchange_bytes = sub.exchange_bytes
+    exchange_kind = sub.exchange_kind
+    sub.close()
+
+    strong = None
+    if not args.no_strong:
+        try:
+            strong = strong_block(ctx, rank, world, barrier, max_over_ranks, args, peak)
+        except Exception as e:  # noqa: BLE001 -- the extra block must not take the headline line down
+            strong = {"error": repr(e)}
 
     line = None
     if rank == 0:
@@ -298,26 +516,66 @@ def run_gpu(args, which):
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": make_config(which, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-                "roofline": roofline,
-                "overlap": not args.no_overlap, "early_exchange": early and not args.no_overlap,
-                "exchange_bytes_per_step_per_gpu": sub.exchange_bytes,
-                "exchange": "shift (3 stages, 6 messages)" if args.shift_exchange else "direct (one message per region)"}
-        if not args.no_cpu:
+                "roofline": roofline, "parity": parity,
+                "overlap": overlap, "early_exchange": early,
+                "exchange_bytes_per_step_per_gpu": exchange_bytes, "exchange": exchange_kind}
+        if kernels is not None:
+            line["kernels"] = kernels
+        if strong is not None:
+            line["strong"] = strong
+        if world == 1 and not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_reference_rate(which, budget_s=args.cpu_seconds)
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"value": None, "unit": "GStencil/s", "cores": 0, "kind": "reference",
                                         "sample": "unavailable: %r" % (e,)}
-        if args.all_stencils:
-            line["kernels"] = all_stencils(ctx, sub, peak)
+        elif world > 1:
+            line["cpu_baseline"] = None  # timed at N = 1 only (the other ranks' host threads would compete)
     if world > 1:
         dist.barrier()
     if line:
         print(json.dumps(line), flush=True)
-    sub.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def strong_block(ctx, rank, world, barrier, max_over_ranks, args, peak, which=125, steps=5):
+    """BASELINE.json configs[4] next to the headline: strong scaling of the 125-point stencil,
+    1024^3 in 128^3 subdomains shared out over the ranks, device-resident, `steps` steps."""
+    from bricklib_b200 import capi, strong
+    dom, sdom = args.dom, args.sdom
+    sd = strong.StrongDomain(ctx, dom, sdom, which, rank=rank, nranks=world)
+    sd.upload()
+    for _ in range(3):
+        sd.step(overlap=not args.no_overlap)
+    barrier()
+    ctx.timer_start(3)
+    for _ in range(steps):
+        sd.step(overlap=not args.no_overlap)
+    ctx.timer_stop(3)
+    ms = ctx.timer_ms(3)
+    barrier()
+    ms_step = max_over_ranks(ms) / steps
+    for _ in range(2):
+        sd.sweep_full(which, sd.in_a, sd.in_b)
+        sd.sweep_full(which, sd.in_b, sd.in_a)
+    ctx.timer_start(3)
+    for _ in range(3):
+        sd.sweep_full(which, sd.in_a, sd.in_b)
+        sd.sweep_full(which, sd.in_b, sd.in_a)
+    ctx.timer_stop(3)
+    k_ms = ctx.timer_ms(3) / 6
+    barrier()
+    g = sd.dec.gdims
+    fr = kernel_fractions(k_ms, [g[0] * sd.nsub, g[1], g[2]], (sdom * sd.nsub, sdom, sdom), peak)
+    out = {"workload": make_config(which, world, (dom, sdom))["workload"],
+           "value": float(dom) ** 3 * capi.ST_ITER[which] / (ms_step * 1e-3) * 1e-9, "unit": "GStencil/s",
+           "ms_per_step": ms_step, "steps": steps, "warmup": 3, "scaling": "strong", "subdomains_rank0": sd.nsub,
+           "exchange_bytes_sent_rank0": sd.exchange_bytes, "kernel_ms": k_ms, "frac": fr["frac"],
+           "frac_interior": fr["frac_interior"], "ghost_overhead": float(g[0] * g[1] * g[2] * 512) / float(sdom) ** 3}
+    sd.close()
+    return out
 
 
 def run_gpu_strong(args, which):
@@ -325,7 +583,7 @@ def run_gpu_strong(args, which):
     subdomains are shared out over the ranks.  value = dom^3 x ST_ITER / time of a step."""
     import ctypes as C
     from bricklib_b200 import capi, strong
-    ctx, rank, world, local, dist, barrier, max_over_ranks = init_ranks(args)
+    ctx, rank, world, local, dist, barrier, max_over_ranks, gather = init_ranks(args)
     dom, sdom = args.dom, args.sdom
     st_iter = capi.ST_ITER[which]
     sd = strong.StrongDomain(ctx, dom, sdom, which, rank=rank, nranks=world)
@@ -367,24 +625,21 @@ def run_gpu_strong(args, which):
     ctx.h2d(sd.d_a, h_in)
     ctx.sync()
     for _ in range(2):
-        sd.plan_full.stencil(which, sd.in_a, sd.in_b)
-        sd.plan_full.stencil(which, sd.in_b, sd.in_a)
+        sd.sweep_full(which, sd.in_a, sd.in_b)
+        sd.sweep_full(which, sd.in_b, sd.in_a)
     reps = 5
     ctx.timer_start(1)
     for _ in range(reps):
-        sd.plan_full.stencil(which, sd.in_a, sd.in_b)
-        sd.plan_full.stencil(which, sd.in_b, sd.in_a)
+        sd.sweep_full(which, sd.in_a, sd.in_b)
+        sd.sweep_full(which, sd.in_b, sd.in_a)
     ctx.timer_stop(1)
     k_ms = ctx.timer_ms(1) / (2 * reps)
     g = sd.dec.gdims
-    launch_pts = float(g[0] * g[1] * g[2] * 512) * sd.nsub
-    achieved = launch_pts * BYTES_PER_POINT / (k_ms * 1e-3) * 1e-9
     peak, peak_src = measured_peak()
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src,
+    roofline = {"bound": "hbm", "peak": peak, "unit": "GB/s", "traffic": None, "peak_source": peak_src,
                 "kernel": "march_kernel (one sweep over %d subdomains x %d^3 bricks, one launch)" % (sd.nsub, g[0]),
-                "kernel_ms": k_ms, "algorithmic_bytes_per_launch": launch_pts * BYTES_PER_POINT,
-                "ghost_overhead": float(g[0] * g[1] * g[2] * 512) / float(sdom) ** 3}
+                "kernel_ms": k_ms, "ghost_overhead": float(g[0] * g[1] * g[2] * 512) / float(sdom) ** 3}
+    roofline.update(kernel_fractions(k_ms, [g[0] * sd.nsub, g[1], g[2]], (sdom * sd.nsub, sdom, sdom), peak))
 
     # ---- end to end with HOST buffers: H2D of every local subdomain, step, D2H of every result
     esteps = max(1, min(args.steps, args.e2e_steps))
@@ -418,8 +673,8 @@ def run_gpu_strong(args, which):
                 "config": make_config(which, world, (dom, sdom)), "clocks": clocks, "e2e": e2e,
                 "gpu_launches": int(launches), "roofline": roofline, "overlap": not args.no_overlap,
                 "subdomains_rank0": sd.nsub, "exchange_bytes_sent_rank0": sd.exchange_bytes,
-                "local_links_rank0": len(sd.plan.links)}
-        if not args.no_cpu:
+                "local_links_rank0": sd.nlinks}
+        if world == 1 and not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_reference_rate(which, budget_s=args.cpu_seconds, dims=(sdom,) * 3)
             except Exception as e:  # noqa: BLE001
@@ -462,9 +717,11 @@ def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
               and np.array_equal(h_out0[:4096], h_out1[:4096]))
     for p in ptrs:
         capi.check(capi.lib().bricks_host_free(p))
+    per_dir = sub.host_step_bytes / (ms / steps * 1e-3) * 1e-9
     return {"value": pts_step / (ms / steps * 1e-3) * 1e-9, "unit": "GStencil/s",
             "h2d_bytes_per_step": sub.host_step_bytes, "d2h_bytes_per_step": sub.host_step_bytes,
             "ms_per_step": ms / steps, "steps": steps, "result_finite": ok,
+            "host_link_gbs_per_direction_per_gpu": per_dir,
             "what": "per step and GPU: H2D of the input field (all owned bricks; ghost bricks are filled by the "
                     "exchange) from pinned host memory, exchange + sweeps, D2H of the result field (all owned bricks); "
                     "steps software-pipelined over two device buffer sets and two copy streams (upload n+1 and "
@@ -474,14 +731,14 @@ def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
 def all_stencils(ctx, sub, peak):
     """Kernel-only numbers for every stencil of the path on the same 66^3-brick grid."""
     out = {}
-    g = sub.gdims
-    launch_pts = float(g[0] * g[1] * g[2] * 512)
     for w in (7, 13, 25, 125):
         sub.upload(sub.host_field())
         ms = kernel_probe(ctx, sub, w, reps=5)
-        gbs = launch_pts * BYTES_PER_POINT / (ms * 1e-3) * 1e-9
-        out[str(w)] = {"ms_per_sweep": ms, "achieved_gbs": gbs, "frac_of_measured_peak": gbs / peak,
-                       "interior_gstencil_per_s": float(np.prod(SUBDOMAIN)) / (ms * 1e-3) * 1e-9}
+        fr = kernel_fractions(ms, sub.gdims, SUBDOMAIN, peak)
+        out[str(w)] = {"ms_per_sweep": ms, "achieved_gbs": fr["achieved"], "frac_of_measured_peak": fr["frac"],
+                       "frac_interior": fr["frac_interior"],
+                       "frac_interior_of_8TBps_nominal": fr["frac_interior_of_8TBps_nominal"],
+                       "interior_gstencil_per_s": fr["interior_gstencil_per_s_kernel_only"]}
     return out
 
 
@@ -499,10 +756,14 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=10)
-    ap.add_argument("--all-stencils", action="store_true", help="add kernel-only numbers for 7/13/25/125-point")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity block in front of the timed loop")
+    ap.add_argument("--no-all-stencils", action="store_true", help="skip the kernel-only numbers for 7/13/25/125-point")
+    ap.add_argument("--all-stencils", action="store_true", help="(the default now; kept for old command lines)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling block (1024^3 in 128^3, 125-point)")
     ap.add_argument("--dom", type=int, default=STRONG_DOM, help="strong workloads: global grid edge")
     ap.add_argument("--sdom", type=int, default=STRONG_SDOM, help="strong workloads: subdomain edge")
     args = ap.parse_args()
+    args.launcher_omp = os.environ.get("OMP_NUM_THREADS", "unset")
     which = WORKLOADS[args.workload]
     if args.impl == "reference":
         return run_reference(args, which)

@@ -53,6 +53,7 @@ _SIGS = {
     "bricks_timer_stop": (C.c_int, [_vp, C.c_int, C.c_int]),
     "bricks_timer_elapsed_ms": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_float)]),
     "bricks_plan_create": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint, C.c_int, _vp, _vpp]),
+    "bricks_plan_derive": (C.c_int, [_vp, C.c_int, _vp, _vpp]),
     "bricks_plan_destroy": (C.c_int, [_vp]),
     "bricks_plan_device_tables": (C.c_int, [_vp, _vpp, _vpp]),
     "bricks_stencil": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
@@ -65,10 +66,24 @@ _SIGS = {
     "bricks_array_stencil7": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "bricks_comm_unique_id": (C.c_int, [_vp]),
     "bricks_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "bricks_comm_init_config": (C.c_int, [_vp, C.c_int, C.c_int, _vp, C.c_int]),
     "bricks_comm_destroy": (C.c_int, [_vp]),
     "bricks_exchange_create": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vpp]),
     "bricks_exchange_destroy": (C.c_int, [_vp]),
     "bricks_exchange_run": (C.c_int, [_vp, _vp, C.c_int]),
+    "bricks_decomp_step_create": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_size_t, _vpp, C.c_char_p, C.c_size_t]),
+    "bricks_strong_step_create": (C.c_int, [_vp, _vp, C.c_int, _vp, _vp, C.c_size_t, _vpp, C.POINTER(C.c_size_t)]),
+    "bricks_step_boxes": (C.c_int, [_vp, C.c_uint, C.c_int, _vp, C.POINTER(C.c_int)]),
+    "bricks_step_create": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint, C.c_uint, _vpp]),
+    "bricks_step_destroy": (C.c_int, [_vp]),
+    "bricks_step_plan": (C.c_int, [_vp, C.c_int, _vpp]),
+    "bricks_step_arena": (C.c_int, [_vp, C.c_size_t, _vpp]),
+    "bricks_step_add_copy": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int]),
+    "bricks_step_add_exchange": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "bricks_step_run": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_int]),
+    "bricks_step_exchange": (C.c_int, [_vp, _vp]),
+    "bricks_step_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_int]),
+    "bricks_step_reset": (C.c_int, [_vp]),
     # include/bricks_b200_probe.h
     "bricks_probe_dfma": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
     "bricks_probe_copy": (C.c_int, [_vp, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
@@ -197,9 +212,13 @@ class Context(object):
         return ms.value
 
     # NCCL -------------------------------------------------------------------
-    def comm_init(self, rank, nranks, unique_id):
+    def comm_init(self, rank, nranks, unique_id, max_ctas=None):
+        """max_ctas: cap of the NCCL send/recv kernel's CTAs (bricks_comm_init_config); default from
+        BRICKS_NCCL_MAX_CTAS, 0 = NCCL's own choice."""
         buf = C.create_string_buffer(bytes(unique_id), 128)
-        check(lib().bricks_comm_init(self._h, rank, nranks, buf))
+        if max_ctas is None:
+            max_ctas = int(os.environ.get("BRICKS_NCCL_MAX_CTAS", "0"))
+        check(lib().bricks_comm_init_config(self._h, rank, nranks, buf, int(max_ctas)))
 
 
 def unique_id():
@@ -215,27 +234,38 @@ def launch_count():
 
 
 class Plan(object):
-    """Launch plan over boxes of the brick grid (bricks_plan_create)."""
+    """Launch plan over boxes of the brick grid (bricks_plan_create).  With `parent`, a plan over
+    other boxes of the parent's grid that shares its device tables (bricks_plan_derive; close it
+    before the parent).  `borrowed`: a handle owned by a Step."""
 
-    def __init__(self, ctx, grid, adj, boxes=None):
-        grid = np.ascontiguousarray(grid, np.uint32)
-        adj = np.ascontiguousarray(adj, np.uint32)
-        assert grid.ndim == 3 and adj.ndim == 2 and adj.shape[1] == 27
-        gd = np.array([grid.shape[2], grid.shape[1], grid.shape[0]], np.uint32)
-        if boxes is None:
-            boxes = [((0, 0, 0), tuple(int(x) for x in gd))]
-        bx = np.array([list(lo) + list(hi) for lo, hi in boxes], np.uint32)
+    def __init__(self, ctx, grid=None, adj=None, boxes=None, parent=None, borrowed=None):
         self.ctx = ctx
         self._h = C.c_void_p()
-        check(lib().bricks_plan_create(ctx._h, _np_ptr(grid), _np_ptr(gd), _np_ptr(adj), adj.shape[0],
-                                       len(boxes), _np_ptr(bx), C.byref(self._h)))
-        self.nbricks = adj.shape[0]
+        self._owned = borrowed is None
+        if borrowed is not None:
+            self._h = C.c_void_p(borrowed)
+            return
+        if parent is not None:
+            bx = np.array([list(lo) + list(hi) for lo, hi in boxes], np.uint32)
+            check(lib().bricks_plan_derive(parent._h, len(boxes), _np_ptr(bx), C.byref(self._h)))
+            self.nbricks = parent.nbricks
+        else:
+            grid = np.ascontiguousarray(grid, np.uint32)
+            adj = np.ascontiguousarray(adj, np.uint32)
+            assert grid.ndim == 3 and adj.ndim == 2 and adj.shape[1] == 27
+            gd = np.array([grid.shape[2], grid.shape[1], grid.shape[0]], np.uint32)
+            if boxes is None:
+                boxes = [((0, 0, 0), tuple(int(x) for x in gd))]
+            bx = np.array([list(lo) + list(hi) for lo, hi in boxes], np.uint32)
+            check(lib().bricks_plan_create(ctx._h, _np_ptr(grid), _np_ptr(gd), _np_ptr(adj), adj.shape[0],
+                                           len(boxes), _np_ptr(bx), C.byref(self._h)))
+            self.nbricks = adj.shape[0]
         self.ncells = int(sum(np.prod(np.array(hi) - np.array(lo)) for lo, hi in boxes))
 
     def close(self):
-        if self._h:
+        if self._h and self._owned:
             lib().bricks_plan_destroy(self._h)
-            self._h = C.c_void_p()
+        self._h = C.c_void_p()
 
     def _run(self, fn, stencil, ins, outs, in_step, out_step, coeff, stream):
         if not isinstance(ins, (list, tuple)):
@@ -298,6 +328,96 @@ class ShiftExchange(object):
         for ex in self.stages:
             ex.close()
         self.stages = []
+
+
+PLAN_FULL, PLAN_INNER, PLAN_SHELL, PLAN_OWNED, PLAN_OSKIN = range(5)
+BASE_ABS, BASE_FIELD, BASE_ARENA = 0, 1, 2
+STEP_OVERLAP, STEP_EARLY, STEP_EARLY_UNSPLIT = 1, 2, 4
+
+
+def step_boxes(gdims, which, ghost_bricks=1):
+    """the boxes of plan `which` of the library's sweep schedule (bricks_step_boxes; host only)"""
+    gd = np.array(list(gdims), np.uint32)
+    bx = np.zeros(36, np.uint32)
+    n = C.c_int()
+    check(lib().bricks_step_boxes(_np_ptr(gd), ghost_bricks, which, _np_ptr(bx), C.byref(n)))
+    return [(tuple(int(x) for x in bx[6 * b:6 * b + 3]), tuple(int(x) for x in bx[6 * b + 3:6 * b + 6]))
+            for b in range(n.value)]
+
+
+class Step(object):
+    """The sweep schedule of one rank (bricks_step_*): five box plans over one device copy of
+    grid / adj plus the communication program (copy tables and exchange plans)."""
+
+    def __init__(self, ctx, grid=None, adj=None, ghost_bricks=1, handle=None):
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        if handle is not None:  # made by Decomp.make_step
+            self._h = C.c_void_p(handle)
+            return
+        grid = np.ascontiguousarray(grid, np.uint32)
+        adj = np.ascontiguousarray(adj, np.uint32)
+        gd = np.array([grid.shape[2], grid.shape[1], grid.shape[0]], np.uint32)
+        check(lib().bricks_step_create(ctx._h, _np_ptr(grid), _np_ptr(gd), _np_ptr(adj), adj.shape[0],
+                                       ghost_bricks, C.byref(self._h)))
+
+    def plan(self, which):
+        """borrowed Plan handle, or None when the subdomain has no inner box"""
+        h = C.c_void_p()
+        if lib().bricks_step_plan(self._h, which, C.byref(h)) != 0:
+            return None
+        return Plan(self.ctx, borrowed=h.value)
+
+    def arena(self, nbytes):
+        p = C.c_void_p()
+        check(lib().bricks_step_arena(self._h, nbytes, C.byref(p)))
+        return p.value
+
+    def add_copy(self, links, src_base=BASE_ABS, dst_base=BASE_ABS):
+        """links: list of (from, to, nbytes); from / to are pointers or offsets from the base"""
+        if not links:
+            return
+        arr = (RegionLink * len(links))(*[RegionLink(s, d, n) for s, d, n in links])
+        check(lib().bricks_step_add_copy(self._h, arr, len(links), src_base, dst_base))
+
+    def add_exchange(self, ex, base=BASE_FIELD):
+        check(lib().bricks_step_add_exchange(self._h, ex._h, base, 1))
+        ex._h = C.c_void_p()  # the step owns it now
+
+    @staticmethod
+    def _ptrs(x):
+        if not isinstance(x, (list, tuple)):
+            x = [x]
+        return (C.c_void_p * len(x))(*x), len(x)
+
+    def run(self, stencil, st_iter, a, b, coeff=None, flags=STEP_OVERLAP):
+        pa, n = self._ptrs(a)
+        pb, _ = self._ptrs(b)
+        cp = None
+        if coeff is not None:
+            coeff = np.ascontiguousarray(coeff, np.float64)
+            cp = _np_ptr(coeff)
+        check(lib().bricks_step_run(self._h, stencil, st_iter, n, pa, pb, cp, flags))
+
+    def exchange(self, field0):
+        check(lib().bricks_step_exchange(self._h, C.c_void_p(field0)))
+
+    def sweep(self, which, stencil, ins, outs, coeff=None, stream=STREAM_COMPUTE):
+        pa, n = self._ptrs(ins)
+        pb, _ = self._ptrs(outs)
+        cp = None
+        if coeff is not None:
+            coeff = np.ascontiguousarray(coeff, np.float64)
+            cp = _np_ptr(coeff)
+        check(lib().bricks_step_sweep(self._h, which, stencil, n, pa, pb, cp, stream))
+
+    def reset(self):
+        check(lib().bricks_step_reset(self._h))
+
+    def close(self):
+        if self._h:
+            lib().bricks_step_destroy(self._h)
+            self._h = C.c_void_p()
 
 
 def copy_regions(ctx, links, stream=STREAM_COMPUTE):
@@ -418,6 +538,16 @@ class Decomp(object):
         check(lib().bricks_decomp_exchange_plan(self._h, step, _np_ptr(ro), _np_ptr(so), _np_ptr(nb),
                                                 _np_ptr(rp), _np_ptr(sp)))
         return ro, so, nb, rp, sp
+
+    def make_step(self, ctx, rank, nranks, kind="regions", step=512):
+        """BrickDecomp::makeStep: the library's sweep schedule for this decomposition with the
+        communication program of exchange `kind` ("regions" | "packed" | "shift"); call rank_map()
+        first.  Returns (Step, description)."""
+        k = {"regions": 0, "packed": 1, "shift": 2}[kind]
+        h = C.c_void_p()
+        what = C.create_string_buffer(200)
+        check(lib().bricks_decomp_step_create(self._h, ctx._h, rank, nranks, k, step, C.byref(h), what, 200))
+        return Step(ctx, handle=h.value), what.value.decode()
 
     def shift_plan(self, step=512):
         """The SHIFT exchange (multiStageExchangeView, brick-mpi.h:587-681) for the rank map set by the

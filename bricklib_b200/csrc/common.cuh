@@ -64,7 +64,7 @@ struct bricks_ctx {
 struct MarchItem {
   unsigned short gi, gj, gk0, nk;
   unsigned valid1; /* second brick of the pair is inside the box */
-  unsigned validj; /* 2x2-brick footprints (cube tile kernel): the +j brick row is inside the box */
+  unsigned pad_;
 };
 
 /* kernel parameters of the sweep kernels (__grid_constant__) */
@@ -76,16 +76,6 @@ struct MarchParams {
   const FieldDev *fields;
   unsigned gd0, gd1;
   double c[27];
-#ifdef MARCH_NB_TABLE
-  /* experiment (tools/build_variants.sh nbtab): per-item neighbour rows built with the plan, see
-   * plan.cu build_nbtab */
-  const unsigned *nbtab;
-  unsigned nbtab_stride; /* unsigned per item */
-#endif
-#ifdef MARCH_PERSIST
-  unsigned *counter; /* next item per field (march_persist.cuh), zeroed before every launch */
-  unsigned nitems;
-#endif
 };
 
 /* Tensor maps of one input field for one kernel variant.  main: P-plane pieces; roll: R-plane
@@ -94,15 +84,10 @@ struct MarchParams {
  * consecutive in storage (main stages only): the two pieces of a pair sit back to back in the
  * stage, so one copy fills both. */
 struct alignas(64) MapSet {
-#ifdef MARCH_JL_SWIZZLE /* [4] / pair[2]: the swizzled four-row -j face box (march_dev.cuh) */
+  /* [4] / pair[2]: the swizzled four-row j-face box of the 25-point star (march_dev.cuh, JSWZ) */
   CUtensorMap main[5];
   CUtensorMap roll[5];
-  CUtensorMap pair[3];
-#else
-  CUtensorMap main[4];
-  CUtensorMap roll[4];
-  CUtensorMap pair[2]; /* [0]=centres of bricks b, b+1; [1]=j-face rows of bricks b, b+1 */
-#endif
+  CUtensorMap pair[3]; /* [0]=centres of bricks b, b+1; [1]=j-face rows of bricks b, b+1; [2]=swizzled j-face rows */
 };
 
 struct alignas(64) FieldDev {
@@ -133,26 +118,34 @@ struct bricks_plan {
   unsigned nbricks = 0;
   unsigned *grid_dev = nullptr;
   unsigned *adj_dev = nullptr;
+  /* a derived plan (bricks_plan_derive) borrows the tables of its parent: one device copy of
+   * grid / adj per subdomain, however many box plans its schedule needs */
+  bool owns_tables = true;
+  std::vector<unsigned> grid_host; /* owner only: to build the brick lists of derived plans */
   /* work items per column-segment length: the best length differs by stencil (plan.cu) */
   struct ItemList {
     MarchItem *dev = nullptr;
     int n = 0;
-#ifdef MARCH_NB_TABLE
-    unsigned *nbtab_dev = nullptr;
-    unsigned nbtab_stride = 0;
-#endif
   };
-#ifdef MARCH_NB_TABLE
-  std::vector<unsigned> grid_host, adj_host; /* kept to build neighbour tables lazily */
-  unsigned *counter_dev = nullptr;           /* item counters of the persistent kernel, one per field */
-  int ncounters = 0;
-#endif
   std::map<unsigned, ItemList> items;
   std::vector<unsigned> boxes; /* kept to build further item lists */
   unsigned *blist_dev = nullptr; /* flat list of every brick in the boxes (naive kernel) */
   long nlist = 0;
   std::map<FieldKey, FieldDev *> fields; /* device arrays, one FieldDev per field */
 };
+
+namespace bricks {
+/* a table of region links in device memory: links[n] followed by the first 64 KiB chunk of each */
+struct LinkBlob {
+  bricks_region_link *dev = nullptr;
+  int n = 0;
+  unsigned nchunks = 0;
+};
+int link_blob_upload(bricks_ctx *ctx, const bricks_region_link *host, int n, LinkBlob *out);
+/* from / to of every link are offsets from src_base / dst_base when that base is not null */
+int link_blob_run(bricks_ctx *ctx, const LinkBlob &b, char *src_base, char *dst_base, cudaStream_t s);
+void link_blob_free(LinkBlob *b);
+}  // namespace bricks
 
 struct bricks_exchange {
   bricks_ctx *ctx = nullptr;
@@ -162,20 +155,15 @@ struct bricks_exchange {
     int recv_peer, send_peer;
   };
   std::vector<Msg> msgs;
-  bricks_region_link *self_links_dev = nullptr; /* offsets relative to the storage base */
-  int nself = 0;
+  bricks::LinkBlob self; /* self neighbours: offsets relative to the storage base */
 };
 
 namespace bricks {
 /* longest column (brick layers) one warp marches for this stencil; measured on B200
  * (profiles/r01_column_length.txt) */
 unsigned column_length(int stencil_id);
-/* the plan's item list for that column length (built and uploaded on first use); fj = bricks per
- * footprint along j (1: brick pairs, 2: 2x2 bricks) */
-int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems, int fj = 1);
-#ifdef MARCH_NB_TABLE
-int plan_nbtab(bricks_plan *plan, unsigned maxcol, const unsigned **tab_dev, unsigned *stride);
-#endif
+/* the plan's item list for that column length (built and uploaded on first use) */
+int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems);
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
                unsigned bj, unsigned bk, bool swizzle64, unsigned bb = 1);
 }

@@ -7,6 +7,7 @@
 //                        ncclSend/ncclRecv straight from/to brick storage (regions are contiguous
 //                        by construction of the layout, so nothing is packed); regions whose
 //                        peer is this rank become on-device copies.
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -17,16 +18,13 @@ namespace {
 constexpr int kCopyThreads = 256;
 constexpr size_t kChunk = 64 * 1024; /* bytes per CTA */
 
-struct CopyJob {
-  unsigned link;
-  unsigned chunk;
-};
-
-/* links[] in device memory; grid.x = total chunks; base_off shifts both ends (self links are
- * stored relative to the storage base) */
+/* links[] in device memory; grid.x = total chunks.  A non-null base turns the `from` (src_base) or
+ * `to` (dst_base) members into byte offsets from it: exchange plans are built once and run on
+ * whatever storage the step is given (self links: both ends in the field; pack / unpack: one end
+ * in the field, the other in the message arena). */
 __global__ void __launch_bounds__(kCopyThreads) copy_regions_kernel(const bricks_region_link *links,
                                                                    const unsigned *chunk_first, int nlinks,
-                                                                   char *base) {
+                                                                   char *src_base, char *dst_base) {
   /* binary search: which link does this CTA's chunk belong to */
   int lo = 0, hi = nlinks - 1;
   const unsigned c = blockIdx.x;
@@ -37,8 +35,8 @@ __global__ void __launch_bounds__(kCopyThreads) copy_regions_kernel(const bricks
   const bricks_region_link l = links[lo];
   const size_t start = (size_t)(c - chunk_first[lo]) * kChunk;
   const size_t end = start + kChunk < l.len ? start + kChunk : l.len;
-  const char *src = (base ? base + (size_t)l.from : (const char *)l.from) + start;
-  char *dst = (base ? base + (size_t)l.to : (char *)l.to) + start;
+  const char *src = (src_base ? src_base + (size_t)l.from : (const char *)l.from) + start;
+  char *dst = (dst_base ? dst_base + (size_t)l.to : (char *)l.to) + start;
   const size_t n16 = (end - start) >> 4;
   const int4 *s4 = reinterpret_cast<const int4 *>(src);
   int4 *d4 = reinterpret_cast<int4 *>(dst);
@@ -53,13 +51,11 @@ __global__ void __launch_bounds__(kCopyThreads) copy_regions_kernel(const bricks
   }
 }
 
-struct LinkTable {
-  bricks_region_link *links;
-  unsigned *chunk_first;
-  unsigned nchunks;
-};
+}  // namespace
 
-int upload_links(bricks_ctx *ctx, const bricks_region_link *host, int n, void **blob, unsigned *nchunks) {
+namespace bricks {
+
+int link_blob_upload(bricks_ctx *ctx, const bricks_region_link *host, int n, LinkBlob *out) {
   /* device blob = links[n] followed by chunk_first[n] */
   std::vector<unsigned> first(n);
   unsigned tot = 0;
@@ -74,33 +70,39 @@ int upload_links(bricks_ctx *ctx, const bricks_region_link *host, int n, void **
   BRK_CUDA(cudaMemcpyAsync(d, host, lb, cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaMemcpyAsync(d + lb, first.data(), fb, cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaStreamSynchronize(s));
-  *blob = d;
-  *nchunks = tot;
+  out->dev = (bricks_region_link *)d;
+  out->n = n;
+  out->nchunks = tot;
   return 0;
 }
 
-}  // namespace
+int link_blob_run(bricks_ctx *ctx, const LinkBlob &b, char *src_base, char *dst_base, cudaStream_t s) {
+  if (!b.dev || b.nchunks == 0) return 0;
+  const unsigned *first = (const unsigned *)((const char *)b.dev + sizeof(bricks_region_link) * b.n);
+  copy_regions_kernel<<<b.nchunks, kCopyThreads, 0, s>>>(b.dev, first, b.n, src_base, dst_base);
+  BRK_CUDA(cudaGetLastError());
+  ++g_launches;
+  return 0;
+}
 
-/* The device blob returned by bricks_links_upload carries its own chunk table after the links;
- * the count of chunks is kept host side, keyed by the blob pointer. */
-static std::map<const void *, std::pair<int, unsigned>> g_link_meta;
+void link_blob_free(LinkBlob *b) {
+  if (b->dev) cudaFree(b->dev);
+  *b = LinkBlob();
+}
+
+}  // namespace bricks
+
+/* Tables handed out through the C ABI (bricks_links_upload) are plain device pointers; their
+ * sizes are kept host side, keyed by the pointer. */
+static std::map<const void *, bricks::LinkBlob> g_link_meta;
 static std::mutex g_link_mutex; /* one host thread per device may be inside the library at once */
 
-static void meta_put(const void *blob, int n, unsigned nchunks) {
-  std::lock_guard<std::mutex> lock(g_link_mutex);
-  g_link_meta[blob] = std::make_pair(n, nchunks);
-}
-static bool meta_get(const void *blob, int *n, unsigned *nchunks) {
+static bool meta_get(const void *blob, bricks::LinkBlob *out) {
   std::lock_guard<std::mutex> lock(g_link_mutex);
   auto it = g_link_meta.find(blob);
   if (it == g_link_meta.end()) return false;
-  *n = it->second.first;
-  *nchunks = it->second.second;
+  *out = it->second;
   return true;
-}
-static void meta_erase(const void *blob) {
-  std::lock_guard<std::mutex> lock(g_link_mutex);
-  g_link_meta.erase(blob);
 }
 
 extern "C" {
@@ -112,22 +114,25 @@ int bricks_links_upload(bricks_ctx *ctx, const bricks_region_link *links_host, i
     BRK_ARG((links_host[i].len & 15) == 0 && ((uintptr_t)links_host[i].from & 15) == 0 &&
             ((uintptr_t)links_host[i].to & 15) == 0);
   BRK_CUDA(cudaSetDevice(ctx->device));
-  void *blob = nullptr;
-  unsigned nchunks = 0;
-  int rc = upload_links(ctx, links_host, n, &blob, &nchunks);
-  if (rc) return rc;
-  meta_put(blob, n, nchunks);
-  *links_dev = (bricks_region_link *)blob;
+  bricks::LinkBlob b;
+  if (int rc = bricks::link_blob_upload(ctx, links_host, n, &b)) return rc;
+  {
+    std::lock_guard<std::mutex> lock(g_link_mutex);
+    g_link_meta[b.dev] = b;
+  }
+  *links_dev = b.dev;
   return 0;
 }
 
 int bricks_links_free(bricks_ctx *ctx, bricks_region_link *links_dev) {
   BRK_ARG(ctx);
   if (!links_dev) return 0;
-  int n = 0;
-  unsigned nchunks = 0;
-  BRK_ARG(meta_get(links_dev, &n, &nchunks)); /* only tables made by bricks_links_upload */
-  meta_erase(links_dev);
+  bricks::LinkBlob b;
+  BRK_ARG(meta_get(links_dev, &b)); /* only tables made by bricks_links_upload */
+  {
+    std::lock_guard<std::mutex> lock(g_link_mutex);
+    g_link_meta.erase(links_dev);
+  }
   BRK_CUDA(cudaSetDevice(ctx->device));
   BRK_CUDA(cudaFree(links_dev));
   return 0;
@@ -135,17 +140,10 @@ int bricks_links_free(bricks_ctx *ctx, bricks_region_link *links_dev) {
 
 int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, int n, int stream) {
   BRK_ARG(ctx && links_dev && stream >= 0 && stream < bricks::kNumStreams);
-  int have = 0;
-  unsigned nchunks = 0;
-  BRK_ARG(meta_get(links_dev, &have, &nchunks) && have == n);
-  if (nchunks == 0) return 0;
+  bricks::LinkBlob b;
+  BRK_ARG(meta_get(links_dev, &b) && b.n == n);
   BRK_CUDA(cudaSetDevice(ctx->device));
-  const unsigned *first = (const unsigned *)((const char *)links_dev + sizeof(bricks_region_link) * n);
-  copy_regions_kernel<<<nchunks, kCopyThreads, 0, ctx->streams[stream]>>>(links_dev, first, n,
-                                                                                  nullptr);
-  BRK_CUDA(cudaGetLastError());
-  ++bricks::g_launches;
-  return 0;
+  return bricks::link_blob_run(ctx, b, nullptr, nullptr, ctx->streams[stream]);
 }
 
 int bricks_comm_unique_id(void *id128) {
@@ -155,15 +153,28 @@ int bricks_comm_unique_id(void *id128) {
   return 0;
 }
 
-int bricks_comm_init(bricks_ctx *ctx, int rank, int nranks, const void *id128) {
-  BRK_ARG(ctx && id128 && nranks > 0 && rank >= 0 && rank < nranks);
+int bricks_comm_init_config(bricks_ctx *ctx, int rank, int nranks, const void *id128, int max_ctas) {
+  BRK_ARG(ctx && id128 && nranks > 0 && rank >= 0 && rank < nranks && max_ctas >= 0);
   BRK_CUDA(cudaSetDevice(ctx->device));
   ncclUniqueId id;
   memcpy(&id, id128, sizeof id);
-  BRK_NCCL(ncclCommInitRank(&ctx->comm, nranks, id, rank));
+  if (max_ctas > 0) {
+    /* the exchange runs beside a sweep kernel that fills every SM with one-warp CTAs; a capped
+     * send/recv kernel takes fewer SM slots away from it (NVLink needs few CTAs for 100 MB) */
+    ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+    cfg.minCTAs = 1;
+    cfg.maxCTAs = max_ctas;
+    BRK_NCCL(ncclCommInitRankConfig(&ctx->comm, nranks, id, rank, &cfg));
+  } else {
+    BRK_NCCL(ncclCommInitRank(&ctx->comm, nranks, id, rank));
+  }
   ctx->rank = rank;
   ctx->nranks = nranks;
   return 0;
+}
+
+int bricks_comm_init(bricks_ctx *ctx, int rank, int nranks, const void *id128) {
+  return bricks_comm_init_config(ctx, rank, nranks, id128, 0);
 }
 
 int bricks_comm_destroy(bricks_ctx *ctx) {
@@ -207,17 +218,12 @@ int bricks_exchange_create_v(bricks_ctx *ctx, int rank, int nregions, const size
       l.len = m.recv_bytes;
       self.push_back(l);
     }
-  ex->nself = (int)self.size();
-  if (ex->nself) {
-    void *blob = nullptr;
-    unsigned nchunks = 0;
-    int rc = upload_links(ctx, self.data(), ex->nself, &blob, &nchunks);
+  if (!self.empty()) {
+    int rc = bricks::link_blob_upload(ctx, self.data(), (int)self.size(), &ex->self);
     if (rc) {
       delete ex;
       return rc;
     }
-    meta_put(blob, ex->nself, nchunks);
-    ex->self_links_dev = (bricks_region_link *)blob;
   }
   *out = ex;
   return 0;
@@ -232,14 +238,13 @@ int bricks_exchange_create(bricks_ctx *ctx, int rank, int nregions, const size_t
 int bricks_exchange_destroy(bricks_exchange *ex) {
   if (!ex) return 0;
   cudaSetDevice(ex->ctx->device);
-  if (ex->self_links_dev) {
-    meta_erase(ex->self_links_dev);
-    cudaFree(ex->self_links_dev);
-  }
+  bricks::link_blob_free(&ex->self);
   delete ex;
   return 0;
 }
 
+/* Stream order is the only ordering between two runs of the same plan (and between a run and the
+ * sweeps that read what it delivered): callers enqueue bricks_stream_wait between the streams. */
 int bricks_exchange_run(bricks_exchange *ex, double *storage, int stream) {
   BRK_ARG(ex && storage && stream >= 0 && stream < bricks::kNumStreams);
   bricks_ctx *ctx = ex->ctx;
@@ -264,21 +269,7 @@ int bricks_exchange_run(bricks_exchange *ex, double *storage, int stream) {
     }
     BRK_NCCL(ncclGroupEnd());
   }
-  if (ex->nself) {
-    int have = 0;
-    unsigned nchunks = 0;
-    if (!meta_get(ex->self_links_dev, &have, &nchunks)) {
-      bricks::set_error("exchange: the table of self links is gone");
-      return -5;
-    }
-    const unsigned *first =
-        (const unsigned *)((const char *)ex->self_links_dev + sizeof(bricks_region_link) * ex->nself);
-    copy_regions_kernel<<<nchunks, kCopyThreads, 0, s>>>(ex->self_links_dev, first, ex->nself,
-                                                                  base);
-    BRK_CUDA(cudaGetLastError());
-    ++bricks::g_launches;
-  }
-  return 0;
+  return bricks::link_blob_run(ctx, ex->self, base, base, s);
 }
 
 }  // extern "C"

@@ -197,6 +197,24 @@ int bricks_decomp_shift_plan(bricks_decomp *d, size_t step, int stage, int cap, 
   });
 }
 
+int bricks_decomp_step_create(bricks_decomp *d, bricks_ctx *ctx, int rank, int nranks, int exchange_kind,
+                              size_t step, bricks_step **out, char *what, size_t what_len) {
+  if (!d || !ctx || !out || exchange_kind < 0 || exchange_kind > 2) return -1;
+  Decomp3 &D = *d->dec;
+  if (D.rank_map.empty()) {
+    bricks::set_error("bricks_decomp_step_create: call bricks_decomp_rank_map first");
+    return -1;
+  }
+  return guarded([&] {
+    D.comm.ctx = ctx;
+    D.comm.rank = rank;
+    D.comm.size = nranks;
+    std::string text;
+    *out = D.makeStep((Decomp3::StepExchange)exchange_kind, step, &text);
+    if (what && what_len) snprintf(what, what_len, "%s", text.c_str());
+  });
+}
+
 int bricks_init_grid3(const long dimlist[3], unsigned *grid, unsigned *adj) {
   if (!dimlist || !grid || !adj) return -1;
   return guarded([&] {
@@ -250,6 +268,18 @@ int bricks_strong_plan_create(unsigned dom_size, unsigned sdom_size, int nranks,
       regs[i].len = (size_t)(D.ghost[i].len - D.ghost[i].first_pad - D.ghost[i].last_pad) * sb;
     }
     *out = new bricks_strong_plan{new StrongPlan(dom_size, sdom_size, nranks, rank, regs)};
+  });
+}
+
+int bricks_strong_step_create(const bricks_strong_plan *p, bricks_ctx *ctx, int rank, const bricks_decomp *d,
+                              void *a_base, size_t sub_bytes, bricks_step **out, size_t *sent_bytes) {
+  if (!p || !ctx || !d || !a_base || !out) return -1;
+  return guarded([&] {
+    Decomp3 &D = *d->dec;
+    BrickInfo<3> info = D.getBrickInfo();
+    const unsigned g[3] = {D.gridDim(0), D.gridDim(1), D.gridDim(2)};
+    *out = makeStrongStep(ctx, rank, *p->plan, D.gridData(), g, &info.adj[0][0], info.nbricks, D.ghostBricks(),
+                          (char *)a_base, sub_bytes, sent_bytes);
   });
 }
 

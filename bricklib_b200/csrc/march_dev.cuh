@@ -139,18 +139,15 @@ template <int R, bool CUBE, int P>
 struct StageLayout {
   static constexpr int HW = R > 2 ? 4 : 2;      /* i-face width in elements (16-byte multiple) */
   static constexpr int C_PL = 512, I_PL = 64 * HW, J_PL = 64 * R, X_PL = 8 * R * HW; /* B/plane */
-  /* experiment -DMARCH_JL_SWIZZLE (125-point cube, 13- and 25-point stars): the -j face box is four rows (4..7 of the neighbour)
-   * copied with SWIZZLE_64B, which stores rows 6 and 7 with their 16-byte chunks XORed by 1 (even
-   * planes) or 3 (odd planes): the rows land on the ODD 16-byte granules, the class the centre
-   * image's own swizzle would give rows -2 and -1, and the two-way bank conflicts between those
-   * rows and centre rows 0..1 (19 % of the LDS wavefronts) are gone.  Costs 1 KB per stage. */
-#ifdef MARCH_JL_SWIZZLE
-  static constexpr bool JLX = R == 2 || (!CUBE && R == 4); /* cube, 13-point star; the 25-point star's -j face IS four rows */
-#else
-  static constexpr bool JLX = false;
-#endif
-  /* with R = 4 the +j face is four rows as well: swizzled, its rows 8..11 continue the centre pattern */
-  static constexpr bool JHX = JLX && !CUBE && R == 4;
+  /* 25-point star (R = 4): both j-face boxes are four rows copied with SWIZZLE_64B, which stores the
+   * rows with their 16-byte chunks XORed by the row pair index (plus 2 in odd planes): face rows
+   * -4..-1 and 8..11 then continue the bank pattern of the centre image, and the two-way bank
+   * conflicts between face rows and centre rows are gone (ncu: 26 % of the kernel's shared-memory
+   * wavefronts were conflicts, L1TEX 90 % busy; 0.613 -> 0.542 ms per 66^3-brick sweep,
+   * profiles/r03_experiments/variants_k_prepared.log).  For R = 2 (13-point star, cube) the same
+   * trick needs a four-row box for a two-row face and measured slower, so it is not used there. */
+  static constexpr bool JLX = !CUBE && R == 4;
+  static constexpr bool JHX = JLX;
   static constexpr int JL_ROWS = JLX ? 4 : R, JL_PL = 64 * JL_ROWS;
   static constexpr int JSUM_PL = 2 * J_PL + 2 * JL_PL; /* the four j-face pieces, bytes per plane */
   static constexpr int C0 = 0, C1 = P * C_PL;
@@ -219,47 +216,18 @@ struct LaneK {
   int rpitch[2 * R + 1]; /* bytes per plane for that row */
   int hrow[2 * R + 1];   /* halo: byte offset of the HW-wide row j+d, plane 0 */
   int hpitch[2 * R + 1];
-#ifdef MARCH_JL_SWIZZLE
   int jx[2 * R + 1]; /* XOR for the quad offsets of row j+d in ODD planes: 0x20 when it is a swizzled face row */
-#endif
 
   __device__ __forceinline__ void init(int lane) {
-#ifdef MARCH_EDGE_HI
-    /* experiment: the 16 lanes on the footprint edge (the only ones that use the i-face values) are
-     * lanes 16..31, one quarter-warp per brick (lane = 16 + bb * 8 + j, ih = bb): a PREDICATED i-face
-     * load then touches two quarter-warps, each reading the eight rows of one i-face piece (one
-     * wavefront).  The inner lanes keep the product's phase shape, four rows x two bricks
-     * (lane = (j >> 2) * 8 + (j & 3) * 2 + bb, ih = 1 - bb).  Grouping found with the stage model
-     * (tools/emulate_stage_layout.py edge). */
-    halo = (lane >> 4) != 0;
-    if (halo) {
-      bb = (lane >> 3) & 1;
-      j = lane & 7;
-      ih = bb;
-    } else {
-      bb = lane & 1;
-      j = ((lane >> 3) & 1) * 4 + ((lane >> 1) & 3);
-      ih = 1 - bb;
-    }
-    {
-      auto lane_of = [](int b, int jj, int i) {
-        return i == b ? 16 + b * 8 + jj : (jj >> 2) * 8 + (jj & 3) * 2 + b;
-      };
-      srcL = ih ? lane_of(bb, j, 0) : (bb ? lane_of(0, j, 1) : lane);
-      srcR = ih ? (bb ? lane : lane_of(1, j, 0)) : lane_of(bb, j, 1);
-    }
-#else
     bb = lane >> 4;
     j = (lane >> 1) & 7;
     ih = lane & 1;
     halo = (ih == bb);
     srcL = ih ? lane - 1 : (bb ? lane - 15 : lane);
     srcR = ih ? (bb ? lane : lane + 15) : lane + 1;
-#endif
 #pragma unroll
     for (int d = -R; d <= R; ++d) {
       const int jj = j + d, a = d + R;
-#ifdef MARCH_JL_SWIZZLE
       jx[a] = 0;
       if (L::JHX && jj > 7) {
         const int rr = jj - 8;
@@ -285,7 +253,6 @@ struct LaneK {
         hpitch[a] = L::X_PL;
         continue;
       }
-#endif
       if (jj >= 0 && jj < 8) {
         const int base = (bb ? L::C1 : L::C0) + jj * 64, sw = (jj >> 1) & 3;
         row0[a] = base + (((2 * ih) ^ sw) << 4);

@@ -53,29 +53,7 @@ __device__ __forceinline__ void gather_i(const double (&x)[4], const double (&h)
  * bytes (a broadcast, no extra wavefront), so the load needs neither a predicate nor a zero fill;
  * only the lane on the footprint edge uses the value (gather_i). */
 template <int HW>
-#ifdef MARCH_EDGE_HI
-/* edge lanes are lanes 16..31 (LaneK::init): the load is predicated, the other half-warp issues nothing */
-__device__ __forceinline__ void ld_halo(const char *st, int off, bool halo, double (&h)[HW]) {
-#pragma unroll
-  for (int q = 0; q < HW / 2; ++q) {
-    double a = 0.0, b = 0.0;
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %3, 0;\n"
-        "@p ld.shared.v2.f64 {%0, %1}, [%2];\n"
-        "}\n"
-        : "+d"(a), "+d"(b)
-        : "r"(smem_u32(st + off + 16 * q)), "r"((int)halo));
-    h[2 * q] = a;
-    h[2 * q + 1] = b;
-  }
-}
-template <int HW>
-__device__ __forceinline__ void ld_halo_unused(const char *st, int off, bool /*halo*/, double (&h)[HW]) {
-#else
 __device__ __forceinline__ void ld_halo(const char *st, int off, bool /*halo*/, double (&h)[HW]) {
-#endif
 #pragma unroll
   for (int q = 0; q < HW / 2; ++q) {
     const double2 v = *reinterpret_cast<const double2 *>(st + off + 16 * q);
@@ -120,20 +98,16 @@ __device__ __forceinline__ void star_step(const char *st, const LaneK<R, false, 
 #pragma unroll
       for (int r = 1; r <= R; ++r) {
         double up[4], dn[4];
-#ifdef MARCH_JL_SWIZZLE
         if (StageLayout<R, false, P>::JHX && (z & 1))
           ld_quad(st, (lk.row0[R + r] + z * lk.rpitch[R + r]) ^ lk.jx[R + r],
                   (lk.row1[R + r] + z * lk.rpitch[R + r]) ^ lk.jx[R + r], up);
         else
-#endif
-        ld_quad(st, lk.row0[R + r] + z * lk.rpitch[R + r], lk.row1[R + r] + z * lk.rpitch[R + r], up);
-#ifdef MARCH_JL_SWIZZLE
+          ld_quad(st, lk.row0[R + r] + z * lk.rpitch[R + r], lk.row1[R + r] + z * lk.rpitch[R + r], up);
         if (StageLayout<R, false, P>::JLX && (z & 1)) /* swizzled -j face rows, odd planes (march_dev.cuh) */
           ld_quad(st, (lk.row0[R - r] + z * lk.rpitch[R - r]) ^ lk.jx[R - r],
                   (lk.row1[R - r] + z * lk.rpitch[R - r]) ^ lk.jx[R - r], dn);
         else
-#endif
-        ld_quad(st, lk.row0[R - r] + z * lk.rpitch[R - r], lk.row1[R - r] + z * lk.rpitch[R - r], dn);
+          ld_quad(st, lk.row0[R - r] + z * lk.rpitch[R - r], lk.row1[R - r] + z * lk.rpitch[R - r], dn);
         if (VAR == 2) relu(up), relu(dn);
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
@@ -303,11 +277,6 @@ __device__ __forceinline__ void cube_step(const char *st, const LaneK<2, true, P
       double xr[5][4], hr[5][HW];
 #pragma unroll
       for (int a = 0; a < 5; ++a) {
-#ifdef MARCH_JL_SWIZZLE
-        if (a < R && (z & 1)) /* swizzled -j face rows: odd planes flip chunk bit 1 (march_dev.cuh) */
-          ld_quad(st, (lk.row0[a] + z * lk.rpitch[a]) ^ lk.jx[a], (lk.row1[a] + z * lk.rpitch[a]) ^ lk.jx[a], xr[a]);
-        else
-#endif
         ld_quad(st, lk.row0[a] + z * lk.rpitch[a], lk.row1[a] + z * lk.rpitch[a], xr[a]);
         ld_halo<HW>(st, lk.hrow[a] + z * lk.hpitch[a], lk.halo, hr[a]);
       }

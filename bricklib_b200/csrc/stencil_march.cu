@@ -6,13 +6,6 @@
 #include <cstring>
 
 #include "march_steps.cuh"
-/* measured re-designs of the cube sweep, built only by tools/build_variants.sh */
-#ifdef MARCH_CUBE_WINDOW
-#include "march_window.cuh"
-#endif
-#ifdef MARCH_CUBE_TILE
-#include "march_tile.cuh"
-#endif
 
 /* Register caps.  The register file is 4 x 16 Ki, one quarter per scheduler, so a one-warp CTA fits
  * floor(16384 / (32 * regs)) times per scheduler: <= 128 registers -> 16 warps per SM, <= 168 ->
@@ -24,12 +17,7 @@
 #define MARCH_CUBE_REGS 168
 #endif
 
-#ifdef MARCH_PERSIST
-#include "march_persist.cuh"
-#endif
-
 namespace {
-
 
 template <int R, bool CUBE, int VAR, int P>
 /* register cap for the cube: measured best on B200 (profiles/r01_maxnreg_sweep.txt) */
@@ -53,11 +41,6 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   }
   __syncwarp();
 
-#ifdef MARCH_NB_TABLE
-  /* experiment (tools/build_variants.sh nbtab): the neighbour rows of this item, resolved at plan
-   * time (plan.cu build_nbtab) -- no grid[] / adj[] lookups in the kernel */
-  const unsigned *nbt = prm.nbtab + (size_t)blockIdx.x * prm.nbtab_stride;
-#else
   /* brick ids of the column: lane t holds layer t */
   unsigned col0 = 0, col1 = 0;
   if (lane < nk) {
@@ -65,7 +48,6 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     col0 = prm.grid[cell];
     col1 = it.valid1 ? prm.grid[cell + 1] : prm.adj[(size_t)col0 * 27 + 14];
   }
-#endif
 
   dev::LaneK<R, CUBE, P> lk;
   lk.init(lane);
@@ -82,11 +64,6 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   };
   /* neighbour brick that lane's piece of stage s is cut from */
   auto load_nb = [&](int s) -> unsigned {
-#ifdef MARCH_NB_TABLE
-    /* lanes 0..11: neighbour brick of the lane's piece; 12, 13: the pair's own bricks; 14: flags */
-    const int row = s == 0 ? 0 : (s == nsteps - 1 ? nk + 1 : 1 + (s - 1) / H);
-    return lane < 16 ? __ldg(nbt + row * 16 + lane) : 0u;
-#else
     int dk;
     const int layer = step_layer(s, dk);
     const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
@@ -95,46 +72,9 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     unsigned nb = 0;
     if (lane < 12) nb = prm.adj[(size_t)rowb * 27 + (dk + 1) * 9 + (pk.dj + 1) * 3 + (pk.di + 1)];
     return nb;
-#endif
   };
   auto issue = [&](int s, unsigned nb) {
     const bool roll = (s == 0) || (s == nsteps - 1);
-#ifdef MARCH_UNI_ISSUE
-    /* experiment (tools/build_variants.sh uni): every operand of a copy is warp-uniform BY
-     * CONSTRUCTION -- the neighbour brick of piece m comes out of a warp reduction (CREDUX writes a
-     * uniform register), the rest is compile-time per piece -- and the issuing lane is picked by
-     * elect.sync, so the copies are straight-line UTMALDG instead of the compiler's
-     * ELECT / R2UR.BROADCAST / BRA.U.ANY loop over the lanes' operands (15 % of the warp's time in
-     * profiles/r02_ncu_full_march125.txt) */
-    {
-      const uint32_t bar = bar0 + 8 * (s & 1);
-      const uint32_t dst0 = smem0 + (s & 1) * L::BYTES;
-      const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
-      constexpr int NP = L::NPIECE_MAIN;
-      unsigned nbm[NP];
-#pragma unroll
-      for (int m = 0; m < NP; ++m) nbm[m] = __reduce_max_sync(0xffffffffu, lane == m ? nb : 0u);
-      if (dev::elect_one()) {
-        dev::mbar_expect_tx(bar, roll ? R * ROLL_PLANE_BYTES : P * MAIN_PLANE_BYTES);
-        const CUtensorMap *maps = roll ? fd.maps.roll : fd.maps.main;
-#pragma unroll
-        for (int m = 0; m < NP; ++m) {
-          if (m >= L::NPIECE_ROLL && roll) break;
-          const dev::PieceK q = dev::piece_of<R, CUBE, P>(m);
-          const bool pairable = (m < 2 || (m >= 4 && m < 8));
-          if (pairable && !(m & 1)) {
-            if (!roll && nbm[m + 1] == nbm[m] + 1) {
-              dev::tma_load_4d(dst0 + q.off, &fd.maps.pair[q.pairmap], q.ci, q.cj, ck, (int)nbm[m], bar);
-              ++m; /* the odd piece came with it */
-              continue;
-            }
-          }
-          dev::tma_load_4d(dst0 + q.off, &maps[q.map], q.ci, q.cj, ck, (int)nbm[m], bar);
-        }
-      }
-      return;
-    }
-#endif
     const uint32_t bar = bar0 + 8 * (s & 1);
     const uint32_t dst = smem0 + (s & 1) * L::BYTES + pk.off;
     const int ck = (s == 0) ? 8 - R : (roll ? 0 : ((s - 1) % H) * P);
@@ -144,16 +84,10 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
      * bricks are consecutive in storage -- the rule inside a BrickDecomp region -- the even lane
      * fills both with one two-brick copy and the odd lane stays idle (9 instead of 12 copies per
      * cube stage: +1-2 %; going further down to 5 changed nothing, profiles/r02_experiments/). */
-#ifdef MARCH_NB_TABLE
-    const unsigned flags = __shfl_sync(0xffffffffu, nb, 14); /* 0 in the roll rows */
-    const bool lead = lane < 12 && ((flags >> (16 + (lane & 15))) & 1u);
-    const bool follow = lane < 12 && ((flags >> (lane & 15)) & 1u);
-#else
     const unsigned nb_up = __shfl_down_sync(0xffffffffu, nb, 1), nb_dn = __shfl_up_sync(0xffffffffu, nb, 1);
     const bool pairable = !roll && (lane < 2 || (lane >= 4 && lane < 8));
     const bool lead = pairable && !(lane & 1) && nb_up == nb + 1;
     const bool follow = pairable && (lane & 1) && nb == nb_dn + 1;
-#endif
     if (lane < np && !follow) {
       const CUtensorMap *map = roll ? &fd.maps.roll[pk.map] : (lead ? &fd.maps.pair[pk.pairmap] : &fd.maps.main[pk.map]);
       dev::tma_load_4d(dst, map, pk.ci, pk.cj, ck, (int)nb, bar);
@@ -180,32 +114,12 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
   unsigned nbn = load_nb(0);
   issue(0, nbn);
   nbn = load_nb(1);
-#ifdef MARCH_NB_AHEAD
-  /* experiment (tools/build_variants.sh nbahead): adjacency rows fetched TWO stages ahead.  The ncu
-   * source view shows ~150 cycles per stage of long-scoreboard wait on the row fetched one stage
-   * (3.5 us) earlier: a first-touch adjacency row is a DRAM miss under a loaded memory system */
-  unsigned nbn2 = nsteps > 2 ? load_nb(2) : 0u;
-#endif
 
-#ifdef MARCH_NB_TABLE
-  unsigned bcur = 0, bnext = 0; /* the lane's own brick in the layer of stage s / s+1 */
-#endif
   for (int s = 0; s < nsteps; ++s) {
-#ifdef MARCH_NB_TABLE
-    bcur = bnext;
-#endif
     if (s + 1 < nsteps) {
       dev::fence_proxy_async();
       issue(s + 1, nbn);
-#ifdef MARCH_NB_TABLE
-      bnext = __shfl_sync(0xffffffffu, nbn, 12 + lk.bb);
-#endif
-#ifdef MARCH_NB_AHEAD
-      nbn = nbn2;
-      if (s + 3 < nsteps) nbn2 = load_nb(s + 3);
-#else
       if (s + 2 < nsteps) nbn = load_nb(s + 2);
-#endif
     }
     dev::mbar_wait(bar0 + 8 * (s & 1), (s >> 1) & 1);
     const char *st = smem + (s & 1) * L::BYTES;
@@ -221,13 +135,9 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
       if (half == 0) {
         o.prev = o.cur;
         o.prevv = o.curv && layer > 0;
-#ifdef MARCH_NB_TABLE
-        o.cur = out_base + (size_t)bcur * out_stride + lane_off;
-#else
         const unsigned b0 = __shfl_sync(0xffffffffu, col0, layer);
         const unsigned b1 = __shfl_sync(0xffffffffu, col1, layer);
         o.cur = out_base + (size_t)(lk.bb ? b1 : b0) * out_stride + lane_off;
-#endif
         o.curv = (lk.bb == 0) || (it.valid1 != 0);
       }
     }
@@ -259,18 +169,17 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
 
 template <int R, bool CUBE, int VAR, int P>
 int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
-#ifdef MARCH_PERSIST
-  return launch_persist<R, CUBE, VAR, P>(plan, stencil_id, fields, nfields, c, s);
-#endif
   using L = dev::StageLayout<R, CUBE, P>;
   const int smem = 2 * L::BYTES + 64;
   auto kern = march_kernel<R, CUBE, VAR, P>;
-  static bool configured[64] = {false};
-  bool &done = configured[plan->ctx->device & 63];
-  if (!done) {
+  /* per device, once; host threads that drive different devices may be here concurrently (setting
+   * the attributes twice is harmless, the mask only saves the calls) */
+  static std::atomic<unsigned long long> configured{0};
+  const unsigned long long bit = 1ull << (plan->ctx->device & 63);
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
     BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     BRK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    done = true;
+    configured.fetch_or(bit, std::memory_order_release);
   }
   MarchParams prm;
   int nitems = 0;
@@ -281,23 +190,15 @@ int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfield
   prm.gd0 = plan->gdims[0];
   prm.gd1 = plan->gdims[1];
   for (int i = 0; i < 27; ++i) prm.c[i] = c[i];
-#ifdef MARCH_NB_TABLE
-  if (int rc = bricks::plan_nbtab(plan, bricks::column_length(stencil_id), &prm.nbtab, &prm.nbtab_stride)) return rc;
-#endif
   kern<<<dim3(nitems, nfields), 32, smem, s>>>(prm);
   BRK_CUDA(cudaGetLastError());
   ++bricks::g_launches;
   return 0;
 }
 
-int planes_per_stage() {
-  static int p = 0;
-  if (!p) {
-    const char *e = getenv("BRICKS_PLANES");
-    p = (e && atoi(e) == 8) ? 8 : 4;
-  }
-  return p;
-}
+/* planes of a brick layer per pipeline stage: two stages of four planes (measured against eight,
+ * profiles/r01_tma_piece_experiments.txt: fewer one-warp CTAs fit) */
+constexpr int kPlanes = 4;
 
 /* build (or find) the device FieldDev array for these storages and this kernel variant */
 int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const double *const *in,
@@ -334,18 +235,14 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
       if (!rc) rc = bricks::encode_map(&m[1], in[f], plan->nbricks, in_step, HW, 8, pk, false);
       if (!rc) rc = bricks::encode_map(&m[2], in[f], plan->nbricks, in_step, 8, R, pk, false);
       if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false);
-#ifdef MARCH_JL_SWIZZLE
-      if (!rc && (R == 2 || (!cube && R == 4)))
+      if (!rc && !cube && R == 4) /* swizzled four-row j-face box (march_dev.cuh StageLayout::JLX) */
         rc = bricks::encode_map(&m[4], in[f], plan->nbricks, in_step, 8, 4, pk, true);
-#endif
       if (rc) return rc;
     }
     int rc = bricks::encode_map(&fd.maps.pair[0], in[f], plan->nbricks, in_step, 8, 8, P, true, 2);
     if (!rc) rc = bricks::encode_map(&fd.maps.pair[1], in[f], plan->nbricks, in_step, 8, R, P, false, 2);
-#ifdef MARCH_JL_SWIZZLE
-    if (!rc && (R == 2 || (!cube && R == 4)))
+    if (!rc && !cube && R == 4)
       rc = bricks::encode_map(&fd.maps.pair[2], in[f], plan->nbricks, in_step, 8, 4, P, true, 2);
-#endif
     if (rc) return rc;
   }
   FieldDev *d = nullptr;
@@ -378,7 +275,7 @@ extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, co
   }
   BRK_CUDA(cudaSetDevice(plan->ctx->device));
   cudaStream_t s = plan->ctx->streams[stream];
-  const int P = planes_per_stage();
+  constexpr int P = kPlanes;
   const FieldDev *fields = nullptr;
   int rc = get_fields(plan, stencil_id, P, nfields, in, out, in_step, out_step, s, &fields);
   if (rc) return rc;
@@ -387,44 +284,31 @@ extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, co
     case BRICKS_ST_7PT_COEFF:
       BRK_ARG(coeff_host);
       for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
-      return P == 8 ? launch<1, false, 1, 8>(plan, stencil_id, fields, nfields, c, s)
-                    : launch<1, false, 1, 4>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, false, 1, P>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_COND: /* cond.py (d3cond, stencils/3axis.cpp:94-163): coeff[0..6] as 7pt.py */
       BRK_ARG(coeff_host);
       for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
-      return P == 8 ? launch<1, false, 2, 8>(plan, stencil_id, fields, nfields, c, s)
-                    : launch<1, false, 2, 4>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, false, 2, P>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_27PT_COEFF: /* d3pt27 (stencils/3axis.cpp:165-247) */
       BRK_ARG(coeff_host);
       for (int i = 0; i < 27; ++i) c[i] = coeff_host[i];
       /* the reference reads term 16 at (k+1, j+1, i), the place of term 25, not at (k, j+1, i) */
       c[25] += c[16];
       c[16] = 0.0;
-      return P == 8 ? launch<1, true, 1, 8>(plan, stencil_id, fields, nfields, c, s)
-                    : launch<1, true, 1, 4>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, true, 1, P>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_7PT: /* MPI_ALPHA, MPI_BETA (stencils/fake.h:11-12) */
       c[0] = 0.4, c[1] = 0.1;
-      return P == 8 ? launch<1, false, 0, 8>(plan, stencil_id, fields, nfields, c, s)
-                    : launch<1, false, 0, 4>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, false, 0, P>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_13PT: /* MPI_B0..B2 (fake.h:20-22) */
       c[0] = 0.4, c[1] = 0.07, c[2] = 0.03;
-      return P == 8 ? launch<2, false, 0, 8>(plan, stencil_id, fields, nfields, c, s)
-                    : launch<2, false, 0, 4>(plan, stencil_id, fields, nfields, c, s);
+      return launch<2, false, 0, P>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_25PT: /* MPI_A0..A4 (fake.h:14-18) */
       c[0] = 0.1, c[1] = 0.06, c[2] = 0.045, c[3] = 0.03, c[4] = 0.015;
-      return P == 8 ? launch<4, false, 0, 8>(plan, stencil_id, fields, nfields, c, s)
-                    : launch<4, false, 0, 4>(plan, stencil_id, fields, nfields, c, s);
+      return launch<4, false, 0, P>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_125PT: { /* MPI_C0..C9 (fake.h:24-33) */
       const double cc[10] = {0.1, 0.04, 0.03, 0.01, 0.006, 0.004, 0.005, 0.002, 0.003, 0.001};
       for (int i = 0; i < 10; ++i) c[i] = cc[i];
-#ifdef MARCH_CUBE_TILE
-      return launch_tile<MARCH_CUBE_TILE, MARCH_TILE_STAGES>(plan, stencil_id, fields, nfields, c, s);
-#endif
-#ifdef MARCH_CUBE_WINDOW
-      return launch_window<MARCH_CUBE_WINDOW>(plan, stencil_id, fields, nfields, c, s);
-#endif
-      return P == 8 ? launch<2, true, 0, 8>(plan, stencil_id, fields, nfields, c, s)
-                    : launch<2, true, 0, 4>(plan, stencil_id, fields, nfields, c, s);
+      return launch<2, true, 0, P>(plan, stencil_id, fields, nfields, c, s);
     }
     default:
       bricks::set_error("unknown stencil id %d", stencil_id);

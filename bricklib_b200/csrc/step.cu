@@ -1,0 +1,265 @@
+// The sweep schedule of one rank: the hot loop `brick_func` of the reference's MPI drivers
+// (weak/main.cu:246-287, strong/main.cu:397-510; CPU twins weak/main.cpp:172-213,
+// strong/main.cpp:349-400) as ONE library object, used by bench.py, the tests and the C++ drop-in
+// drivers alike:
+//
+//   comm    : wait(compute) -- [pack] -- exchange -- [unpack] -- [local links] ------------+
+//   compute : sweep 1 over the bricks that read no ghost brick (the inner box) ------------+ wait(comm)
+//             -- sweep 1 over the shell -- sweeps 2 .. ST_ITER-1 over every brick -- last sweep over
+//             the owned bricks only (ghost output is overwritten by the next exchange: the CPU
+//             driver's skip, weak/main.cpp:204-209)
+//
+// EARLY: the last sweep computes the owned skin bricks first, the communication stream starts the
+// NEXT step's exchange as soon as they are written, and the rest of that sweep plus the next
+// step's first sweep run while the messages are in flight.  The communication program is a list
+// of region-copy tables and exchange plans so that the weak driver (exchange straight out of the
+// brick storage, or one packed message per peer), the SHIFT exchange (three stages) and the strong
+// driver (pack -> per-peer messages -> unpack -> intra-GPU links) share the code.
+#include "common.cuh"
+
+struct bricks_step {
+  bricks_ctx *ctx = nullptr;
+  /* box plans over one shared device copy of grid / adj: [0] every brick, [1] the inner box (reads
+   * no ghost brick), [2] the shell around it, [3] the owned bricks, [4] the owned skin = owned minus inner */
+  bricks_plan *plans[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool has_inner = false;
+  struct Op {
+    int kind; /* 0 copy table, 1 exchange */
+    bricks::LinkBlob links;
+    int src_base = 0, dst_base = 0;
+    bricks_exchange *ex = nullptr;
+    int base = 0;
+    bool owned = false;
+  };
+  std::vector<Op> comm;
+  char *arena = nullptr;
+  size_t arena_bytes = 0;
+  const double *in_flight = nullptr; /* field 0 of the storages whose exchange the last step started early */
+};
+
+namespace {
+
+char *resolve_base(const bricks_step *st, int kind, double *field0) {
+  switch (kind) {
+    case BRICKS_BASE_FIELD: return (char *)field0;
+    case BRICKS_BASE_ARENA: return st->arena;
+    default: return nullptr;
+  }
+}
+
+int run_comm(bricks_step *st, double *field0) {
+  bricks_ctx *ctx = st->ctx;
+  cudaStream_t s = ctx->streams[BRICKS_STREAM_COMM];
+  for (auto &op : st->comm) {
+    if (op.kind == 0) {
+      if (int rc = bricks::link_blob_run(ctx, op.links, resolve_base(st, op.src_base, field0),
+                                         resolve_base(st, op.dst_base, field0), s))
+        return rc;
+    } else {
+      double *base = (double *)resolve_base(st, op.base, field0);
+      if (int rc = bricks_exchange_run(op.ex, base, BRICKS_STREAM_COMM)) return rc;
+    }
+  }
+  return 0;
+}
+
+void box6(unsigned *o, unsigned a0, unsigned a1, unsigned a2, unsigned b0, unsigned b1, unsigned b2) {
+  o[0] = a0, o[1] = a1, o[2] = a2, o[3] = b0, o[4] = b1, o[5] = b2;
+}
+
+/* six disjoint slabs covering [olo, ohi) minus [ilo, ihi), i fastest */
+void shell6(unsigned *o, const unsigned olo[3], const unsigned ohi[3], const unsigned ilo[3], const unsigned ihi[3]) {
+  box6(o + 0, olo[0], olo[1], olo[2], ohi[0], ohi[1], ilo[2]);
+  box6(o + 6, olo[0], olo[1], ihi[2], ohi[0], ohi[1], ohi[2]);
+  box6(o + 12, olo[0], olo[1], ilo[2], ohi[0], ilo[1], ihi[2]);
+  box6(o + 18, olo[0], ihi[1], ilo[2], ohi[0], ohi[1], ihi[2]);
+  box6(o + 24, olo[0], ilo[1], ilo[2], ilo[0], ihi[1], ihi[2]);
+  box6(o + 30, ihi[0], ilo[1], ilo[2], ohi[0], ihi[1], ihi[2]);
+}
+
+}  // namespace
+
+extern "C" {
+
+int bricks_step_boxes(const unsigned gdims[3], unsigned ghost_bricks, int which, unsigned *boxes, int *nboxes) {
+  BRK_ARG(gdims && boxes && nboxes && ghost_bricks >= 1 && which >= 0 && which < 5);
+  const unsigned g = ghost_bricks;
+  unsigned zero[3] = {0, 0, 0}, full[3], ilo[3], ihi[3], olo[3], ohi[3];
+  bool has_inner = true;
+  for (int d = 0; d < 3; ++d) {
+    BRK_ARG(gdims[d] > 2 * g);
+    full[d] = gdims[d];
+    olo[d] = g, ohi[d] = gdims[d] - g;
+    ilo[d] = 2 * g, ihi[d] = gdims[d] > 4 * g ? gdims[d] - 2 * g : 2 * g;
+    if (ihi[d] <= ilo[d]) has_inner = false;
+  }
+  *nboxes = 0;
+  switch (which) {
+    case BRICKS_PLAN_FULL: box6(boxes, 0, 0, 0, full[0], full[1], full[2]); *nboxes = 1; break;
+    case BRICKS_PLAN_OWNED: box6(boxes, olo[0], olo[1], olo[2], ohi[0], ohi[1], ohi[2]); *nboxes = 1; break;
+    case BRICKS_PLAN_INNER:
+      if (has_inner) { box6(boxes, ilo[0], ilo[1], ilo[2], ihi[0], ihi[1], ihi[2]); *nboxes = 1; }
+      break;
+    case BRICKS_PLAN_SHELL:
+      if (has_inner) { shell6(boxes, zero, full, ilo, ihi); *nboxes = 6; }
+      break;
+    case BRICKS_PLAN_OSKIN:
+      if (has_inner) { shell6(boxes, olo, ohi, ilo, ihi); *nboxes = 6; }
+      break;
+  }
+  return 0;
+}
+
+int bricks_step_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigned gdims[3],
+                       const unsigned *adj_host, unsigned nbricks, unsigned ghost_bricks, bricks_step **out) {
+  BRK_ARG(ctx && grid_host && gdims && adj_host && out && ghost_bricks >= 1);
+  for (int d = 0; d < 3; ++d) BRK_ARG(gdims[d] > 2 * ghost_bricks);
+  bricks_step *st = new bricks_step;
+  st->ctx = ctx;
+  unsigned boxes[36];
+  int nb = 0;
+  int rc = bricks_step_boxes(gdims, ghost_bricks, BRICKS_PLAN_FULL, boxes, &nb);
+  if (!rc) rc = bricks_plan_create(ctx, grid_host, gdims, adj_host, nbricks, nb, boxes, &st->plans[0]);
+  for (int which = 1; which < 5 && !rc; ++which) {
+    rc = bricks_step_boxes(gdims, ghost_bricks, which, boxes, &nb);
+    if (!rc && nb) rc = bricks_plan_derive(st->plans[0], nb, boxes, &st->plans[which]);
+  }
+  st->has_inner = st->plans[BRICKS_PLAN_INNER] != nullptr;
+  if (rc) {
+    bricks_step_destroy(st);
+    return rc;
+  }
+  *out = st;
+  return 0;
+}
+
+int bricks_step_destroy(bricks_step *st) {
+  if (!st) return 0;
+  cudaSetDevice(st->ctx->device);
+  for (int i = 4; i >= 0; --i) bricks_plan_destroy(st->plans[i]); /* derived plans before their parent */
+  for (auto &op : st->comm) {
+    if (op.kind == 0) bricks::link_blob_free(&op.links);
+    if (op.kind == 1 && op.owned) bricks_exchange_destroy(op.ex);
+  }
+  if (st->arena) cudaFree(st->arena);
+  delete st;
+  return 0;
+}
+
+int bricks_step_plan(bricks_step *st, int which, bricks_plan **plan) {
+  BRK_ARG(st && plan && which >= 0 && which < 5);
+  BRK_ARG(st->plans[which]);
+  *plan = st->plans[which];
+  return 0;
+}
+
+int bricks_step_arena(bricks_step *st, size_t bytes, void **arena_dev) {
+  BRK_ARG(st && !st->arena && arena_dev);
+  BRK_CUDA(cudaSetDevice(st->ctx->device));
+  BRK_CUDA(cudaMalloc(&st->arena, bytes ? bytes : 256));
+  st->arena_bytes = bytes;
+  *arena_dev = st->arena;
+  return 0;
+}
+
+int bricks_step_add_copy(bricks_step *st, const bricks_region_link *links_host, int n, int src_base, int dst_base) {
+  BRK_ARG(st && src_base >= 0 && src_base <= BRICKS_BASE_ARENA && dst_base >= 0 && dst_base <= BRICKS_BASE_ARENA);
+  BRK_ARG((src_base != BRICKS_BASE_ARENA && dst_base != BRICKS_BASE_ARENA) || st->arena);
+  if (n == 0) return 0;
+  BRK_ARG(links_host && n > 0);
+  for (int i = 0; i < n; ++i)
+    BRK_ARG((links_host[i].len & 15) == 0 && ((uintptr_t)links_host[i].from & 15) == 0 &&
+            ((uintptr_t)links_host[i].to & 15) == 0);
+  BRK_CUDA(cudaSetDevice(st->ctx->device));
+  bricks_step::Op op;
+  op.kind = 0;
+  op.src_base = src_base;
+  op.dst_base = dst_base;
+  if (int rc = bricks::link_blob_upload(st->ctx, links_host, n, &op.links)) return rc;
+  st->comm.push_back(op);
+  return 0;
+}
+
+int bricks_step_add_exchange(bricks_step *st, bricks_exchange *ex, int base, int take_ownership) {
+  BRK_ARG(st && ex && (base == BRICKS_BASE_FIELD || (base == BRICKS_BASE_ARENA && st->arena)));
+  bricks_step::Op op;
+  op.kind = 1;
+  op.ex = ex;
+  op.base = base;
+  op.owned = take_ownership != 0;
+  st->comm.push_back(op);
+  return 0;
+}
+
+int bricks_step_exchange(bricks_step *st, double *field0) {
+  BRK_ARG(st && field0);
+  BRK_CUDA(cudaSetDevice(st->ctx->device));
+  st->in_flight = nullptr;
+  if (int rc = bricks_stream_wait(st->ctx, BRICKS_STREAM_COMM, BRICKS_STREAM_COMPUTE)) return rc;
+  return run_comm(st, field0);
+}
+
+int bricks_step_sweep(bricks_step *st, int which, int stencil_id, int nfields, const double *const *in,
+                      double *const *out, const double *coeff_host, int stream) {
+  BRK_ARG(st && which >= 0 && which < 5 && st->plans[which]);
+  return bricks_stencil(st->plans[which], stencil_id, nfields, in, out, 512, 512, coeff_host, stream);
+}
+
+int bricks_step_reset(bricks_step *st) {
+  BRK_ARG(st);
+  st->in_flight = nullptr;
+  return 0;
+}
+
+int bricks_step_run(bricks_step *st, int stencil_id, int st_iter, int nfields, double *const *a,
+                    double *const *b, const double *coeff_host, int flags) {
+  BRK_ARG(st && a && b && nfields > 0 && st_iter >= 2 && st_iter % 2 == 0);
+  bricks_ctx *ctx = st->ctx;
+  const int C = BRICKS_STREAM_COMPUTE, X = BRICKS_STREAM_COMM;
+  const bool overlap = (flags & BRICKS_STEP_OVERLAP) && st->has_inner;
+  const bool early = overlap && (flags & BRICKS_STEP_EARLY);
+  int rc = 0;
+  /* the exchange reads the skin written by the previous step's last sweep -- unless that step
+   * already started it behind its own last sweep (EARLY) */
+  const bool arrived_early = st->in_flight == a[0];
+  if (!arrived_early) {
+    if ((rc = bricks_stream_wait(ctx, X, C))) return rc;
+    if ((rc = run_comm(st, a[0]))) return rc;
+  }
+  st->in_flight = nullptr;
+  double *const *src = a, *const *dst = b;
+  for (int it = 0; it < st_iter; ++it) {
+    const bool last = it == st_iter - 1;
+    auto sweep = [&](int which) {
+      return bricks_stencil(st->plans[which], stencil_id, nfields, src, dst, 512, 512, coeff_host, C);
+    };
+    if (it == 0) {
+      if (overlap && !(arrived_early && (flags & BRICKS_STEP_EARLY_UNSPLIT))) {
+        if ((rc = sweep(1))) return rc;
+        if ((rc = bricks_stream_wait(ctx, C, X))) return rc;
+        if ((rc = sweep(2))) return rc;
+      } else {
+        /* serial schedule, or the messages have had the whole inner part of the previous step's
+         * last sweep to arrive: one unsplit sweep instead of inner + shell */
+        if ((rc = bricks_stream_wait(ctx, C, X))) return rc;
+        if ((rc = sweep(0))) return rc;
+      }
+    } else if (last && early) {
+      if ((rc = sweep(4))) return rc;
+      if ((rc = bricks_stream_wait(ctx, X, C))) return rc;
+      if ((rc = run_comm(st, dst[0]))) return rc; /* dst == a: the input of the next step */
+      st->in_flight = dst[0];
+      if ((rc = sweep(1))) return rc;
+    } else if (last) {
+      if ((rc = sweep(3))) return rc;
+    } else {
+      if ((rc = sweep(0))) return rc;
+    }
+    double *const *t = src;
+    src = dst;
+    dst = t;
+  }
+  return 0;
+}
+
+}  // extern "C"

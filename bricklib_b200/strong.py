@@ -20,7 +20,6 @@ communication stream, and the last sweep skips the ghost bricks.
 import numpy as np
 
 from . import capi
-from .weak import shell_boxes
 
 
 class StrongDomain(object):
@@ -42,22 +41,14 @@ class StrongDomain(object):
         self.in_a = [self.d_a + s * self.sub_bytes for s in range(self.nsub)]
         self.in_b = [self.d_b + s * self.sub_bytes for s in range(self.nsub)]
 
-        g = self.dec.gdims
-        gb = depth // 8
-        full = ((0, 0, 0), tuple(g))
-        inner = (tuple(2 * gb for _ in g), tuple(x - 2 * gb for x in g))
-        owned = (tuple(gb for _ in g), tuple(x - gb for x in g))
-        P = capi.Plan
-        self.plan_full = P(ctx, self.dec.grid, self.dec.adj, [full])
-        self.plan_owned = P(ctx, self.dec.grid, self.dec.adj, [owned])
-        self.has_inner = all(b > a for a, b in zip(inner[0], inner[1]))
-        if self.has_inner:
-            self.plan_inner = P(ctx, self.dec.grid, self.dec.adj, [inner])
-            self.plan_shell = P(ctx, self.dec.grid, self.dec.adj, shell_boxes(g, inner[0], inner[1]))
+        # the schedule and its communication program live in the library (csrc/step.cu)
+        S = self.step_obj = capi.Step(ctx, self.dec.grid, self.dec.adj, depth // 8)
+        self.plan_full = S.plan(capi.PLAN_FULL)
+        self.plan_owned = S.plan(capi.PLAN_OWNED)
+        self.plan_inner = S.plan(capi.PLAN_INNER)
+        self.plan_shell = S.plan(capi.PLAN_SHELL)
+        self.has_inner = self.plan_inner is not None
 
-        # intra-GPU neighbours: neighbour's skin[i] -> my ghost[i] (strong/main.cu:201-208)
-        self.local = capi.LinkTable(ctx, [(self.in_a[ss] + so, self.in_a[ds] + do, n)
-                                          for ss, ds, so, do, n in self.plan.links])
         # inter-GPU: one packed buffer per peer and direction, all inside one arena
         peers = sorted(set(p["rank"] for p in self.plan.send) | set(p["rank"] for p in self.plan.recv))
         send = {p["rank"]: p for p in self.plan.send}
@@ -73,15 +64,22 @@ class StrongDomain(object):
             off += (n + 255) // 256 * 256
         self.arena_bytes = off
         self.exchange_bytes = int(sum(sb))
-        self.arena = ctx.malloc(max(off, 256))
         pack, unpack = [], []
         for k, r in enumerate(peers):
             if r in send:
-                pack += [(self.in_a[s] + o, self.arena + so[k] + bo, n) for s, _, o, n, bo, _ in send[r]["pieces"]]
+                pack += [(self.in_a[s] + o, so[k] + bo, n) for s, _, o, n, bo, _ in send[r]["pieces"]]
             if r in recv:
-                unpack += [(self.arena + ro[k] + bo, self.in_a[s] + o, n) for s, _, o, n, bo, _ in recv[r]["pieces"]]
-        self.pack, self.unpack = capi.LinkTable(ctx, pack), capi.LinkTable(ctx, unpack)
-        self.exchange = capi.ExchangeV(ctx, rank, ro, rb, peers, so, sb, peers) if peers else None
+                unpack += [(ro[k] + bo, self.in_a[s] + o, n) for s, _, o, n, bo, _ in recv[r]["pieces"]]
+        # communication program: pack -> per-peer messages -> unpack -> intra-GPU links
+        # (strong/main.cu:416-435 and 201-208: neighbour's skin[i] -> my ghost[i])
+        if peers:
+            S.arena(max(off, 256))
+            S.add_copy(pack, capi.BASE_ABS, capi.BASE_ARENA)
+            S.add_exchange(capi.ExchangeV(ctx, rank, ro, rb, peers, so, sb, peers), capi.BASE_ARENA)
+            S.add_copy(unpack, capi.BASE_ARENA, capi.BASE_ABS)
+        self.nlinks = len(self.plan.links)
+        S.add_copy([(self.in_a[ss] + so_, self.in_a[ds] + do, n) for ss, ds, so_, do, n in self.plan.links],
+                   capi.BASE_ABS, capi.BASE_ABS)
 
     # ------------------------------------------------------------------ data
     def host_field(self, local_index):
@@ -100,48 +98,24 @@ class StrongDomain(object):
         return self.ctx.download(self.in_a[local_index], self.dec.nbricks * 512)
 
     # ------------------------------------------------------------------ one step
-    def exchange_only(self, stream=capi.STREAM_COMM):
-        """pack -> per-peer messages -> unpack -> local links, all on one stream."""
-        self.pack.run(stream)
-        if self.exchange is not None:
-            self.exchange.run(self.arena, stream)
-        self.unpack.run(stream)
-        self.local.run(stream)
+    def exchange_only(self):
+        """pack -> per-peer messages -> unpack -> local links, on the communication stream."""
+        self.step_obj.exchange(self.in_a[0])
+
+    def sweep_full(self, stencil, src, dst, coeff=None):
+        """one launch over every brick of every local subdomain"""
+        self.step_obj.sweep(capi.PLAN_FULL, stencil, src, dst, coeff)
 
     def step(self, overlap=True, coeff=None):
-        C_, X = capi.STREAM_COMPUTE, capi.STREAM_COMM
-        ctx, st = self.ctx, self.stencil
+        """bricks_step_run over all local subdomains: each sweep is ONE launch batched over them"""
         n0 = capi.launch_count()
-        ctx.stream_wait(X, C_)
-        self.exchange_only(X)
-        src, dst = self.in_a, self.in_b
-        for it in range(self.st_iter):
-            last = it == self.st_iter - 1
-            if it == 0:
-                if overlap and self.has_inner:
-                    self.plan_inner.stencil(st, src, dst, 512, 512, coeff, C_)
-                    ctx.stream_wait(C_, X)
-                    self.plan_shell.stencil(st, src, dst, 512, 512, coeff, C_)
-                else:
-                    ctx.stream_wait(C_, X)
-                    self.plan_full.stencil(st, src, dst, 512, 512, coeff, C_)
-            elif last:
-                self.plan_owned.stencil(st, src, dst, 512, 512, coeff, C_)
-            else:
-                self.plan_full.stencil(st, src, dst, 512, 512, coeff, C_)
-            src, dst = dst, src
-        assert src is self.in_a
+        self.step_obj.run(self.stencil, self.st_iter, self.in_a, self.in_b, coeff,
+                          capi.STEP_OVERLAP if overlap else 0)
         return capi.launch_count() - n0
 
     def close(self):
-        plans = [self.plan_full, self.plan_owned] + ([self.plan_inner, self.plan_shell] if self.has_inner else [])
-        for p in plans:
-            p.close()
-        if self.exchange is not None:
-            self.exchange.close()
-        for t in (self.local, self.pack, self.unpack):
-            t.close()
-        for d in (self.d_a, self.d_b, self.arena):
+        self.step_obj.close()
+        for d in (self.d_a, self.d_b):
             self.ctx.free(d)
         self.plan.close()
         self.dec.close()

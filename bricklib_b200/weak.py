@@ -15,33 +15,27 @@ do not read ghost data ([2, n-2) cells of the brick grid = the inner-inner regio
 waits for the exchange; (2) the last sweep skips the ghost bricks (the CPU driver's skip=1,
 weak/main.cpp:204-209): their output is never read because the next exchange overwrites it.
 """
+import os as _os
+
 import numpy as np
 
 from . import capi
 
 
-def shell_boxes(g, inner_lo, inner_hi):
-    """Six disjoint slabs covering [0,g)^3 minus [inner_lo, inner_hi)^3 (i fastest)."""
-    (g0, g1, g2), (a0, a1, a2), (b0, b1, b2) = g, inner_lo, inner_hi
-    return [((0, 0, 0), (g0, g1, a2)), ((0, 0, b2), (g0, g1, g2)),
-            ((0, 0, a2), (g0, a1, b2)), ((0, b1, a2), (g0, g1, b2)),
-            ((0, a1, a2), (a0, b1, b2)), ((b0, a1, a2), (g0, b1, b2))]
-
-
-def shell_between(outer_lo, outer_hi, inner_lo, inner_hi):
-    """Six disjoint slabs covering [outer_lo, outer_hi) minus [inner_lo, inner_hi) (i fastest)."""
-    (o0, o1, o2), (g0, g1, g2) = outer_lo, outer_hi
-    (a0, a1, a2), (b0, b1, b2) = inner_lo, inner_hi
-    return [((o0, o1, o2), (g0, g1, a2)), ((o0, o1, b2), (g0, g1, g2)),
-            ((o0, o1, a2), (g0, a1, b2)), ((o0, b1, a2), (g0, g1, b2)),
-            ((o0, a1, a2), (a0, b1, b2)), ((b0, a1, a2), (g0, b1, b2))]
-
-
 class WeakSubdomain(object):
-    """One rank's subdomain: BrickDecomp tables, two ping-pong storages on the device, the box
-    plans of the sweep schedule and the exchange plan."""
+    """One rank's subdomain: BrickDecomp tables, two ping-pong storages on the device and the
+    library's step object (bricks_step_*: the box plans of the sweep schedule over one device copy
+    of grid / adj, and the communication program).
 
-    def __init__(self, ctx, dims, stencil, rank=0, procdims=(1, 1, 1), depth=8, seed=20240601, shift=False):
+    exchange: "regions" -- one ncclSend/ncclRecv pair per BrickDecomp region straight out of the
+                           storage (BrickDecomp::exchange, brick-mpi.h:466-495; 42 pairs at depth 8)
+              "packed"  -- one message per peer rank (the role of ExchangeView, brick-mpi.h:96-123,
+                           525-580: one message per neighbour; the mmap views become a pack kernel,
+                           one send/recv per peer and an unpack kernel over a device arena)
+              "shift"   -- MultiStageExchangeView (brick-mpi.h:587-681): 3 stages, 6 messages"""
+
+    def __init__(self, ctx, dims, stencil, rank=0, procdims=(1, 1, 1), depth=8, seed=20240601, shift=False,
+                 exchange=None):
         self.ctx, self.stencil, self.rank = ctx, stencil, rank
         self.procdims = list(procdims)
         self.nranks = int(np.prod(procdims))
@@ -51,7 +45,6 @@ class WeakSubdomain(object):
         self.coo = capi.cart_coords(rank, self.procdims)
         self.rank_map = self.dec.rank_map(self.procdims, self.coo)
         g = self.dec.gdims
-        gb = depth // 8
         self.gdims = g
         nb = self.dec.nbricks
         self.nbytes = nb * 512 * 8
@@ -59,26 +52,19 @@ class WeakSubdomain(object):
         self.d_b = ctx.malloc(self.nbytes)
         ctx.memset(self.d_a, 0, self.nbytes)
         ctx.memset(self.d_b, 0, self.nbytes)
-        full = ((0, 0, 0), tuple(g))
-        inner = (tuple(2 * gb for _ in g), tuple(x - 2 * gb for x in g))
-        owned = (tuple(gb for _ in g), tuple(x - gb for x in g))
-        self.plan_full = capi.Plan(ctx, self.dec.grid, self.dec.adj, [full])
-        self.plan_inner = capi.Plan(ctx, self.dec.grid, self.dec.adj, [inner])
-        self.plan_shell = capi.Plan(ctx, self.dec.grid, self.dec.adj, shell_boxes(g, inner[0], inner[1]))
-        self.plan_owned = capi.Plan(ctx, self.dec.grid, self.dec.adj, [owned])
-        # the owned bricks that some neighbour needs (skin) = owned box minus the inner box
-        self.plan_oskin = capi.Plan(ctx, self.dec.grid, self.dec.adj,
-                                    shell_between(owned[0], owned[1], inner[0], inner[1]))
-        self._exchange_in_flight = None  # storage whose exchange was started by the previous step
-        self._pairs = None               # device storage pairs of the host-fed pipeline (host_steps)
-        self.host_step_bytes = int(self.dec.sep_pos[1]) * 512 * 8
         ro, so, nbts, rp, sp = self.dec.exchange_plan(512)
         self.exchange_bytes = int(nbts.sum())
-        if shift:
-            # SHIFT exchange (multiStageExchangeView, brick-mpi.h:587-681): 3 stages, 6 messages
-            self.exchange = capi.ShiftExchange(ctx, rank, self.dec.shift_plan(512))
-        else:
-            self.exchange = capi.Exchange(ctx, rank, ro, so, nbts, rp, sp)
+        kind = exchange or ("shift" if shift else "regions")
+        # the schedule and its communication program are built by the C++ host layer
+        # (BrickDecomp::makeStep) and run by the library (csrc/step.cu)
+        self.step_obj, self.exchange_kind = self.dec.make_step(ctx, rank, self.nranks, kind, 512)
+        self.plan_full = self.step_obj.plan(capi.PLAN_FULL)
+        self.plan_inner = self.step_obj.plan(capi.PLAN_INNER)
+        self.plan_shell = self.step_obj.plan(capi.PLAN_SHELL)
+        self.plan_owned = self.step_obj.plan(capi.PLAN_OWNED)
+        self.plan_oskin = self.step_obj.plan(capi.PLAN_OSKIN)
+        self._pairs = None               # device storage pairs of the host-fed pipeline (host_steps)
+        self.host_step_bytes = int(self.dec.sep_pos[1]) * 512 * 8
         self.seed = seed + 1000 * rank
         self.launches_per_step = None
 
@@ -92,7 +78,7 @@ class WeakSubdomain(object):
 
     def upload(self, field):
         self.ctx.sync()
-        self._exchange_in_flight = None
+        self.step_obj.reset()
         self.ctx.h2d(self.d_a, field)
         self.ctx.sync()
 
@@ -100,49 +86,36 @@ class WeakSubdomain(object):
         return self.ctx.download(self.d_a, self.dec.nbricks * 512)
 
     # ------------------------------------------------------------------ one step
-    def step(self, overlap=True, coeff=None, pair=None, early=False):
+    def step(self, overlap=True, coeff=None, pair=None, early=False, unsplit=None):
         """exchange(d_a) + ST_ITER ping-pong sweeps; the result ends in d_a (ST_ITER is even).
-        Everything is enqueued asynchronously; returns the number of kernels launched.
+        The schedule itself lives in the library (bricks_step_run, csrc/step.cu): everything is
+        enqueued asynchronously; returns the number of kernels launched.
         `pair` = (in/out storage, scratch storage) overrides (d_a, d_b).
         `early`: the last sweep computes the skin bricks first and the exchange of the NEXT step
         starts as soon as they are written, so it also hides behind the rest of that sweep (only
         valid when the next step continues from this result; any host access to the field must
-        be preceded by ctx.sync(), which covers the communication stream too)."""
-        C, X = capi.STREAM_COMPUTE, capi.STREAM_COMM
+        be preceded by ctx.sync(), which covers the communication stream too).
+        `unsplit`: with early, a first sweep whose exchange is already in flight runs as one launch
+        (default: BRICKS_EARLY_UNSPLIT=1 in the environment)."""
         n0 = capi.launch_count()
-        ctx, st = self.ctx, self.stencil
         d_a, d_b = pair if pair is not None else (self.d_a, self.d_b)
-        if self._exchange_in_flight != d_a:
-            # the exchange reads the skin written by the previous step's last sweep
-            ctx.stream_wait(X, C)
-            self.exchange.run(d_a, X)
-        self._exchange_in_flight = None
-        src, dst = d_a, d_b
-        for it in range(self.st_iter):
-            last = it == self.st_iter - 1
-            if it == 0:
-                if overlap:
-                    self.plan_inner.stencil(st, src, dst, 512, 512, coeff, C)
-                    ctx.stream_wait(C, X)
-                    self.plan_shell.stencil(st, src, dst, 512, 512, coeff, C)
-                else:
-                    ctx.stream_wait(C, X)
-                    self.plan_full.stencil(st, src, dst, 512, 512, coeff, C)
-            elif last and early and overlap:
-                self.plan_oskin.stencil(st, src, dst, 512, 512, coeff, C)
-                ctx.stream_wait(X, C)
-                self.exchange.run(dst, X)  # dst == d_a: input of the next step
-                self._exchange_in_flight = dst
-                self.plan_inner.stencil(st, src, dst, 512, 512, coeff, C)
-            elif last:
-                self.plan_owned.stencil(st, src, dst, 512, 512, coeff, C)
-            else:
-                self.plan_full.stencil(st, src, dst, 512, 512, coeff, C)
-            src, dst = dst, src
-        assert src == d_a
+        flags = (capi.STEP_OVERLAP if overlap else 0) | (capi.STEP_EARLY if early else 0)
+        if unsplit is None:
+            unsplit = _os.environ.get("BRICKS_EARLY_UNSPLIT", "0") == "1"
+        if unsplit:
+            flags |= capi.STEP_EARLY_UNSPLIT
+        self.step_obj.run(self.stencil, self.st_iter, d_a, d_b, coeff, flags)
         # NCCL launches its own kernels; count ours plus one per remote exchange
         self.launches_per_step = capi.launch_count() - n0
         return self.launches_per_step
+
+    def exchange_only(self, storage=None):
+        """the communication program alone, on the communication stream"""
+        self.step_obj.exchange(self.d_a if storage is None else storage)
+
+    def sweep_full(self, stencil, src, dst, coeff=None):
+        """one sweep over every brick of the grid (ghost bricks included): the dominant kernel"""
+        self.step_obj.sweep(capi.PLAN_FULL, stencil, src, dst, coeff)
 
     # ------------------------------------------------------------------ host-fed steps
     def host_steps(self, h_in, h_outs, steps, overlap=True):
@@ -154,9 +127,8 @@ class WeakSubdomain(object):
         enqueued; the caller synchronises."""
         ctx = self.ctx
         C, U, D = capi.STREAM_COMPUTE, capi.STREAM_H2D, capi.STREAM_D2H
-        if self._exchange_in_flight is not None:  # an early exchange of a device-resident run
-            ctx.sync()
-            self._exchange_in_flight = None
+        ctx.sync()  # an early exchange of a device-resident run may still be in flight
+        self.step_obj.reset()
         # ghost bricks are neither input (the exchange fills them) nor result: BrickDecomp numbers
         # them last, so only bricks [0, sep_pos[1]) cross the bus
         nbytes = int(self.dec.sep_pos[1]) * 512 * 8
@@ -181,9 +153,7 @@ class WeakSubdomain(object):
         ctx.stream_wait(C, D)
 
     def close(self):
-        for p in (self.plan_full, self.plan_inner, self.plan_shell, self.plan_owned, self.plan_oskin):
-            p.close()
-        self.exchange.close()
+        self.step_obj.close()
         for a1, b1 in (self._pairs or [])[1:]:
             self.ctx.free(a1)
             self.ctx.free(b1)

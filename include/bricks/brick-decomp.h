@@ -366,6 +366,7 @@ class BrickDecomp {
   BrickInfo<dim> getBrickInfo() { return *bInfo; }
   const unsigned *gridData() const { return grid; }
   unsigned gridDim(unsigned axis) const { return td[axis]; }
+  unsigned ghostBricks() const { return gd[0]; }
 
   /// Halo exchange of one DEVICE storage created from this decomposition (blocking, like the
   /// reference's BrickDecomp::exchange(BrickStorage&), brick-mpi.h:466-495).
@@ -475,6 +476,131 @@ class BrickDecomp {
       done = done | axis;
     }
     return out;
+  }
+
+  /// How the halo exchange of a step travels (makeStep).
+  enum StepExchange {
+    STEP_REGIONS = 0,  ///< one send/recv pair per region straight out of the storage (exchange(), :466-495)
+    STEP_PACKED = 1,   ///< one message per peer rank: the role of ExchangeView (brick-mpi.h:96-123, 525-580);
+                       ///< the mmap views become a pack kernel, one send/recv per peer and an unpack kernel
+    STEP_SHIFT = 2     ///< MultiStageExchangeView (brick-mpi.h:587-681): 3 stages, 6 messages
+  };
+
+  /// The library's sweep schedule for this decomposition (bricks_step_*, csrc/step.cu): the box plans
+  /// of the overlapped schedule over ONE device copy of grid / adj, and the communication program
+  /// of the chosen exchange.  Replaces the body of `brick_func` (weak/main.cu:246-287); used by the
+  /// C++ drivers and, through bricks_decomp_step_create, by bench.py and the tests.  The caller
+  /// owns the result (bricks_step_destroy).  `what`, if given, receives a one-line description.
+  bricks_step *makeStep(StepExchange kind, size_t step_elems, std::string *what = nullptr) {
+    static_assert(dim == 3, "the sweep kernels are 3-D");
+    if (!comm.ctx) throw std::runtime_error("BrickDecomp::comm has no device context");
+    using bricks_detail::require;
+    bricks_step *st = nullptr;
+    require(bricks_step_create(comm.ctx, grid, td, &bInfo->adj[0][0], bInfo->nbricks, gd[0], &st), "bricks_step_create");
+    try {
+      const size_t sb = step_elems * sizeof(bElem);
+      const size_t n = ghost.size();
+      std::vector<size_t> roff(n), soff(n), bytes(n);
+      std::vector<int> rpeer(n), speer(n);
+      for (size_t i = 0; i < n; ++i) {
+        roff[i] = (size_t)(ghost[i].pos + ghost[i].first_pad) * sb;
+        soff[i] = (size_t)(skin[i].pos + skin[i].first_pad) * sb;
+        bytes[i] = (size_t)(ghost[i].len - ghost[i].first_pad - ghost[i].last_pad) * sb;
+        rpeer[i] = rank_map.at(ghost[i].neighbor.set);
+        speer[i] = rank_map.at(skin[i].neighbor.set);
+      }
+      char text[160];
+      if (kind == STEP_REGIONS) {
+        bricks_exchange *ex = nullptr;
+        require(bricks_exchange_create(comm.ctx, comm.rank, (int)n, roff.data(), soff.data(), bytes.data(), rpeer.data(),
+                                       speer.data(), &ex), "bricks_exchange_create");
+        require(bricks_step_add_exchange(st, ex, BRICKS_BASE_FIELD, 1), "bricks_step_add_exchange");
+        snprintf(text, sizeof text, "direct (one ncclSend/ncclRecv pair per region, %zu regions)", n);
+      } else if (kind == STEP_SHIFT) {
+        std::string counts;
+        for (const auto &stage : shiftPieces()) {
+          const size_t m = stage.size();
+          std::vector<size_t> ro(m), so(m), nb_(m);
+          std::vector<int> rp(m), sp(m);
+          for (size_t i = 0; i < m; ++i) {
+            ro[i] = (size_t)stage[i].recv_pos * sb;
+            so[i] = (size_t)stage[i].send_pos * sb;
+            nb_[i] = (size_t)stage[i].len * sb;
+            rp[i] = rank_map.at(stage[i].from.set);
+            sp[i] = rank_map.at((!stage[i].from).set);
+          }
+          bricks_exchange *ex = nullptr;
+          require(bricks_exchange_create(comm.ctx, comm.rank, (int)m, ro.data(), so.data(), nb_.data(), rp.data(),
+                                         sp.data(), &ex), "bricks_exchange_create");
+          require(bricks_step_add_exchange(st, ex, BRICKS_BASE_FIELD, 1), "bricks_step_add_exchange");
+          counts += (counts.empty() ? "" : "+") + std::to_string(m);
+        }
+        snprintf(text, sizeof text, "shift (3 stages, 6 messages, %s pieces)", counts.c_str());
+      } else {
+        // One message per peer.  Region i travels with MPI tag i in the reference; here the regions
+        // of a peer are packed in the order i on both sides (region i of the sender is region i of
+        // the receiver: every rank holds the same tables).  Self neighbours stay one copy table.
+        std::vector<int> peers;
+        for (size_t i = 0; i < n; ++i)
+          for (int p : {rpeer[i], speer[i]})
+            if (p != comm.rank && std::find(peers.begin(), peers.end(), p) == peers.end()) peers.push_back(p);
+        std::sort(peers.begin(), peers.end());
+        std::vector<bricks_region_link> pack, unpack, self;
+        std::vector<size_t> s_off, s_bytes, r_off, r_bytes;
+        size_t off = 0;
+        auto link = [](size_t from, size_t to, size_t len) {
+          bricks_region_link l;
+          l.from = (double *)from;
+          l.to = (double *)to;
+          l.len = len;
+          return l;
+        };
+        for (int p : peers) {
+          s_off.push_back(off);
+          for (size_t i = 0; i < n; ++i)
+            if (speer[i] == p && bytes[i]) {
+              pack.push_back(link(soff[i], off, bytes[i]));
+              off += bytes[i];
+            }
+          s_bytes.push_back(off - s_off.back());
+          off = (off + 255) / 256 * 256;
+        }
+        for (int p : peers) {
+          r_off.push_back(off);
+          for (size_t i = 0; i < n; ++i)
+            if (rpeer[i] == p && bytes[i]) {
+              unpack.push_back(link(off, roff[i], bytes[i]));
+              off += bytes[i];
+            }
+          r_bytes.push_back(off - r_off.back());
+          off = (off + 255) / 256 * 256;
+        }
+        for (size_t i = 0; i < n; ++i)
+          if (rpeer[i] == comm.rank && bytes[i]) self.push_back(link(soff[i], roff[i], bytes[i]));
+        if (!peers.empty()) {
+          void *arena = nullptr;
+          require(bricks_step_arena(st, off, &arena), "bricks_step_arena");
+          require(bricks_step_add_copy(st, pack.data(), (int)pack.size(), BRICKS_BASE_FIELD, BRICKS_BASE_ARENA),
+                  "bricks_step_add_copy");
+          bricks_exchange *ex = nullptr;
+          require(bricks_exchange_create_v(comm.ctx, comm.rank, (int)peers.size(), r_off.data(), r_bytes.data(),
+                                           peers.data(), s_off.data(), s_bytes.data(), peers.data(), &ex),
+                  "bricks_exchange_create_v");
+          require(bricks_step_add_exchange(st, ex, BRICKS_BASE_ARENA, 1), "bricks_step_add_exchange");
+          require(bricks_step_add_copy(st, unpack.data(), (int)unpack.size(), BRICKS_BASE_ARENA, BRICKS_BASE_FIELD),
+                  "bricks_step_add_copy");
+        }
+        require(bricks_step_add_copy(st, self.data(), (int)self.size(), BRICKS_BASE_FIELD, BRICKS_BASE_FIELD),
+                "bricks_step_add_copy");
+        snprintf(text, sizeof text, "packed (one message per peer rank: %zu peers, %zu regions packed, %zu self regions)",
+                 peers.size(), pack.size(), self.size());
+      }
+      if (what) *what = text;
+    } catch (...) {
+      bricks_step_destroy(st);
+      throw;
+    }
+    return st;
   }
 
   /// SHIFT exchange bound to a device storage (brick-mpi.h:587: multiStageExchangeView)

@@ -18,8 +18,10 @@
 #include <algorithm>
 #include <map>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
+#include "../bricks_b200.h"
 #include "bitset.h"
 #include "zmort.h"
 
@@ -133,5 +135,84 @@ class StrongPlan {
     }
   }
 };
+
+/// The library's sweep schedule (bricks_step_*, csrc/step.cu) for the local subdomains of a
+/// StrongPlan: the box plans over the ONE grid / BrickInfo every subdomain shares, and the
+/// communication program of strong/main.cu:397-447 -- pack the pieces every peer needs into one
+/// buffer per peer (an arena owned by the step), one send/recv per peer, unpack, then the
+/// intra-GPU links neighbour's skin[i] -> my ghost[i] (main.cu:201-208).  Subdomain s of the input
+/// field lives at a_base + s * sub_bytes; the link tables hold absolute device addresses, so a
+/// step always exchanges THAT field (ST_ITER is even: the result ends there).
+/// Used by drivers/strong.cpp and, through bricks_strong_step_create, by bench.py and the tests.
+inline bricks_step *makeStrongStep(bricks_ctx *ctx, int rank, const StrongPlan &sp, const unsigned *grid,
+                                   const unsigned gdims[3], const unsigned *adj, unsigned nbricks,
+                                   unsigned ghost_bricks, char *a_base, size_t sub_bytes, size_t *sent_bytes = nullptr) {
+  auto require = [](int rc, const char *what) {
+    if (rc != 0) throw std::runtime_error(std::string(what) + ": " + bricks_last_error());
+  };
+  bricks_step *st = nullptr;
+  require(bricks_step_create(ctx, grid, gdims, adj, nbricks, ghost_bricks, &st), "bricks_step_create");
+  try {
+    std::vector<int> peers;
+    for (auto &p : sp.send) peers.push_back(p.rank);
+    for (auto &p : sp.recv) peers.push_back(p.rank);
+    std::sort(peers.begin(), peers.end());
+    peers.erase(std::unique(peers.begin(), peers.end()), peers.end());
+    auto find = [](const std::vector<StrongPeer> &v, int r) -> const StrongPeer * {
+      for (auto &p : v)
+        if (p.rank == r) return &p;
+      return nullptr;
+    };
+    std::vector<size_t> so, sb, ro, rb;
+    size_t off = 0, sent = 0;
+    for (int r : peers) {
+      const StrongPeer *p = find(sp.send, r);
+      so.push_back(off), sb.push_back(p ? p->bytes : 0);
+      off += (sb.back() + 255) / 256 * 256;
+      sent += sb.back();
+    }
+    for (int r : peers) {
+      const StrongPeer *p = find(sp.recv, r);
+      ro.push_back(off), rb.push_back(p ? p->bytes : 0);
+      off += (rb.back() + 255) / 256 * 256;
+    }
+    if (sent_bytes) *sent_bytes = sent;
+    auto link = [](size_t from, size_t to, size_t len) {
+      bricks_region_link l;
+      l.from = (double *)from;
+      l.to = (double *)to;
+      l.len = len;
+      return l;
+    };
+    const size_t a0 = (size_t)a_base;
+    std::vector<bricks_region_link> local, pack, unpack;
+    for (auto &l : sp.links)
+      local.push_back(link(a0 + l.src_sub * sub_bytes + l.src_off, a0 + l.dst_sub * sub_bytes + l.dst_off, l.len));
+    for (size_t k = 0; k < peers.size(); ++k) {
+      if (const StrongPeer *p = find(sp.send, peers[k]))
+        for (auto &pc : p->pieces) pack.push_back(link(a0 + pc.sub * sub_bytes + pc.off, so[k] + pc.buf_off, pc.len));
+      if (const StrongPeer *p = find(sp.recv, peers[k]))
+        for (auto &pc : p->pieces) unpack.push_back(link(ro[k] + pc.buf_off, a0 + pc.sub * sub_bytes + pc.off, pc.len));
+    }
+    if (!peers.empty()) {
+      void *arena = nullptr;
+      require(bricks_step_arena(st, off, &arena), "bricks_step_arena");
+      require(bricks_step_add_copy(st, pack.data(), (int)pack.size(), BRICKS_BASE_ABS, BRICKS_BASE_ARENA),
+              "bricks_step_add_copy");
+      bricks_exchange *ex = nullptr;
+      require(bricks_exchange_create_v(ctx, rank, (int)peers.size(), ro.data(), rb.data(), peers.data(), so.data(),
+                                       sb.data(), peers.data(), &ex), "bricks_exchange_create_v");
+      require(bricks_step_add_exchange(st, ex, BRICKS_BASE_ARENA, 1), "bricks_step_add_exchange");
+      require(bricks_step_add_copy(st, unpack.data(), (int)unpack.size(), BRICKS_BASE_ARENA, BRICKS_BASE_ABS),
+              "bricks_step_add_copy");
+    }
+    require(bricks_step_add_copy(st, local.data(), (int)local.size(), BRICKS_BASE_ABS, BRICKS_BASE_ABS),
+            "bricks_step_add_copy");
+  } catch (...) {
+    bricks_step_destroy(st);
+    throw;
+  }
+  return st;
+}
 
 #endif  // BRICKS_B200_STRONG_PLAN_H

@@ -33,6 +33,7 @@ extern "C" {
 typedef struct bricks_ctx bricks_ctx;         /* one per device */
 typedef struct bricks_plan bricks_plan;       /* a stencil launch plan over a brick-grid box */
 typedef struct bricks_exchange bricks_exchange; /* a halo-exchange plan */
+typedef struct bricks_step bricks_step;       /* the sweep schedule of one rank: exchange + ST_ITER sweeps */
 
 /* Stencil ids.  Point sets and coefficients: stencils/7pt.py:19-26 (7 runtime coefficients
  * coeff[0..6] = centre,i+1,i-1,j+1,j-1,k+1,k-1), stencils/mpi7pt.py, mpi13pt.py, mpi25pt.py,
@@ -93,6 +94,9 @@ int bricks_timer_elapsed_ms(bricks_ctx *ctx, int slot, float *ms); /* synchronis
 int bricks_plan_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigned gdims[3],
                        const unsigned *adj_host, unsigned nbricks, int nboxes,
                        const unsigned *boxes, bricks_plan **plan);
+/* a plan over other boxes of the SAME grid: borrows the parent's device copies of grid / adj (the
+ * reference keeps one grid / BrickInfo per subdomain, weak/main.cu:90-100); destroy it before the parent */
+int bricks_plan_derive(bricks_plan *parent, int nboxes, const unsigned *boxes, bricks_plan **plan);
 int bricks_plan_destroy(bricks_plan *plan);
 /* device copies held by the plan (for callers that want them, e.g. the exchange) */
 int bricks_plan_device_tables(const bricks_plan *plan, const unsigned **adj_dev,
@@ -153,6 +157,9 @@ int bricks_array_stencil7(bricks_ctx *ctx, const double *in_dev, double *out_dev
  * on-device copies.  Offsets/sizes in BYTES relative to the storage base passed at run time. */
 int bricks_comm_unique_id(void *id128);            /* ncclGetUniqueId; 128 bytes */
 int bricks_comm_init(bricks_ctx *ctx, int rank, int nranks, const void *id128);
+/* max_ctas > 0: ncclCommInitRankConfig with minCTAs = 1, maxCTAs = max_ctas, so that the send/recv
+ * kernel of an exchange takes few SM slots from the sweep it overlaps; 0 = NCCL's default */
+int bricks_comm_init_config(bricks_ctx *ctx, int rank, int nranks, const void *id128, int max_ctas);
 int bricks_comm_destroy(bricks_ctx *ctx);
 int bricks_exchange_create(bricks_ctx *ctx, int rank, int nregions, const size_t *recv_off,
                            const size_t *send_off, const size_t *nbytes, const int *recv_peer,
@@ -166,6 +173,49 @@ int bricks_exchange_create_v(bricks_ctx *ctx, int rank, int nregions, const size
 int bricks_exchange_destroy(bricks_exchange *ex);
 /* enqueue the whole exchange of one storage on `stream` (normally BRICKS_STREAM_COMM) */
 int bricks_exchange_run(bricks_exchange *ex, double *storage_dev, int stream);
+
+/* ---- the sweep schedule: replaces the hot loop `brick_func` of the MPI drivers (weak/main.cu:246-287,
+ * strong/main.cu:397-510; CPU twins weak/main.cpp:172-213, strong/main.cpp:349-400): one exchange, then
+ * ST_ITER ping-pong sweeps a -> b -> a ..., with the exchange hidden behind the part of the first sweep
+ * that reads no ghost brick.  A step object holds the five box plans of that schedule over ONE device
+ * copy of grid / adj (ghost_bricks = ghost depth in bricks, 1 for GZ = 8) and a communication program:
+ * region-copy tables and exchange plans run in the order they were added, on the communication stream. */
+enum { BRICKS_PLAN_FULL = 0, BRICKS_PLAN_INNER = 1, BRICKS_PLAN_SHELL = 2, BRICKS_PLAN_OWNED = 3, BRICKS_PLAN_OSKIN = 4 };
+/* what the from / to members of a copy table (and the offsets of an exchange plan) are relative to */
+enum { BRICKS_BASE_ABS = 0, BRICKS_BASE_FIELD = 1 /* a[0] of the step */, BRICKS_BASE_ARENA = 2 };
+enum {
+  BRICKS_STEP_OVERLAP = 1,      /* first sweep split into inner box (before the exchange lands) + shell */
+  BRICKS_STEP_EARLY = 2,        /* last sweep: owned skin first, then start the NEXT step's exchange */
+  BRICKS_STEP_EARLY_UNSPLIT = 4 /* with EARLY: a first sweep whose exchange was started early runs unsplit */
+};
+/* host only: the boxes (lo[3], hi[3] per box, i first) of plan `which` for a brick grid of gdims cells;
+ * *nboxes = 0 when the subdomain has no inner box; `boxes` holds up to 36 entries */
+int bricks_step_boxes(const unsigned gdims[3], unsigned ghost_bricks, int which, unsigned *boxes, int *nboxes);
+int bricks_step_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigned gdims[3],
+                       const unsigned *adj_host, unsigned nbricks, unsigned ghost_bricks, bricks_step **step);
+int bricks_step_destroy(bricks_step *step);
+/* borrowed: BRICKS_PLAN_INNER / SHELL / OSKIN do not exist for subdomains without an inner box */
+int bricks_step_plan(bricks_step *step, int which, bricks_plan **plan);
+/* device scratch for packed messages, owned by the step */
+int bricks_step_arena(bricks_step *step, size_t bytes, void **arena_dev);
+int bricks_step_add_copy(bricks_step *step, const bricks_region_link *links_host, int n, int src_base, int dst_base);
+/* base = BRICKS_BASE_FIELD or BRICKS_BASE_ARENA; take_ownership != 0: bricks_step_destroy destroys `ex`,
+ * else it is borrowed (destroy it after the step) */
+int bricks_step_add_exchange(bricks_step *step, bricks_exchange *ex, int base, int take_ownership);
+/* One step over nfields storage pairs (a[f], b[f]); st_iter even, the result ends in a.  Everything is
+ * enqueued asynchronously: sweeps on BRICKS_STREAM_COMPUTE, the communication program on
+ * BRICKS_STREAM_COMM.  With BRICKS_STEP_EARLY the exchange of the next step is already in flight at
+ * return: the next call must continue from the same a, and any other access to a must be preceded by
+ * bricks_sync(ctx, -1) and bricks_step_reset. */
+int bricks_step_run(bricks_step *step, int stencil_id, int st_iter, int nfields, double *const *a,
+                    double *const *b, const double *coeff_host, int flags);
+/* the communication program alone (after everything enqueued on the compute stream so far) */
+int bricks_step_exchange(bricks_step *step, double *field0);
+/* one sweep over one of the step's plans */
+int bricks_step_sweep(bricks_step *step, int which, int stencil_id, int nfields, const double *const *in,
+                      double *const *out, const double *coeff_host, int stream);
+/* forget an exchange started early (the caller rewrote the field) */
+int bricks_step_reset(bricks_step *step);
 
 #ifdef __cplusplus
 }

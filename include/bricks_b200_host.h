@@ -19,6 +19,8 @@ extern "C" {
 #endif
 
 typedef struct bricks_decomp bricks_decomp;
+struct bricks_ctx;  /* bricks_b200.h */
+struct bricks_step;
 
 /* BrickDecomp<3,8,8,8>::g_region (include/brick-mpi.h:183-191) flattened */
 typedef struct {
@@ -55,6 +57,15 @@ int bricks_decomp_shift_plan(bricks_decomp *d, size_t step, int stage, int cap, 
                              size_t *recv_off, size_t *send_off, size_t *nbytes, int *recv_peer,
                              int *send_peer);
 
+/* BrickDecomp::makeStep (include/bricks/brick-decomp.h): the library's sweep schedule (bricks_step_* of
+ * bricks_b200.h) for this decomposition with the communication program of the chosen exchange --
+ * 0 = one send/recv pair per region (BrickDecomp::exchange, brick-mpi.h:466-495), 1 = one packed
+ * message per peer rank (the role of ExchangeView, brick-mpi.h:96-123), 2 = the SHIFT exchange
+ * (brick-mpi.h:587-681) -- using the rank map of the last bricks_decomp_rank_map call.  The one
+ * entry of this header that touches a device (it uploads the tables).  The caller owns *step. */
+int bricks_decomp_step_create(bricks_decomp *d, struct bricks_ctx *ctx, int rank, int nranks, int exchange_kind,
+                              size_t step_elems, struct bricks_step **step, char *what, size_t what_len);
+
 /* init_grid<3> (bricksetup.h:73-90): grid[n0*n1*n2], adj[n0*n1*n2][27] */
 int bricks_init_grid3(const long dimlist[3], unsigned *grid, unsigned *adj);
 /* copyToBrick<3> (to_brick != 0) / copyFromBrick<3> (bricksetup.h:172-221) on row-major bricks */
@@ -83,6 +94,12 @@ typedef struct {
 int bricks_strong_plan_create(unsigned dom_size, unsigned sdom_size, int nranks, int rank, const bricks_decomp *d,
                               size_t step, bricks_strong_plan **out);
 int bricks_strong_plan_destroy(bricks_strong_plan *p);
+/* makeStrongStep (include/bricks/strong-plan.h): the library's sweep schedule for the local subdomains of
+ * the plan with the communication program of strong/main.cu:397-447 (pack -> one message per peer ->
+ * unpack -> intra-GPU links); subdomain s of the exchanged field lives at a_base + s * sub_bytes on the
+ * device.  Touches the device (uploads tables).  The caller owns *step. */
+int bricks_strong_step_create(const bricks_strong_plan *p, struct bricks_ctx *ctx, int rank, const bricks_decomp *d,
+                              void *a_base, size_t sub_bytes, struct bricks_step **step, size_t *sent_bytes);
 int bricks_strong_plan_sizes(const bricks_strong_plan *p, unsigned long *first_id, unsigned long *last_id,
                              size_t *nlinks, int *nsend_peers, int *nrecv_peers);
 int bricks_strong_plan_links(const bricks_strong_plan *p, bricks_strong_link *out);

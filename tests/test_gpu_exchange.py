@@ -209,6 +209,76 @@ def test_multi_gpu_weak_step_equals_global_periodic_array(built, oracle, nranks,
         assert relerr(interior_of(got[r]), e) <= REL_TOL, r
 
 
+@pytest.mark.parametrize("kind", ("regions", "packed", "shift"))
+@pytest.mark.parametrize("nranks", (1, 2, 4, 8))
+def test_exchange_kinds_fill_the_ghost_zone_like_the_oracle(built, oracle, nranks, kind):
+    """every form of the exchange the step object can run -- one send/recv pair per region
+    (BrickDecomp::exchange, brick-mpi.h:466-495), one packed message per peer (the role of
+    ExchangeView, brick-mpi.h:96-123) and the SHIFT exchange (brick-mpi.h:587-681) -- leaves the
+    storage bit-identical to the oracle's emulation on `nranks` virtual ranks"""
+    if _ndev(built) < nranks:
+        pytest.skip("needs %d GPUs" % nranks)
+    from bricklib_b200 import weak
+    dims = (32, 40, 48)
+    procdims = built.cart_dims(nranks)
+    nb = built.Decomp(dims, 8).nbricks
+    fields = [built.uniform(nb * 512, seed=700 + r) for r in range(nranks)]
+
+    def fn(r, c):
+        sub = weak.WeakSubdomain(c, dims, 7, rank=r, procdims=procdims, exchange=kind)
+        sub.upload(fields[r])
+        sub.exchange_only()
+        c.sync()
+        out = sub.download()
+        sub.close()
+        return out
+
+    got = _ranks_in_threads(built, nranks, fn)
+    odec = oracle.Decomp(dims, 8)
+    exp = oracle.exchange([f.copy() for f in fields], odec, procdims)
+    for r in range(nranks):
+        assert np.array_equal(got[r].view(np.uint64), exp[r].view(np.uint64)), r
+
+
+def test_plan_rejects_an_adjacency_that_contradicts_the_grid(ctx, built):
+    """the marching kernels take the +i / +-k neighbours from the grid, the reference accessor from
+    adj (brick.h:229-246): a BrickInfo that is not lattice-consistent is an error, not a silent
+    difference"""
+    dec = built.Decomp((16, 16, 16), 8)
+    adj = dec.adj.copy()
+    b = int(dec.grid[1, 1, 1])
+    adj[b, 14] = int(dec.grid[2, 2, 2])
+    with pytest.raises(built.BricksError, match="consistent with the grid"):
+        built.Plan(ctx, dec.grid, adj)
+    dec.close()
+
+
+def test_derived_plans_share_tables_and_give_the_same_sweep(ctx, built):
+    """bricks_plan_derive: a plan over other boxes of the parent's grid borrows its device tables"""
+    dec = built.Decomp((32, 32, 32), 8)
+    g = tuple(int(x) for x in dec.gdims)
+    parent = built.Plan(ctx, dec.grid, dec.adj)
+    own = [((1, 1, 1), tuple(x - 1 for x in g))]
+    child = built.Plan(ctx, boxes=own, parent=parent)
+    alone = built.Plan(ctx, dec.grid, dec.adj, own)
+    assert child.device_tables() == parent.device_tables() != alone.device_tables()
+    f = built.uniform(dec.nbricks * 512, seed=4)
+    d_in = ctx.upload(f)
+    outs = []
+    for p in (child, alone):
+        d = ctx.upload(np.zeros_like(f))
+        p.stencil(125, d_in, d)
+        ctx.sync()
+        outs.append(ctx.download(d, dec.nbricks * 512))
+        ctx.free(d)
+    assert np.array_equal(outs[0].view(np.uint64), outs[1].view(np.uint64)) and outs[0].any()
+    child.close()
+    alone.close()
+    parent.close()
+    ctx.free(d_in)
+    dec.close()
+
+
 def test_host_steps_pipeline_matches_plain_step(ctx, built):
     """the software-pipelined host-fed steps (two device pairs, copy streams) give the same field
     as upload -> step -> download, for every step of the pipeline"""
@@ -231,19 +301,22 @@ def test_host_steps_pipeline_matches_plain_step(ctx, built):
 
 
 @pytest.mark.parametrize("which", (7, 25, 125))
-def test_early_exchange_schedule_is_bitwise_the_plain_schedule(ctx, built, which):
-    """starting the next step's exchange right after the last sweep's skin bricks (early=True)
-    changes the order of launches only: three steps give the same bits on the owned bricks"""
+@pytest.mark.parametrize("kind", ("regions", "packed"))
+def test_early_exchange_schedule_is_bitwise_the_plain_schedule(ctx, built, which, kind):
+    """starting the next step's exchange right after the last sweep's skin bricks (early), with the
+    following first sweep split or unsplit, changes the order of launches only: three steps give
+    the same bits on the owned bricks as the serial schedule"""
     from bricklib_b200 import weak
-    sub = weak.WeakSubdomain(ctx, (32, 40, 48), which)
+    sub = weak.WeakSubdomain(ctx, (32, 40, 48), which, exchange=kind)
     f = sub.host_field()
     res = []
-    for early in (False, True):
+    for overlap, early, unsplit in ((False, False, False), (True, False, False), (True, True, False), (True, True, True)):
         sub.upload(f)
         for _ in range(3):
-            sub.step(overlap=True, early=early)
+            sub.step(overlap=overlap, early=early, unsplit=unsplit)
         ctx.sync()
         res.append(sub.download())
     n = int(sub.dec.sep_pos[1]) * 512
-    assert np.array_equal(res[0][:n].view(np.uint64), res[1][:n].view(np.uint64))
+    for r in res[1:]:
+        assert np.array_equal(res[0][:n].view(np.uint64), r[:n].view(np.uint64))
     sub.close()

@@ -1,6 +1,7 @@
-"""Full-size (512^3, the size BASELINE.json names) checks of the CUDA path.  The oracle cannot
-sweep 287k bricks of a 125-point stencil in seconds, so the whole field is checked through
-size-independent properties and a sample of bricks is checked against the oracle."""
+"""Full-size (512^3, the size BASELINE.json names) checks of the CUDA path: the WHOLE field (all
+287 496 bricks, ghost bricks included) against the compiled reference (oracle/_ref: the reference's
+own codegen brick kernels, a fraction of a second per sweep on the host cores), a sample of bricks
+against the slow C oracle as a second opinion, and size-independent properties."""
 import numpy as np
 import pytest
 
@@ -39,6 +40,33 @@ def big(ctx, built):
     for p in (d_a, d_b, d_c):
         ctx.free(p)
     dec.close()
+
+
+@pytest.mark.parametrize("which", STENCILS)
+def test_512_whole_field_matches_compiled_reference(ctx, built, big, which):
+    """every brick of the 66^3-brick grid, CUDA sweep vs the reference's generated brick kernel
+    (brick(...) of weak/main.cpp:140-170 / stencils/3axis.cpp:57-66 compiled from /root/reference by
+    oracle/Makefile) on the same field: <= 1e-12 max relative error over all 147 197 952 points"""
+    from oracle import refload as R
+    from bricklib_b200 import synth
+    if not R.available():
+        pytest.skip("oracle/_ref is not built for this host ISA")
+    dec, plan, (d_a, d_b, _), nb = big["dec"], big["plan"], big["d"], big["nb"]
+    coeff = synth.coefficients() if which == 0 else None
+    ctx.h2d(d_a, big["fa"])
+    ctx.memset(d_b, 0, nb * 4096)
+    plan.stencil(which, d_a, d_b, 512, 512, coeff)
+    ctx.sync()
+    got = ctx.download(d_b, nb * 512)
+    exp = R.aligned_empty(nb * 512)
+    exp[:] = 0.0
+    inp = R.aligned_empty(nb * 512)
+    inp[:] = big["fa"]
+    blist = dec.grid.reshape(-1)
+    R.brick_sweep_rm(which, dec.adj, blist, inp, exp, 512, coeff)
+    assert blist.size == 66 ** 3 and np.unique(blist).size == blist.size
+    assert relerr(got[512:], exp[512:]) <= REL_TOL
+    assert np.all(got[:512] == 0.0)  # the sentinel brick is never written
 
 
 @pytest.mark.parametrize("which", STENCILS)

@@ -18,31 +18,39 @@ def _paint(shape, boxes):
 
 
 @pytest.mark.parametrize("g", [(6, 7, 8), (66, 66, 66), (18, 18, 18), (5, 5, 5)])
-def test_shell_slabs_tile_the_grid_minus_the_inner_box(g):
-    """weak.shell_boxes / shell_between (the boxes of the overlapped sweeps, weak/main.cu:246-287
-    has no such split): every cell outside the inner box exactly once, none inside"""
-    from bricklib_b200 import weak
-    inner_lo, inner_hi = (2, 2, 2), tuple(x - 2 for x in g)
-    a = _paint(g[::-1], weak.shell_boxes(g, inner_lo, inner_hi))
+def test_shell_slabs_tile_the_grid_minus_the_inner_box(built, g):
+    """the boxes of the library's sweep schedule (bricks_step_boxes; weak/main.cu:246-287 has no such
+    split): shell = every cell outside the inner box exactly once, none inside; owned skin = owned
+    box minus inner box"""
+    inner = built.step_boxes(g, built.PLAN_INNER)
+    assert inner == [((2, 2, 2), tuple(x - 2 for x in g))]
+    (inner_lo, inner_hi), = inner
+    assert built.step_boxes(g, built.PLAN_FULL) == [((0, 0, 0), g)]
+    assert built.step_boxes(g, built.PLAN_OWNED) == [((1, 1, 1), tuple(x - 1 for x in g))]
+    a = _paint(g[::-1], built.step_boxes(g, built.PLAN_SHELL))
     want = np.ones(g[::-1], np.int32)
     want[inner_lo[2]:inner_hi[2], inner_lo[1]:inner_hi[1], inner_lo[0]:inner_hi[0]] = 0
     assert np.array_equal(a, want)
     # owned skin = owned box minus inner box (the bricks the next exchange sends)
-    own_lo, own_hi = (1, 1, 1), tuple(x - 1 for x in g)
-    b = _paint(g[::-1], weak.shell_between(own_lo, own_hi, inner_lo, inner_hi))
+    b = _paint(g[::-1], built.step_boxes(g, built.PLAN_OSKIN))
     want2 = np.zeros(g[::-1], np.int32)
     want2[1:g[2] - 1, 1:g[1] - 1, 1:g[0] - 1] = 1
     want2[inner_lo[2]:inner_hi[2], inner_lo[1]:inner_hi[1], inner_lo[0]:inner_hi[0]] = 0
     assert np.array_equal(b, want2)
 
 
+def test_subdomains_without_an_inner_box_have_no_split_plans(built):
+    for which in (built.PLAN_INNER, built.PLAN_SHELL, built.PLAN_OSKIN):
+        assert built.step_boxes((4, 4, 4), which) == []
+    assert built.step_boxes((4, 4, 4), built.PLAN_OWNED) == [((1, 1, 1), (3, 3, 3))]
+
+
 def test_owned_skin_covers_every_brick_an_exchange_sends(built):
     """the early-exchange schedule may start the exchange after the owned-skin slabs only if
     every skin region of BrickDecomp lies inside them"""
-    from bricklib_b200 import weak
     dec = built.Decomp((48, 32, 40), 8)
     g = tuple(int(x) for x in dec.gdims)
-    slabs = weak.shell_between((1, 1, 1), tuple(x - 1 for x in g), (2, 2, 2), tuple(x - 2 for x in g))
+    slabs = built.step_boxes(g, built.PLAN_OSKIN)
     covered = _paint(g[::-1], slabs).astype(bool)
     ids = set(int(x) for x in dec.grid[covered])
     for r in dec.skin:

@@ -26,7 +26,7 @@ names=("$@"); [ ${#names[@]} -eq 0 ] && names=("${!FLAGS[@]}")
 for n in "${names[@]}"; do
   [ -z "${FLAGS[$n]:-}" ] && { echo "unknown variant $n"; exit 1; }
   # WAIT_TRAP=0 builds without the hang guard (final timing of a variant that already ran clean)
-  guard="-DMARCH_WAIT_TRAP"; [ "${WAIT_TRAP:-1}" = 0 ] && guard=""
+  guard="-DMARCH_WAIT_TRAP -DBRICKS_EXPERIMENT"; [ "${WAIT_TRAP:-1}" = 0 ] && guard=""
   ( BRICKS_EXP_NAME=$n BRICKS_EXP_FLAGS="${FLAGS[$n]} $guard" python bricklib_b200/build.py >/dev/null && echo "built $n" ) &
 done
 wait
