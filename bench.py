@@ -344,7 +344,7 @@ def init_ranks(args):
     return ctx, rank, world, local, dist, barrier, max_over_ranks, gather
 
 
-def parity_block(ctx, rank, world, gather, overlap, early, shift):
+def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False):
     """Correctness evidence inside the run the driver times (module docstring).  Same code path as
     the timed loop -- WeakSubdomain over the C ABI, NCCL between the ranks -- on PARITY_DIMS per
     rank.  Checked on rank 0 against (1) the oracle's restatement of BrickDecomp::exchange
@@ -354,7 +354,7 @@ def parity_block(ctx, rank, world, gather, overlap, early, shift):
     dims = PARITY_DIMS
     procdims = capi.cart_dims(world)
     out = {"nranks": world, "subdomain_per_rank": list(dims), "process_grid": list(procdims), "tolerance": REL_TOL,
-           "schedule": {"overlap": overlap, "early_exchange": early, "shift_exchange": shift},
+           "schedule": {"overlap": overlap, "early_exchange": early, "exchange": kind, "unsplit": unsplit},
            "checker": "oracle/oracle.py exchange() (bit-exact) and the global periodic array through the oracle's "
                       "array stencil"}
     ok = True
@@ -364,7 +364,7 @@ def parity_block(ctx, rank, world, gather, overlap, early, shift):
         odec = O.Decomp(dims, 8)
 
     # (1) one bare exchange of a random storage
-    sub = weak.WeakSubdomain(ctx, dims, 7, rank=rank, procdims=procdims, shift=shift)
+    sub = weak.WeakSubdomain(ctx, dims, 7, rank=rank, procdims=procdims, exchange=kind)
     nb = sub.dec.nbricks
     f = capi.uniform(nb * 512, seed=9000 + rank)
     sub.upload(f)
@@ -393,11 +393,11 @@ def parity_block(ctx, rank, world, gather, overlap, early, shift):
     errs = {}
     nsteps = 2
     for which in (7, 125):
-        sub = weak.WeakSubdomain(ctx, dims, which, rank=rank, procdims=procdims, shift=shift)
+        sub = weak.WeakSubdomain(ctx, dims, which, rank=rank, procdims=procdims, exchange=kind)
         f0 = sub.host_field()
         sub.upload(f0)
         for _ in range(nsteps):
-            sub.step(overlap=overlap, early=early)
+            sub.step(overlap=overlap, early=early, unsplit=unsplit)
         ctx.sync()
         res = gather(sub.download())
         f0s = gather(f0)
@@ -446,20 +446,30 @@ def run_gpu(args, which):
 
     parity = None
     if not args.no_parity:
-        parity = parity_block(ctx, rank, world, gather, overlap, early, args.shift_exchange)
+        parity = parity_block(ctx, rank, world, gather, overlap, early, args.exchange, args.unsplit)
         bad = 0.0 if (rank != 0 or parity["ok"]) else 1.0
         if max_over_ranks(bad) > 0:
             if rank == 0:
                 print(json.dumps({"error": "parity check failed", "parity": parity}), flush=True)
             return 3
 
-    sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims, shift=args.shift_exchange)
+    sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims, exchange=args.exchange)
     field = sub.host_field()
     sub.upload(field)
 
     # ---- device-resident timing: W warm-up steps, then exactly K steps
     for _ in range(max(args.warmup, 3)):
-        sub.step(overlap=overlap, early=early)
+        sub.step(overlap=overlap, early=early, unsplit=args.unsplit)
+    if args.trace:  # one traced step per rank, outside the timed region
+        barrier()
+        sub.step_obj.trace(True)
+        sub.step(overlap=overlap, early=early, unsplit=args.unsplit)
+        tl = sub.step_obj.trace_read()
+        sub.step_obj.trace(False)
+        with open("%s.rank%d.json" % (args.trace, rank), "w") as f:
+            json.dump({"rank": rank, "nranks": world, "workload": args.workload, "exchange": sub.exchange_kind,
+                       "early": early, "unsplit": args.unsplit,
+                       "timeline_ms": [{"op": n, "start": a, "end": b} for n, a, b in tl]}, f, indent=1)
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
@@ -467,7 +477,7 @@ def run_gpu(args, which):
     n0 = capi.launch_count()
     ctx.timer_start(0)
     for _ in range(args.steps):
-        sub.step(overlap=overlap, early=early)
+        sub.step(overlap=overlap, early=early, unsplit=args.unsplit)
     ctx.stream_wait(capi.STREAM_COMPUTE, capi.STREAM_COMM)  # nothing of the K steps is left in flight
     ctx.timer_stop(0)
     ms = ctx.timer_ms(0)
@@ -517,7 +527,8 @@ def run_gpu(args, which):
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": make_config(which, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": roofline, "parity": parity,
-                "overlap": overlap, "early_exchange": early,
+                "overlap": overlap, "early_exchange": early, "early_unsplit": bool(args.unsplit and early),
+                "nccl_max_ctas": int(os.environ.get("BRICKS_NCCL_MAX_CTAS", "0")),
                 "exchange_bytes_per_step_per_gpu": exchange_bytes, "exchange": exchange_kind}
         if kernels is not None:
             line["kernels"] = kernels
@@ -753,6 +764,15 @@ def main():
     ap.add_argument("--no-early", action="store_true", help="start each exchange at the step boundary only")
     ap.add_argument("--shift-exchange", action="store_true",
                     help="weak workloads: the SHIFT exchange (3 stages, 6 messages) instead of one message per region")
+    ap.add_argument("--exchange", default=None, choices=["regions", "packed", "shift"],
+                    help="weak workloads: one send/recv pair per region (default), one packed message per peer, or SHIFT")
+    ap.add_argument("--unsplit", action="store_true", default=True,
+                    help="with the early exchange: run a first sweep whose exchange is already in flight as ONE launch "
+                         "(default: measured faster at 2 GPUs, profiles/r03_scaling/)")
+    ap.add_argument("--no-unsplit", dest="unsplit", action="store_false",
+                    help="keep the inner + shell split of every first sweep")
+    ap.add_argument("--trace", default=None, metavar="FILE",
+                    help="write every rank's timeline of one traced step (bricks_step_trace) to FILE.rank<r>.json")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=10)
@@ -764,6 +784,9 @@ def main():
     ap.add_argument("--sdom", type=int, default=STRONG_SDOM, help="strong workloads: subdomain edge")
     args = ap.parse_args()
     args.launcher_omp = os.environ.get("OMP_NUM_THREADS", "unset")
+    if args.exchange is None:
+        args.exchange = "shift" if args.shift_exchange else "regions"
+    args.shift_exchange = args.exchange == "shift"
     which = WORKLOADS[args.workload]
     if args.impl == "reference":
         return run_reference(args, which)

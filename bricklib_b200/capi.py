@@ -84,6 +84,8 @@ _SIGS = {
     "bricks_step_exchange": (C.c_int, [_vp, _vp]),
     "bricks_step_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_int]),
     "bricks_step_reset": (C.c_int, [_vp]),
+    "bricks_step_trace": (C.c_int, [_vp, C.c_int]),
+    "bricks_step_trace_read": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int), _vp, _vp, _vp]),
     # include/bricks_b200_probe.h
     "bricks_probe_dfma": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
     "bricks_probe_copy": (C.c_int, [_vp, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
@@ -413,6 +415,30 @@ class Step(object):
 
     def reset(self):
         check(lib().bricks_step_reset(self._h))
+
+    def trace(self, enable=True):
+        check(lib().bricks_step_trace(self._h, 1 if enable else 0))
+
+    def trace_read(self):
+        """timeline of the last traced step: list of (name, start_ms, end_ms), synchronises"""
+        n = C.c_int()
+        check(lib().bricks_step_trace_read(self._h, 0, C.byref(n), None, None, None))
+        if n.value == 0:
+            return []
+        codes = np.zeros(n.value, np.int32)
+        t0, t1 = np.zeros(n.value, np.float32), np.zeros(n.value, np.float32)
+        check(lib().bricks_step_trace_read(self._h, n.value, C.byref(n), _np_ptr(codes), _np_ptr(t0), _np_ptr(t1)))
+        names = {PLAN_FULL: "full", PLAN_INNER: "inner", PLAN_SHELL: "shell", PLAN_OWNED: "owned", PLAN_OSKIN: "oskin"}
+        out = []
+        for c, a, b in zip(codes.tolist(), t0.tolist(), t1.tolist()):
+            if c >= 3000:
+                name = "comm[%d] exchange" % (c - 3000)
+            elif c >= 2000:
+                name = "comm[%d] copy table" % (c - 2000)
+            else:
+                name = "sweep %d %s" % ((c - 1000) // 10 + 1, names[(c - 1000) % 10])
+            out.append((name, a, b))
+        return out
 
     def close(self):
         if self._h:

@@ -35,6 +35,15 @@ struct bricks_step {
   char *arena = nullptr;
   size_t arena_bytes = 0;
   const double *in_flight = nullptr; /* field 0 of the storages whose exchange the last step started early */
+  /* optional timeline of one step (bricks_step_trace): an event pair around every operation */
+  struct Rec {
+    int code; /* BRICKS_TRACE_* + detail */
+    cudaEvent_t e0, e1;
+  };
+  bool trace = false;
+  std::vector<Rec> recs;
+  std::vector<cudaEvent_t> pool; /* events are reused between traced steps */
+  size_t pool_used = 0;
 };
 
 namespace {
@@ -47,18 +56,48 @@ char *resolve_base(const bricks_step *st, int kind, double *field0) {
   }
 }
 
+cudaEvent_t trace_event(bricks_step *st) {
+  if (st->pool_used == st->pool.size()) {
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    st->pool.push_back(e);
+  }
+  return st->pool[st->pool_used++];
+}
+
+/* event pair around one operation on `stream` when tracing; fn enqueues the operation */
+template <typename F>
+int traced(bricks_step *st, int code, int stream, F fn) {
+  if (!st->trace) return fn();
+  bricks_step::Rec r;
+  r.code = code;
+  r.e0 = trace_event(st);
+  r.e1 = trace_event(st);
+  BRK_CUDA(cudaEventRecord(r.e0, st->ctx->streams[stream]));
+  if (int rc = fn()) return rc;
+  BRK_CUDA(cudaEventRecord(r.e1, st->ctx->streams[stream]));
+  st->recs.push_back(r);
+  return 0;
+}
+
 int run_comm(bricks_step *st, double *field0) {
   bricks_ctx *ctx = st->ctx;
   cudaStream_t s = ctx->streams[BRICKS_STREAM_COMM];
+  int idx = 0;
   for (auto &op : st->comm) {
+    int rc = 0;
     if (op.kind == 0) {
-      if (int rc = bricks::link_blob_run(ctx, op.links, resolve_base(st, op.src_base, field0),
-                                         resolve_base(st, op.dst_base, field0), s))
-        return rc;
+      rc = traced(st, BRICKS_TRACE_COPY + idx, BRICKS_STREAM_COMM, [&] {
+        return bricks::link_blob_run(ctx, op.links, resolve_base(st, op.src_base, field0),
+                                     resolve_base(st, op.dst_base, field0), s);
+      });
     } else {
       double *base = (double *)resolve_base(st, op.base, field0);
-      if (int rc = bricks_exchange_run(op.ex, base, BRICKS_STREAM_COMM)) return rc;
+      rc = traced(st, BRICKS_TRACE_EXCHANGE + idx, BRICKS_STREAM_COMM,
+                  [&] { return bricks_exchange_run(op.ex, base, BRICKS_STREAM_COMM); });
     }
+    if (rc) return rc;
+    ++idx;
   }
   return 0;
 }
@@ -137,6 +176,7 @@ int bricks_step_destroy(bricks_step *st) {
   if (!st) return 0;
   cudaSetDevice(st->ctx->device);
   for (int i = 4; i >= 0; --i) bricks_plan_destroy(st->plans[i]); /* derived plans before their parent */
+  for (cudaEvent_t e : st->pool) cudaEventDestroy(e);
   for (auto &op : st->comm) {
     if (op.kind == 0) bricks::link_blob_free(&op.links);
     if (op.kind == 1 && op.owned) bricks_exchange_destroy(op.ex);
@@ -205,6 +245,34 @@ int bricks_step_sweep(bricks_step *st, int which, int stencil_id, int nfields, c
   return bricks_stencil(st->plans[which], stencil_id, nfields, in, out, 512, 512, coeff_host, stream);
 }
 
+int bricks_step_trace(bricks_step *st, int enable) {
+  BRK_ARG(st);
+  st->trace = enable != 0;
+  return 0;
+}
+
+int bricks_step_trace_read(bricks_step *st, int cap, int *n, int *codes, float *start_ms, float *end_ms) {
+  BRK_ARG(st && n);
+  *n = (int)st->recs.size();
+  if (cap <= 0 || st->recs.empty()) return 0;
+  BRK_ARG(codes && start_ms && end_ms && cap >= *n);
+  BRK_CUDA(cudaSetDevice(st->ctx->device));
+  BRK_CUDA(cudaDeviceSynchronize());
+  /* origin: the earliest start among the records */
+  cudaEvent_t origin = st->recs[0].e0;
+  for (auto &r : st->recs) {
+    float d = 0;
+    BRK_CUDA(cudaEventElapsedTime(&d, origin, r.e0));
+    if (d < 0) origin = r.e0;
+  }
+  for (size_t i = 0; i < st->recs.size(); ++i) {
+    codes[i] = st->recs[i].code;
+    BRK_CUDA(cudaEventElapsedTime(&start_ms[i], origin, st->recs[i].e0));
+    BRK_CUDA(cudaEventElapsedTime(&end_ms[i], origin, st->recs[i].e1));
+  }
+  return 0;
+}
+
 int bricks_step_reset(bricks_step *st) {
   BRK_ARG(st);
   st->in_flight = nullptr;
@@ -216,6 +284,11 @@ int bricks_step_run(bricks_step *st, int stencil_id, int st_iter, int nfields, d
   BRK_ARG(st && a && b && nfields > 0 && st_iter >= 2 && st_iter % 2 == 0);
   bricks_ctx *ctx = st->ctx;
   const int C = BRICKS_STREAM_COMPUTE, X = BRICKS_STREAM_COMM;
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  if (st->trace) { /* the timeline holds the last traced step */
+    st->recs.clear();
+    st->pool_used = 0;
+  }
   const bool overlap = (flags & BRICKS_STEP_OVERLAP) && st->has_inner;
   const bool early = overlap && (flags & BRICKS_STEP_EARLY);
   int rc = 0;
@@ -231,7 +304,9 @@ int bricks_step_run(bricks_step *st, int stencil_id, int st_iter, int nfields, d
   for (int it = 0; it < st_iter; ++it) {
     const bool last = it == st_iter - 1;
     auto sweep = [&](int which) {
-      return bricks_stencil(st->plans[which], stencil_id, nfields, src, dst, 512, 512, coeff_host, C);
+      return traced(st, BRICKS_TRACE_SWEEP + 10 * it + which, C, [&] {
+        return bricks_stencil(st->plans[which], stencil_id, nfields, src, dst, 512, 512, coeff_host, C);
+      });
     };
     if (it == 0) {
       if (overlap && !(arrived_early && (flags & BRICKS_STEP_EARLY_UNSPLIT))) {

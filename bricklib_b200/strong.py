@@ -41,45 +41,21 @@ class StrongDomain(object):
         self.in_a = [self.d_a + s * self.sub_bytes for s in range(self.nsub)]
         self.in_b = [self.d_b + s * self.sub_bytes for s in range(self.nsub)]
 
-        # the schedule and its communication program live in the library (csrc/step.cu)
-        S = self.step_obj = capi.Step(ctx, self.dec.grid, self.dec.adj, depth // 8)
+        # the schedule and its communication program (pack -> one message per peer -> unpack ->
+        # intra-GPU links; strong/main.cu:397-447, 201-208) are built by the C++ host layer
+        # (makeStrongStep, include/bricks/strong-plan.h) and run by the library (csrc/step.cu)
+        h, sent = capi.C.c_void_p(), capi.C.c_size_t()
+        capi.check(capi.lib().bricks_strong_step_create(self.plan._h, ctx._h, rank, self.dec._h,
+                                                        capi.C.c_void_p(self.d_a), self.sub_bytes,
+                                                        capi.C.byref(h), capi.C.byref(sent)))
+        S = self.step_obj = capi.Step(ctx, handle=h.value)
+        self.exchange_bytes = int(sent.value)
+        self.nlinks = len(self.plan.links)
         self.plan_full = S.plan(capi.PLAN_FULL)
         self.plan_owned = S.plan(capi.PLAN_OWNED)
         self.plan_inner = S.plan(capi.PLAN_INNER)
         self.plan_shell = S.plan(capi.PLAN_SHELL)
         self.has_inner = self.plan_inner is not None
-
-        # inter-GPU: one packed buffer per peer and direction, all inside one arena
-        peers = sorted(set(p["rank"] for p in self.plan.send) | set(p["rank"] for p in self.plan.recv))
-        send = {p["rank"]: p for p in self.plan.send}
-        recv = {p["rank"]: p for p in self.plan.recv}
-        off, so, sb, ro, rb = 0, [], [], [], []
-        for r in peers:
-            n = send[r]["bytes"] if r in send else 0
-            so.append(off), sb.append(n)
-            off += (n + 255) // 256 * 256
-        for r in peers:
-            n = recv[r]["bytes"] if r in recv else 0
-            ro.append(off), rb.append(n)
-            off += (n + 255) // 256 * 256
-        self.arena_bytes = off
-        self.exchange_bytes = int(sum(sb))
-        pack, unpack = [], []
-        for k, r in enumerate(peers):
-            if r in send:
-                pack += [(self.in_a[s] + o, so[k] + bo, n) for s, _, o, n, bo, _ in send[r]["pieces"]]
-            if r in recv:
-                unpack += [(ro[k] + bo, self.in_a[s] + o, n) for s, _, o, n, bo, _ in recv[r]["pieces"]]
-        # communication program: pack -> per-peer messages -> unpack -> intra-GPU links
-        # (strong/main.cu:416-435 and 201-208: neighbour's skin[i] -> my ghost[i])
-        if peers:
-            S.arena(max(off, 256))
-            S.add_copy(pack, capi.BASE_ABS, capi.BASE_ARENA)
-            S.add_exchange(capi.ExchangeV(ctx, rank, ro, rb, peers, so, sb, peers), capi.BASE_ARENA)
-            S.add_copy(unpack, capi.BASE_ARENA, capi.BASE_ABS)
-        self.nlinks = len(self.plan.links)
-        S.add_copy([(self.in_a[ss] + so_, self.in_a[ds] + do, n) for ss, ds, so_, do, n in self.plan.links],
-                   capi.BASE_ABS, capi.BASE_ABS)
 
     # ------------------------------------------------------------------ data
     def host_field(self, local_index):

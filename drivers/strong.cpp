@@ -1,12 +1,14 @@
 // strong.cpp -- strong-scaling driver: a fixed dom^3 periodic grid in (dom/sdom)^3 subdomains named
 // by Z-Morton ids, contiguous id ranges per GPU.  Drop-in for the reference's strong/main.cu
 // (flow :113-574) and strong/args.cpp (flags -d -s -I -v -h), with -S 7|13|25|125 for the
-// stencil, -G ngpus replacing `mpirun -np` and -n for the serial schedule.
+// stencil, -G ngpus replacing `mpirun -np`, -n for the serial schedule and -v for the validation
+// against the GLOBAL periodic array on the host (strong/main.cpp:402-476 validates against the array path).
 //
 // Per step (strong/main.cu:397-510): pack the skins bound for other GPUs, one message per peer
 // (NCCL), unpack into the ghost bricks, device copies between subdomains of the same GPU, then
-// ST_ITER sweeps, each ONE launch batched over all local subdomains.  Prints the reference's
-// lines (strong/main.cu:550-566).
+// ST_ITER sweeps, each ONE launch batched over all local subdomains -- all of it the library's
+// bricks_step_run over the program makeStrongStep builds (include/bricks/strong-plan.h), the same
+// code bench.py times.  Prints the reference's lines (strong/main.cu:550-566).
 #include <unistd.h>
 
 #include <chrono>
@@ -14,14 +16,17 @@
 #include <cstring>
 #include <memory>
 
+#include "bricks/brickcompare.h"
+#include "bricks/bricksetup.h"
 #include "bricks/multiarray.h"
 #include "bricks/strong-plan.h"
 #include "common.h"
+#include "host_twin.h"
 
 namespace {
 constexpr unsigned GZ = 8, TILE = 8;
 typedef BrickDecomp<3, 8, 8, 8> Decomp3D;
-typedef BrickStencilPlan::Box Box;
+typedef Brick<Dim<8, 8, 8>, Dim<1>> Brick3D;
 
 const char *help =
     "Running the strong-scaling brick stencil on B200s with %s\n\n"
@@ -32,39 +37,13 @@ const char *help =
     "  -s: Int, subdomain size is s^3 (default 128)\n"
     "  -I: number of iterations, default %d\n"
     "  -S: stencil 7|13|25|125, default 125\n"
-    "  -v: validate against the naive device kernel\n"
+    "  -v: validate against the stencil applied to the global periodic array on the host\n"
     "  -n: no overlap (exchange, then sweeps)\n"
     "Example usage:\n"
     "  %s -G 8 -d 1024 -s 128\n";
 
 double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-/// a RegionLink list on the device (strong/main.cu:62-83 cudaCopy)
-struct Links {
-  bricks_ctx *ctx = nullptr;
-  bricks_region_link *dev = nullptr;
-  int n = 0;
-  void upload(bricks_ctx *c, const std::vector<bricks_region_link> &host) {
-    ctx = c, n = (int)host.size();
-    if (n) gpuCheck(bricks_links_upload(c, host.data(), n, &dev));
-  }
-  void run(int stream) const {
-    if (n) gpuCheck(bricks_copy_regions(ctx, dev, n, stream));
-  }
-  ~Links() {
-    if (dev) bricks_links_free(ctx, dev);
-  }
-};
-
-std::vector<Box> shell_of(const unsigned g[3], const unsigned lo[3], const unsigned hi[3]) {
-  auto box = [](unsigned a0, unsigned a1, unsigned a2, unsigned b0, unsigned b1, unsigned b2) {
-    Box b = {{a0, a1, a2}, {b0, b1, b2}};
-    return b;
-  };
-  return {box(0, 0, 0, g[0], g[1], lo[2]),           box(0, 0, hi[2], g[0], g[1], g[2]),
-          box(0, 0, lo[2], g[0], lo[1], hi[2]),      box(0, hi[1], lo[2], g[0], g[1], hi[2]),
-          box(0, lo[1], lo[2], lo[0], hi[1], hi[2]), box(hi[0], lo[1], lo[2], g[0], hi[1], hi[2])};
-}
 }  // namespace
 
 int main(int argc, char **argv) {
@@ -144,156 +123,98 @@ int main(int argc, char **argv) {
       in_b[s] = out_b[s] = (double *)(d_b + s * sub_bytes);
     }
 
-    // link tables and the per-peer messages (strong/main.cu:188-395)
-    std::vector<int> peers;
-    for (auto &p : sp.send) peers.push_back(p.rank);
-    for (auto &p : sp.recv) peers.push_back(p.rank);
-    std::sort(peers.begin(), peers.end());
-    peers.erase(std::unique(peers.begin(), peers.end()), peers.end());
-    auto find = [](const std::vector<StrongPeer> &v, int r) -> const StrongPeer * {
-      for (auto &p : v)
-        if (p.rank == r) return &p;
-      return nullptr;
-    };
-    std::vector<size_t> so, sb, ro, rb;
-    size_t off = 0, tsize = 0;
-    for (int r : peers) {
-      const StrongPeer *p = find(sp.send, r);
-      so.push_back(off), sb.push_back(p ? p->bytes : 0);
-      off += (sb.back() + 255) / 256 * 256;
-      tsize += sb.back();
-    }
-    for (int r : peers) {
-      const StrongPeer *p = find(sp.recv, r);
-      ro.push_back(off), rb.push_back(p ? p->bytes : 0);
-      off += (rb.back() + 255) / 256 * 256;
-      tsize += rb.back();
-    }
-    char *arena = nullptr;
-    gpuCheck(gpuMalloc(&arena, std::max<size_t>(off, 256)));
-    std::vector<bricks_region_link> h_local, h_pack, h_unpack;
-    auto link = [](char *from, char *to, size_t len) { return bricks_region_link{(double *)from, (double *)to, len}; };
-    for (auto &l : sp.links)
-      h_local.push_back(link(d_a + l.src_sub * sub_bytes + l.src_off, d_a + l.dst_sub * sub_bytes + l.dst_off, l.len));
-    for (size_t k = 0; k < peers.size(); ++k) {
-      if (const StrongPeer *p = find(sp.send, peers[k]))
-        for (auto &pc : p->pieces)
-          h_pack.push_back(link(d_a + pc.sub * sub_bytes + pc.off, arena + so[k] + pc.buf_off, pc.len));
-      if (const StrongPeer *p = find(sp.recv, peers[k]))
-        for (auto &pc : p->pieces)
-          h_unpack.push_back(link(arena + ro[k] + pc.buf_off, d_a + pc.sub * sub_bytes + pc.off, pc.len));
-    }
-    Links local, pack, unpack;
-    local.upload(rk.ctx, h_local), pack.upload(rk.ctx, h_pack), unpack.upload(rk.ctx, h_unpack);
-    bricks_exchange *ex = nullptr;
-    if (!peers.empty())
-      gpuCheck(bricks_exchange_create_v(rk.ctx, rk.rank, (int)peers.size(), ro.data(), rb.data(), peers.data(), so.data(),
-                                        sb.data(), peers.data(), &ex));
-
-    // launch plans over the shared brick grid
-    const unsigned gb = GZ / TILE, zero[3] = {0, 0, 0};
-    unsigned in_lo[3], in_hi[3], ow_lo[3], ow_hi[3];
-    bool has_inner = true;
-    for (int a = 0; a < 3; ++a) {
-      in_lo[a] = 2 * gb, in_hi[a] = g[a] - 2 * gb, ow_lo[a] = gb, ow_hi[a] = g[a] - gb;
-      has_inner = has_inner && in_hi[a] > in_lo[a];
-    }
-    auto one = [](const unsigned lo[3], const unsigned hi[3]) {
-      Box b = {{lo[0], lo[1], lo[2]}, {hi[0], hi[1], hi[2]}};
-      return std::vector<Box>{b};
-    };
-    BrickStencilPlan full(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, one(zero, g));
-    BrickStencilPlan owned(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, one(ow_lo, ow_hi));
-    std::unique_ptr<BrickStencilPlan> inner, shell;
-    if (has_inner && overlap) {
-      inner.reset(new BrickStencilPlan(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, one(in_lo, in_hi)));
-      shell.reset(new BrickStencilPlan(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, shell_of(g, in_lo, in_hi)));
-    }
-
-    const int C_ = BRICKS_STREAM_COMPUTE, X = BRICKS_STREAM_COMM;
+    // the step object: box plans over the shared grid + the communication program (pack -> one
+    // message per peer -> unpack -> intra-GPU links; strong/main.cu:188-395, 397-447)
+    size_t sent = 0;
+    bricks_step *stepo = makeStrongStep(rk.ctx, rk.rank, sp, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, GZ / TILE, d_a,
+                                        sub_bytes, &sent);
+    size_t recvd = 0;
+    for (auto &p : sp.recv) recvd += p.bytes;
+    const size_t tsize = sent + recvd;
+    const int C_ = BRICKS_STREAM_COMPUTE;
+    const int flags = overlap ? BRICKS_STEP_OVERLAP : 0;
     double calltime_l = 0;
-    auto exchange = [&]() {
+    auto brick_func = [&]() {
       const double t0 = now();
-      gpuCheck(bricks_stream_wait(rk.ctx, X, C_));
-      pack.run(X);
-      if (ex) gpuCheck(bricks_exchange_run(ex, (double *)arena, X));
-      unpack.run(X);
-      local.run(X);
+      gpuCheck(bricks_step_run(stepo, which, st_iter, (int)nsub, out_a.data(), out_b.data(), nullptr, flags));
       calltime_l += now() - t0;
     };
-    auto sweeps = [&](bool naive, bool time_calc) {
-      for (int it = 0; it < st_iter; ++it) {
-        const auto &src = it % 2 ? in_b : in_a;
-        const auto &dst = it % 2 ? out_a : out_b;
-        if (naive) {
-          gpuCheck(bricks_stencil_naive(full.handle(), which, (int)nsub, src.data(), dst.data(), step, step, nullptr, C_));
-        } else if (it == 0) {
-          if (inner) {
-            if (time_calc) gpuCheck(bricks_timer_start(rk.ctx, C_, 1));
-            inner->run(which, src, dst, step, step);
-            gpuCheck(bricks_stream_wait(rk.ctx, C_, X));
-            shell->run(which, src, dst, step, step);
-          } else {
-            gpuCheck(bricks_stream_wait(rk.ctx, C_, X));
-            if (time_calc) gpuCheck(bricks_timer_start(rk.ctx, C_, 1));
-            full.run(which, src, dst, step, step);
-          }
-        } else if (it == st_iter - 1) {
-          owned.run(which, src, dst, step, step);
-        } else {
-          full.run(which, src, dst, step, step);
-        }
-      }
-      if (time_calc) gpuCheck(bricks_timer_stop(rk.ctx, C_, 1));
-    };
-    auto brick_func = [&](bool time_calc) {
-      exchange();
-      sweeps(false, time_calc);
-    };
 
-    // ---- validation: same exchange, then the naive kernel's sweeps, vs one real (overlapped) step
+    // ---- validation: one step against the stencil applied to the GLOBAL periodic array on the host
     bool ok = true;
     if (validate) {
-      char *keep = nullptr, *want = nullptr;
-      gpuCheck(gpuMalloc(&keep, nsub * sub_bytes));
-      gpuCheck(gpuMalloc(&want, nsub * sub_bytes));
-      gpuCheck(gpuMemcpy(keep, d_a, nsub * sub_bytes, gpuMemcpyDeviceToDevice));
-      exchange();
-      gpuCheck(bricks_stream_wait(rk.ctx, C_, X));
-      sweeps(true, false);
-      gpuCheck(gpuMemcpy(want, d_a, nsub * sub_bytes, gpuMemcpyDeviceToDevice));
-      gpuCheck(gpuMemcpy(d_a, keep, nsub * sub_bytes, gpuMemcpyDeviceToDevice));
-      rk.barrier->wait();
-      brick_func(false);
-      gpuCheck(bricks_sync(rk.ctx, -1));
-      std::vector<double> hg(sub_elems), hw(sub_elems);
-      double worst = 0;
-      for (unsigned s = 0; s < nsub; ++s) {
-        gpuCheck(gpuMemcpy(hg.data(), d_a + s * sub_bytes, sub_bytes, gpuMemcpyDeviceToHost));
-        gpuCheck(gpuMemcpy(hw.data(), want + s * sub_bytes, sub_bytes, gpuMemcpyDeviceToHost));
-        for (unsigned k = gb; k < g[2] - gb; ++k)
-          for (unsigned j = gb; j < g[1] - gb; ++j)
-            for (unsigned i = gb; i < g[0] - gb; ++i) {
-              const size_t b = (size_t)grid_ptr[(k * g[1] + j) * g[0] + i] * step;
-              for (unsigned e = 0; e < 512; ++e)
-                worst = std::max(worst, std::fabs(hg[b + e] - hw[b + e]) / std::max(std::fabs(hw[b + e]), 1e-300));
-            }
+      static std::vector<double> glob;  // dom^3, shared by the rank threads
+      static std::mutex glob_mutex;
+      const long D = dom_size, S = sdom_size, E = S + 2 * GZ;
+      {
+        std::lock_guard<std::mutex> lk(glob_mutex);
+        if (glob.size() != (size_t)D * D * D) glob.assign((size_t)D * D * D, 0.0);
       }
-      ok = worst <= 1e-12;
+      rk.barrier->wait();
+      const std::vector<long> dlist = {S, S, S}, pad0 = {0, 0, 0}, gzv = {(long)GZ, (long)GZ, (long)GZ}, ext = {E, E, E};
+      std::vector<double> hs(sub_elems);
+      BrickStorage view;
+      view.chunks = bInfo.nbricks, view.step = step;
+      view.dat = std::shared_ptr<bElem>(hs.data(), [](bElem *) {});
+      Brick3D bv(&bInfo, view, 0);
+      bElem *arr = zeroArray(ext);
+      // every local subdomain's interior into the global array
+      for (unsigned s_ = 0; s_ < nsub; ++s_) {
+        gpuCheck(gpuMemcpy(hs.data(), d_a + s_ * sub_bytes, sub_bytes, gpuMemcpyDeviceToHost));
+        copyFromBrick<3>(dlist, pad0, gzv, arr, const_cast<unsigned *>(grid_ptr), bv);
+        unsigned c3[3];
+        sp.coords(sp.first_id + s_, c3);
+#pragma omp parallel for collapse(2)
+        for (long k = 0; k < S; ++k)
+          for (long j = 0; j < S; ++j)
+            for (long i = 0; i < S; ++i)
+              glob[((c3[2] * S + k) * D + c3[1] * S + j) * D + c3[0] * S + i] = arr[((k + GZ) * E + j + GZ) * E + i + GZ];
+      }
+      rk.barrier->wait();
+      brick_func();
+      gpuCheck(bricks_sync(rk.ctx, -1));
+      double worst = 0;
+      bool match = true;
+      bElem *tmp = zeroArray(ext);
+      const long R = drv::stencil_radius(which);
+      for (unsigned s_ = 0; s_ < nsub; ++s_) {
+        unsigned c3[3];
+        sp.coords(sp.first_id + s_, c3);
+        // the subdomain plus its periodic ghost band, cut out of the global array
+#pragma omp parallel for collapse(2)
+        for (long k = 0; k < E; ++k)
+          for (long j = 0; j < E; ++j)
+            for (long i = 0; i < E; ++i) {
+              const long gk = ((long)c3[2] * S + k - GZ + D) % D, gj = ((long)c3[1] * S + j - GZ + D) % D,
+                         gi = ((long)c3[0] * S + i - GZ + D) % D;
+              arr[(k * E + j) * E + i] = glob[(gk * D + gj) * D + gi];
+            }
+        bElem *p = arr, *q = tmp;
+        for (int it = 0; it < st_iter; ++it) {
+          const long grow = R * (st_iter - 1 - it);
+          const long lo[3] = {(long)GZ - grow, (long)GZ - grow, (long)GZ - grow};
+          const long hi[3] = {E - GZ + grow, E - GZ + grow, E - GZ + grow};
+          twin::sweep(which, p, q, ext.data(), lo, hi);
+          std::swap(p, q);
+        }
+        gpuCheck(gpuMemcpy(hs.data(), d_a + s_ * sub_bytes, sub_bytes, gpuMemcpyDeviceToHost));
+        match = compareBrick<3>(dlist, pad0, gzv, p, const_cast<unsigned *>(grid_ptr), bv) && match;
+        worst = std::max(worst, maxRelErrBrick<3>(dlist, pad0, gzv, p, const_cast<unsigned *>(grid_ptr), bv));
+      }
+      free(arr);
+      free(tmp);
+      ok = match && worst <= 1e-12;
       rk.put(9, worst);
-      gpuCheck(gpuMemcpy(d_a, keep, nsub * sub_bytes, gpuMemcpyDeviceToDevice));
-      gpuFree(keep);
-      gpuFree(want);
       rk.barrier->wait();
     }
 
-    // ---- warm-up, timed loop, then a second pass that times the sweeps of each step
-    for (int w = 0; w < 3; ++w) brick_func(false);
+    // ---- warm-up, timed loop, then the sweeps and the exchange program of a step on their own
+    for (int w = 0; w < 3; ++w) brick_func();
     gpuCheck(bricks_sync(rk.ctx, -1));
     rk.barrier->wait();
     calltime_l = 0;
     gpuCheck(bricks_timer_start(rk.ctx, C_, 0));
-    for (int i = 0; i < iters; ++i) brick_func(false);
+    for (int i = 0; i < iters; ++i) brick_func();
     gpuCheck(bricks_timer_stop(rk.ctx, C_, 0));
     float ms = 0;
     gpuCheck(bricks_timer_elapsed_ms(rk.ctx, 0, &ms));
@@ -302,19 +223,39 @@ int main(int argc, char **argv) {
     const double call_step = calltime_l / iters;
     double calc_s = 0, pack_s = 0;
     const int cal_iters = std::min(iters, 10);
-    for (int i = 0; i < cal_iters; ++i) {
-      brick_func(true);
+    {
+      bricks_plan *probe = nullptr;
+      const bool split = overlap && bricks_step_plan(stepo, BRICKS_PLAN_INNER, &probe) == 0;
+      gpuCheck(bricks_timer_start(rk.ctx, C_, 1));
+      for (int i = 0; i < cal_iters; ++i)
+        for (int it = 0; it < st_iter; ++it) {
+          const auto &src = it % 2 ? in_b : in_a;
+          const auto &dst = it % 2 ? out_a : out_b;
+          auto sw = [&](int plan) {
+            gpuCheck(bricks_step_sweep(stepo, plan, which, (int)nsub, src.data(), dst.data(), nullptr, C_));
+          };
+          if (it == 0 && split) {
+            sw(BRICKS_PLAN_INNER);
+            sw(BRICKS_PLAN_SHELL);
+          } else if (it == st_iter - 1) {
+            sw(BRICKS_PLAN_OWNED);
+          } else {
+            sw(BRICKS_PLAN_FULL);
+          }
+        }
+      gpuCheck(bricks_timer_stop(rk.ctx, C_, 1));
       float cms = 0;
       gpuCheck(bricks_timer_elapsed_ms(rk.ctx, 1, &cms));
-      calc_s += cms * 1e-3;
-    }
-    for (int i = 0; i < cal_iters; ++i) {  // pack + unpack + local links alone
-      gpuCheck(bricks_timer_start(rk.ctx, X, 2));
-      pack.run(X), unpack.run(X), local.run(X);
-      gpuCheck(bricks_timer_stop(rk.ctx, X, 2));
+      calc_s = cms * 1e-3;
+      // the communication program alone (pack, messages, unpack, local links), nothing to hide behind
+      gpuCheck(bricks_sync(rk.ctx, -1));
+      rk.barrier->wait();
+      gpuCheck(bricks_timer_start(rk.ctx, BRICKS_STREAM_COMM, 2));
+      for (int i = 0; i < cal_iters; ++i) gpuCheck(bricks_step_exchange(stepo, out_a[0]));
+      gpuCheck(bricks_timer_stop(rk.ctx, BRICKS_STREAM_COMM, 2));
       float pms = 0;
       gpuCheck(bricks_timer_elapsed_ms(rk.ctx, 2, &pms));
-      pack_s += pms * 1e-3;
+      pack_s = pms * 1e-3;
     }
     const long cnt = (long)iters * st_iter;
     const double total_l = ms * 1e-3 / cnt, calc_l = calc_s / ((double)cal_iters * st_iter);
@@ -333,7 +274,7 @@ int main(int argc, char **argv) {
       const double total = rk.stats(0).max;
       std::cout << "Bri: " << total << " : " << total << std::endl;
       std::cout << "calc : " << rk.stats(1) << std::endl;
-      std::cout << "pack : " << rk.stats(2) << std::endl;
+      std::cout << "pack : " << rk.stats(2) << std::endl;  // the whole exchange program run alone
       std::cout << "  | pack speed (GB/s): " << rk.stats(3) << std::endl;
       std::cout << "call : " << rk.stats(4) << std::endl;
       std::cout << "wait : " << rk.stats(5) << std::endl;
@@ -353,11 +294,11 @@ int main(int argc, char **argv) {
       }
       rk.barrier->wait();
       if (rk.rank == 0)
-        std::cout << (failures ? "Not validated" : "Validated") << ", max relative error vs naive kernel " << rk.stats(9).max
-                  << std::endl;
+        std::cout << (failures ? "Not validated" : "Validated") << ", max relative error vs the global periodic array "
+                  << rk.stats(9).max << std::endl;
     }
-    if (ex) bricks_exchange_destroy(ex);
-    gpuFree(arena);
+    gpuCheck(bricks_sync(rk.ctx, -1));
+    bricks_step_destroy(stepo);
     gpuFree(d_a);
     gpuFree(d_b);
   });

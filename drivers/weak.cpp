@@ -1,8 +1,12 @@
 // weak.cpp -- weak-scaling driver: one periodic subdomain per GPU, one halo exchange per ST_ITER
 // stencil sweeps.  Drop-in for the reference's weak/main.cu (flow :45-338) and weak/args.cpp
 // (flags -d -s -I -b -h), with -S 7|13|25|125 selecting the stencil at run time (the reference
-// picks it with -DMPI_7PT...), -G ngpus replacing `mpirun -np`, -v for the validation twin and
-// -n for the reference's serial schedule (no exchange/compute overlap).  -m uses the SHIFT exchange.
+// picks it with -DMPI_7PT...), -G ngpus replacing `mpirun -np`, -v for the validation against the
+// host ARRAY twin (weak/main.cu:143-214, 321-323), -n for the reference's serial schedule (no
+// exchange/compute overlap), -E to start every exchange at the step boundary only, -m for the SHIFT
+// exchange and -p for one packed message per peer.  The step itself (exchange + ST_ITER sweeps, the
+// body of brick_func, weak/main.cu:246-287) is the library's bricks_step_run -- the same code
+// bench.py times.
 //
 // Prints the reference's lines (weak/main.cu:304-318): Bri / calc / move / call / wait /
 // "  | MPI size (MB)" / "  | MPI speed (GB/s)" / "perf X GStencil/s".
@@ -16,12 +20,12 @@
 #include "bricks/bricksetup.h"
 #include "bricks/multiarray.h"
 #include "common.h"
+#include "host_twin.h"
 
 namespace {
 constexpr unsigned GZ = 8, TILE = 8;
 typedef Brick<Dim<8, 8, 8>, Dim<1>> Brick3D;
 typedef BrickDecomp<3, 8, 8, 8> Decomp3D;
-typedef BrickStencilPlan::Box Box;
 
 const char *help =
     "Running the weak-scaling brick stencil on B200s with %s\n\n"
@@ -35,31 +39,24 @@ const char *help =
     "  Benchmark control:\n"
     "  -I: number of iterations, default %d\n"
     "  -S: stencil 7|13|25|125, default 7\n"
-    "  -v: validate against the naive device kernel\n"
+    "  -v: validate against the array computation on the host (periodic exchange between the ranks' arrays)\n"
     "  -n: no overlap (exchange, then sweeps)\n"
+    "  -E: no early exchange (default with more than one GPU: the next step's exchange starts behind the\n"
+    "      last sweep's skin bricks)\n"
     "  -m: SHIFT exchange (three stages, six messages) instead of one message per region\n"
+    "  -p: one packed message per peer rank (pack kernel, send/recv, unpack kernel)\n"
     "Example usage:\n"
     "  %s -G 8 -s 512,512,512 -S 125\n";
 
 double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-/// six slabs covering [0,g) minus [lo,hi)
-std::vector<Box> shell_of(const unsigned g[3], const unsigned lo[3], const unsigned hi[3]) {
-  auto box = [](unsigned a0, unsigned a1, unsigned a2, unsigned b0, unsigned b1, unsigned b2) {
-    Box b = {{a0, a1, a2}, {b0, b1, b2}};
-    return b;
-  };
-  return {box(0, 0, 0, g[0], g[1], lo[2]),         box(0, 0, hi[2], g[0], g[1], g[2]),
-          box(0, 0, lo[2], g[0], lo[1], hi[2]),    box(0, hi[1], lo[2], g[0], g[1], hi[2]),
-          box(0, lo[1], lo[2], lo[0], hi[1], hi[2]), box(hi[0], lo[1], lo[2], g[0], hi[1], hi[2])};
-}
 }  // namespace
 
 int main(int argc, char **argv) {
   std::vector<unsigned> dom(3, 64);
   int sel = 0, iters = 100, ngpus = 1, which = 7, c;
-  bool bin = false, validate = false, overlap = true, shift = false;
-  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vnm")) != -1) {
+  bool bin = false, validate = false, overlap = true, shift = false, packed = false, no_early = false;
+  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vnmpE")) != -1) {
     switch (c) {
       case 'b': bin = true; break;
       case 'd': drv::parse_tuple(optarg, dom, 3); sel = sel ? -2 : 1; break;
@@ -70,6 +67,8 @@ int main(int argc, char **argv) {
       case 'v': validate = true; break;
       case 'n': overlap = false; break;
       case 'm': shift = true; break;
+      case 'p': packed = true; break;
+      case 'E': no_early = true; break;
       default: printf("Unknown options %c\n", c);  // fall through
       case 'h': printf(help, argv[0], iters, argv[0]); sel = sel ? -2 : -1;
     }
@@ -152,130 +151,124 @@ int main(int argc, char **argv) {
     bElem *in_ptr = randomArray(ext, 1234 + rk.rank);
     copyToBrick<3>(ext, in_ptr, const_cast<unsigned *>(grid_ptr), bIn);
     memset(bStorageOut.dat.get(), 0, bStorageOut.step * bStorageOut.chunks * sizeof(bElem));
-    free(in_ptr);
 
-    // device side: storages, launch plans, exchange view
+    // device side: storages and the library's step object (box plans + communication program)
     BrickStorage bStorage_dev = movBrickStorage(bStorage, gpuMemcpyHostToDevice);
     BrickStorage bStorageOut_dev = movBrickStorage(bStorageOut, gpuMemcpyHostToDevice);
-    Brick3D bIn_dev(&bInfo, bStorage_dev, 0), bOut_dev(&bInfo, bStorageOut_dev, 0);
-    const unsigned gb = GZ / TILE;
-    const unsigned zero[3] = {0, 0, 0};
-    unsigned in_lo[3], in_hi[3], ow_lo[3], ow_hi[3];
-    bool has_inner = true;
-    for (int a = 0; a < 3; ++a) {
-      in_lo[a] = 2 * gb, in_hi[a] = g[a] - 2 * gb, ow_lo[a] = gb, ow_hi[a] = g[a] - gb;
-      has_inner = has_inner && in_hi[a] > in_lo[a];
-    }
-    auto one = [](const unsigned lo[3], const unsigned hi[3]) {
-      Box b = {{lo[0], lo[1], lo[2]}, {hi[0], hi[1], hi[2]}};
-      return std::vector<Box>{b};
-    };
-    BrickStencilPlan full(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, one(zero, g));
-    BrickStencilPlan owned(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, one(ow_lo, ow_hi));
-    std::unique_ptr<BrickStencilPlan> inner, shell;
-    if (has_inner && overlap) {
-      inner.reset(new BrickStencilPlan(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, one(in_lo, in_hi)));
-      shell.reset(new BrickStencilPlan(rk.ctx, grid_ptr, g, &bInfo.adj[0][0], bInfo.nbricks, shell_of(g, in_lo, in_hi)));
-    }
-    ExchangeView ev_direct = bDecomp.exchangeView(bStorage_dev);
+    std::string exchange_text;
+    bricks_step *step = bDecomp.makeStep(shift ? Decomp3D::STEP_SHIFT : (packed ? Decomp3D::STEP_PACKED : Decomp3D::STEP_REGIONS),
+                                         Brick3D::BRICKSIZE, &exchange_text);
     size_t tsize = 0;
-    for (size_t n : ev_direct.seclen) tsize += n;
-    // -m: the SHIFT exchange (multiStageExchangeView, brick-mpi.h:587-681): 3 stages, 6 messages
-    MultiStageExchangeView ev_shift;
-    if (shift) ev_shift = bDecomp.multiStageExchangeView(bStorage_dev);
-    struct {
-      ExchangeView *d;
-      MultiStageExchangeView *m;
-      void start() { m ? m->start() : d->start(); }
-      void wait() { m ? m->wait() : d->wait(); }
-    } ev = {&ev_direct, shift ? &ev_shift : nullptr};
+    for (size_t i = 0; i < bDecomp.ghost.size(); ++i)
+      tsize += (size_t)(bDecomp.ghost[i].len - bDecomp.ghost[i].first_pad - bDecomp.ghost[i].last_pad) * bStorage.step *
+               sizeof(bElem);
+    const bool early = overlap && !no_early && nranks > 1;
+    const int flags = (overlap ? BRICKS_STEP_OVERLAP : 0) | (early ? BRICKS_STEP_EARLY : 0);
+    if (rk.rank == 0)
+      std::cout << "exchange: " << exchange_text << (early ? ", started early behind the last sweep" : "") << std::endl;
 
+    double *fa[1] = {bStorage_dev.dat.get()}, *fb[1] = {bStorageOut_dev.dat.get()};
     double calltime_l = 0;
     // one step = exchange + ST_ITER sweeps (weak/main.cu:246-287); everything is asynchronous
-    auto brick_func = [&](bool time_calc) {
+    auto brick_func = [&]() {
       const double t0 = now();
-      ev.start();
+      gpuCheck(bricks_step_run(step, which, st_iter, 1, fa, fb, nullptr, flags));
       calltime_l += now() - t0;
-      Brick3D *src = &bIn_dev, *dst = &bOut_dev;
-      for (int it = 0; it < st_iter; ++it) {
-        if (it == 0) {
-          if (inner) {
-            if (time_calc) gpuCheck(bricks_timer_start(rk.ctx, BRICKS_STREAM_COMPUTE, 1));
-            inner->run(which, *src, *dst);
-            ev.wait();
-            shell->run(which, *src, *dst);
-          } else {
-            ev.wait();
-            if (time_calc) gpuCheck(bricks_timer_start(rk.ctx, BRICKS_STREAM_COMPUTE, 1));
-            full.run(which, *src, *dst);
-          }
-        } else if (it == st_iter - 1) {
-          owned.run(which, *src, *dst);
-        } else {
-          full.run(which, *src, *dst);
-        }
-        std::swap(src, dst);
-      }
-      if (time_calc) gpuCheck(bricks_timer_stop(rk.ctx, BRICKS_STREAM_COMPUTE, 1));
     };
 
-    // validation twin before the timed loop consumes the initial field
+    // validation before the timed loop consumes the initial field: one step against the ARRAY twin
+    // on the host (weak/main.cu:143-214 array_stencil with exchangeArr, :321-323 compareBrick)
     bool ok = true;
     if (validate) {
-      BrickStorage a2 = movBrickStorage(bStorage, gpuMemcpyHostToDevice);
-      BrickStorage b2 = movBrickStorage(bStorageOut, gpuMemcpyHostToDevice);
-      bDecomp.exchange(a2);
-      const double *i2[1];
-      double *o2[1];
-      bElem *p = a2.dat.get(), *q = b2.dat.get();
-      for (int it = 0; it < st_iter; ++it) {
-        i2[0] = p, o2[0] = q;
-        gpuCheck(bricks_stencil_naive(full.handle(), which, 1, i2, o2, a2.step, b2.step, nullptr, BRICKS_STREAM_COMPUTE));
-        std::swap(p, q);
+      static std::vector<double *> arrays;  // the ranks' arrays: the host stand-in for exchangeArr
+      static std::mutex arrays_mutex;
+      {
+        std::lock_guard<std::mutex> lk(arrays_mutex);
+        arrays.resize(nranks);
+        arrays[rk.rank] = in_ptr;
       }
       rk.barrier->wait();
-      brick_func(false);
+      const long dml[3] = {(long)dom_size[0], (long)dom_size[1], (long)dom_size[2]};
+      twin::fill_ghost(in_ptr, arrays, dml, GZ, [&](int sk, int sj, int si) {
+        BitSet n;
+        if (si) n.flip(si * 1);
+        if (sj) n.flip(sj * 2);
+        if (sk) n.flip(sk * 3);
+        return bDecomp.rank_map.at(n.set);
+      });
+      rk.barrier->wait();  // nobody sweeps before every ghost band is filled
+      bElem *out_ptr = zeroArray(ext);
+      bElem *p = in_ptr, *q = out_ptr;
+      const long R = drv::stencil_radius(which);
+      for (int it = 0; it < st_iter; ++it) {
+        const long grow = R * (st_iter - 1 - it);  // the valid region shrinks by R per sweep
+        const long lo[3] = {(long)GZ - grow, (long)GZ - grow, (long)GZ - grow};
+        const long hi[3] = {ext[0] - GZ + grow, ext[1] - GZ + grow, ext[2] - GZ + grow};
+        twin::sweep(which, p, q, ext.data(), lo, hi);
+        std::swap(p, q);
+      }
+      brick_func();
       gpuCheck(bricks_sync(rk.ctx, -1));
+      gpuCheck(bricks_step_reset(step));
       BrickStorage got = movBrickStorage(bStorage_dev, gpuMemcpyDeviceToHost);
-      BrickStorage want = movBrickStorage(a2, gpuMemcpyDeviceToHost);
-      double worst = 0;
-      for (unsigned k = gb; k < g[2] - gb; ++k)
-        for (unsigned j = gb; j < g[1] - gb; ++j)
-          for (unsigned i = gb; i < g[0] - gb; ++i) {
-            const size_t b = (size_t)grid_ptr[(k * g[1] + j) * g[0] + i] * got.step;
-            for (unsigned e = 0; e < 512; ++e) {
-              const double w = want.dat.get()[b + e], d = std::fabs(got.dat.get()[b + e] - w);
-              worst = std::max(worst, d / std::max(std::fabs(w), 1e-300));
-            }
-          }
-      ok = worst <= 1e-12;
+      Brick3D bGot(&bInfo, got, 0);
+      const std::vector<long> dlist = {dml[0], dml[1], dml[2]}, pad0 = {0, 0, 0}, gzv = {(long)GZ, (long)GZ, (long)GZ};
+      const bool match = compareBrick<3>(dlist, pad0, gzv, p, const_cast<unsigned *>(grid_ptr), bGot);
+      const double worst = maxRelErrBrick<3>(dlist, pad0, gzv, p, const_cast<unsigned *>(grid_ptr), bGot);
+      ok = match && worst <= 1e-12;
       rk.put(7, worst);
+      rk.barrier->wait();  // the neighbours have read this rank's array
+      if (p == out_ptr) std::swap(in_ptr, out_ptr);  // keep the pair straight for the frees below
+      free(out_ptr);
       // restart from the initial field
       gpuCheck(gpuMemcpy(bStorage_dev.dat.get(), bStorage.dat.get(), bStorage.step * bStorage.chunks * sizeof(bElem),
                          gpuMemcpyHostToDevice));
     }
+    free(in_ptr);
 
     // warm-up, then the timed loop (stencils/fake.h time_mpi: barrier, cnt iterations)
-    for (int w = 0; w < 3; ++w) brick_func(false);
+    for (int w = 0; w < 3; ++w) brick_func();
     gpuCheck(bricks_sync(rk.ctx, -1));
     rk.barrier->wait();
     calltime_l = 0;
     gpuCheck(bricks_timer_start(rk.ctx, BRICKS_STREAM_COMPUTE, 0));
-    for (int i = 0; i < iters; ++i) brick_func(false);
+    for (int i = 0; i < iters; ++i) brick_func();
+    gpuCheck(bricks_stream_wait(rk.ctx, BRICKS_STREAM_COMPUTE, BRICKS_STREAM_COMM));  // an early exchange is part of the run
     gpuCheck(bricks_timer_stop(rk.ctx, BRICKS_STREAM_COMPUTE, 0));
     float ms = 0;
     gpuCheck(bricks_timer_elapsed_ms(rk.ctx, 0, &ms));
     gpuCheck(bricks_sync(rk.ctx, -1));
+    gpuCheck(bricks_step_reset(step));
     rk.barrier->wait();
     const double call_step = calltime_l / iters;
-    // second pass: time the sweeps of each step on their own (the reference synchronises per step too)
+    // second pass: the sweeps of a step on their own (no exchange in flight): calc
     double calc_s = 0;
     const int cal_iters = std::min(iters, 20);
-    for (int i = 0; i < cal_iters; ++i) {
-      brick_func(true);
+    {
+      const double *ia[1] = {fa[0]}, *ib[1] = {fb[0]};
+      bricks_plan *probe = nullptr;
+      const bool split = overlap && bricks_step_plan(step, BRICKS_PLAN_INNER, &probe) == 0;
+      gpuCheck(bricks_timer_start(rk.ctx, BRICKS_STREAM_COMPUTE, 1));
+      for (int i = 0; i < cal_iters; ++i)
+        for (int it = 0; it < st_iter; ++it) {
+          const double *const *src = it % 2 ? ib : ia;
+          double *const *dst = it % 2 ? fa : fb;
+          auto sw = [&](int plan) {
+            gpuCheck(bricks_step_sweep(step, plan, which, 1, src, dst, nullptr, BRICKS_STREAM_COMPUTE));
+          };
+          if (it == 0 && split) {
+            sw(BRICKS_PLAN_INNER);
+            sw(BRICKS_PLAN_SHELL);
+          } else if (it == st_iter - 1) {
+            sw(BRICKS_PLAN_OWNED);
+          } else {
+            sw(BRICKS_PLAN_FULL);
+          }
+        }
+      gpuCheck(bricks_timer_stop(rk.ctx, BRICKS_STREAM_COMPUTE, 1));
       float cms = 0;
       gpuCheck(bricks_timer_elapsed_ms(rk.ctx, 1, &cms));
-      calc_s += cms * 1e-3;
+      calc_s = cms * 1e-3;
     }
     const long cnt = (long)iters * st_iter;
     const double total_l = ms * 1e-3 / cnt, calc_l = calc_s / ((double)cal_iters * st_iter);
@@ -310,8 +303,12 @@ int main(int argc, char **argv) {
         ++failures;
       }
       rk.barrier->wait();
-      if (rk.rank == 0) std::cout << "max relative error vs naive kernel " << rk.stats(7).max << std::endl;
+      if (rk.rank == 0)
+        std::cout << (failures ? "result mismatch" : "result match") << ": max relative error vs the host array twin "
+                  << rk.stats(7).max << std::endl;
     }
+    gpuCheck(bricks_sync(rk.ctx, -1));
+    bricks_step_destroy(step);
   });
   return rc ? rc : (failures ? 1 : 0);
 }

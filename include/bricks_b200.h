@@ -214,6 +214,16 @@ int bricks_step_exchange(bricks_step *step, double *field0);
 /* one sweep over one of the step's plans */
 int bricks_step_sweep(bricks_step *step, int which, int stencil_id, int nfields, const double *const *in,
                       double *const *out, const double *coeff_host, int stream);
+/* Timeline of a step, for profiles: with tracing on, bricks_step_run puts a CUDA event pair around every
+ * operation it enqueues (replaces the per-phase cudaEvent / MPI_Wtime pairs of weak/main.cu:251-286).
+ * bricks_step_trace_read synchronises the device and returns, for the LAST traced step, one record per
+ * operation: code = BRICKS_TRACE_SWEEP + 10 * sweep + plan, BRICKS_TRACE_COPY + op or
+ * BRICKS_TRACE_EXCHANGE + op (op = index in the communication program), and its start / end in ms
+ * relative to the earliest start.  An event on a stream completes when the work before it has, so
+ * a record's span includes time its stream spent waiting for the other one. */
+enum { BRICKS_TRACE_SWEEP = 1000, BRICKS_TRACE_COPY = 2000, BRICKS_TRACE_EXCHANGE = 3000 };
+int bricks_step_trace(bricks_step *step, int enable);
+int bricks_step_trace_read(bricks_step *step, int cap, int *n, int *codes, float *start_ms, float *end_ms);
 /* forget an exchange started early (the caller rewrote the field) */
 int bricks_step_reset(bricks_step *step);
 

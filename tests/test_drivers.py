@@ -66,14 +66,19 @@ def test_weak_driver_validates(drivers, which):
     for key in ("Bri: ", "calc ", "move ", "call ", "wait ", "  | MPI size (MB): ", "  | MPI speed (GB/s): "):
         assert key in out, out
     assert _perf(out) > 0 and "mismatch" not in out
+    # -v compares with the ARRAY twin on the host (weak/main.cu:143-214, 321-323), not with another kernel
+    m = re.search(r"result match: max relative error vs the host array twin ([0-9.eE+-]+)", out)
+    assert m and float(m.group(1)) <= 1e-12, out
 
 
 @pytest.mark.gpu
-def test_weak_driver_validates_with_the_shift_exchange(drivers):
-    """-m: MultiStageExchangeView; the validation twin exchanges directly, so the two must agree"""
-    rc, out = _run(os.path.join(drivers, "weak"), "-s", "64,48,32", "-I", "3", "-S", "13", "-v", "-m")
+@pytest.mark.parametrize("flag", ("-m", "-p", "-n"))
+def test_weak_driver_validates_with_the_other_exchanges(drivers, flag):
+    """-m: MultiStageExchangeView, -p: one packed message per peer, -n: the serial schedule; the host
+    array twin exchanges periodically on its own, so every form must agree with it"""
+    rc, out = _run(os.path.join(drivers, "weak"), "-s", "64,48,32", "-I", "3", "-S", "13", "-v", flag)
     assert rc == 0, out
-    assert _perf(out) > 0 and "mismatch" not in out
+    assert _perf(out) > 0 and "mismatch" not in out and "result match" in out
 
 
 @pytest.mark.gpu
@@ -84,6 +89,8 @@ def test_strong_driver_validates(drivers, which):
     for key in ("Bri: ", "calc : ", "pack : ", "call : ", "wait : ", "move : ", "part "):
         assert key in out, out
     assert _perf(out) > 0 and "Validated" in out and "mismatch" not in out
+    m = re.search(r"Validated, max relative error vs the global periodic array ([0-9.eE+-]+)", out)
+    assert m and float(m.group(1)) <= 1e-12, out
 
 
 @pytest.mark.gpu
@@ -97,6 +104,10 @@ def test_drivers_multi_gpu_validate(drivers, built, ngpus):
     rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "125", "-v")
     assert rc == 0 and "mismatch" not in out, out
     rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "7", "-v", "-m")
+    assert rc == 0 and "mismatch" not in out, out
+    rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "13", "-v", "-p")
+    assert rc == 0 and "mismatch" not in out, out
+    rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "25", "-v", "-E")
     assert rc == 0 and "mismatch" not in out, out
     rc, out = _run(os.path.join(drivers, "strong"), "-G", str(ngpus), "-d", "128", "-s", "32", "-I", "3", "-v")
     assert rc == 0 and "Validated" in out, out

@@ -320,3 +320,21 @@ def test_early_exchange_schedule_is_bitwise_the_plain_schedule(ctx, built, which
     for r in res[1:]:
         assert np.array_equal(res[0][:n].view(np.uint64), r[:n].view(np.uint64))
     sub.close()
+
+
+def test_step_trace_gives_one_record_per_operation(ctx, built):
+    """bricks_step_trace: the timeline of a step (the per-phase timers of weak/main.cu:251-286):
+    a self exchange, the split first sweep, the middle sweeps and the owned-bricks last sweep"""
+    from bricklib_b200 import weak
+    sub = weak.WeakSubdomain(ctx, (64, 64, 64), 125)
+    sub.upload(sub.host_field())
+    sub.step_obj.trace(True)
+    sub.step(overlap=True)
+    tl = sub.step_obj.trace_read()
+    sub.step_obj.trace(False)
+    names = [n for n, _, _ in tl]
+    assert names == ["comm[0] exchange", "sweep 1 inner", "sweep 1 shell", "sweep 2 full", "sweep 3 full", "sweep 4 owned"]
+    assert all(0.0 <= a <= b for _, a, b in tl) and min(a for _, a, _ in tl) == 0.0
+    sub.step(overlap=True)  # untraced steps leave the last timeline alone
+    assert [n for n, _, _ in sub.step_obj.trace_read()] == names
+    sub.close()
