@@ -62,6 +62,7 @@ _SIGS = {
     "bricks_links_upload": (C.c_int, [_vp, _vp, C.c_int, _vpp]),
     "bricks_copy_regions": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
     "bricks_links_free": (C.c_int, [_vp, _vp]),
+    "bricks_copy_regions_static": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
     "bricks_copy_array": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, C.c_int]),
     "bricks_array_stencil7": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]),
     "bricks_comm_unique_id": (C.c_int, [_vp]),
@@ -444,6 +445,16 @@ class Step(object):
         if self._h:
             lib().bricks_step_destroy(self._h)
             self._h = C.c_void_p()
+
+
+COPY_STATIC_MAX_LINKS = 2048  # BRICKS_COPY_STATIC_MAX_LINKS
+
+
+def copy_regions_static(ctx, links, stream=STREAM_COMPUTE):
+    """bricks_copy_regions_static: the same copies without any allocation (the table is staged in a
+    static device array of the library).  links: list of (src_dev, dst_dev, nbytes)."""
+    arr = (RegionLink * max(len(links), 1))(*[RegionLink(s, d, n) for s, d, n in links])
+    check(lib().bricks_copy_regions_static(ctx._h, arr, len(links), stream))
 
 
 def copy_regions(ctx, links, stream=STREAM_COMPUTE):

@@ -7,6 +7,8 @@
 //                        ncclSend/ncclRecv straight from/to brick storage (regions are contiguous
 //                        by construction of the layout, so nothing is packed); regions whose
 //                        peer is this rank become on-device copies.
+#include <alloca.h>
+
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -49,6 +51,32 @@ __global__ void __launch_bounds__(kCopyThreads) copy_regions_kernel(const bricks
     for (int u = 0; u < 4; ++u)
       if (i + u * kCopyThreads < n16) __stcs(d4 + i + u * kCopyThreads, v[u]);
   }
+}
+
+/* Scratch of bricks_copy_regions_static: the link table + first-chunk table of ONE call, in device
+ * memory that exists from library load to process exit on every GPU that loads the library
+ * (kStaticMaxLinks * 28 bytes = 56 KiB).  In host code the name below is only a stand-in for the
+ * symbol: the device address comes from cudaGetSymbolAddress, once per device (static_table()). */
+constexpr int kStaticMaxLinks = BRICKS_COPY_STATIC_MAX_LINKS;
+struct StaticLinkTable {
+  bricks_region_link links[kStaticMaxLinks];
+  unsigned chunk_first[kStaticMaxLinks];
+};
+static __device__ __align__(256) StaticLinkTable g_static_links;
+
+/* device address of g_static_links on the CURRENT device, looked up once per device */
+int static_table(int device, StaticLinkTable **out) {
+  static std::mutex m;
+  static StaticLinkTable *addr[64] = {nullptr};
+  BRK_ARG(device >= 0 && device < 64);
+  std::lock_guard<std::mutex> lock(m);
+  if (!addr[device]) {
+    void *p = nullptr;
+    BRK_CUDA(cudaGetSymbolAddress(&p, g_static_links)); /* the caller made `device` current */
+    addr[device] = (StaticLinkTable *)p;
+  }
+  *out = addr[device];
+  return 0;
 }
 
 }  // namespace
@@ -144,6 +172,43 @@ int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, in
   BRK_ARG(meta_get(links_dev, &b) && b.n == n);
   BRK_CUDA(cudaSetDevice(ctx->device));
   return bricks::link_blob_run(ctx, b, nullptr, nullptr, ctx->streams[stream]);
+}
+
+int bricks_copy_regions_static(bricks_ctx *ctx, const bricks_region_link *links_host, int n, int stream) {
+  BRK_ARG(ctx && links_host && stream >= 0 && stream < bricks::kNumStreams);
+  if (n < 0 || n > kStaticMaxLinks) {
+    bricks::set_error("bricks_copy_regions_static: %d links, the static table holds at most %d "
+                      "(BRICKS_COPY_STATIC_MAX_LINKS); use bricks_links_upload + bricks_copy_regions", n, kStaticMaxLinks);
+    return -1;
+  }
+  if (n == 0) return 0;
+  /* the table of this call, built on the stack: no host allocation either */
+  StaticLinkTable *host = (StaticLinkTable *)alloca(sizeof(bricks_region_link) * n + sizeof(unsigned) * n);
+  bricks_region_link *hl = (bricks_region_link *)host;
+  unsigned *hf = (unsigned *)(hl + n);
+  unsigned long long tot = 0;
+  for (int i = 0; i < n; ++i) {
+    BRK_ARG((links_host[i].len & 15) == 0 && ((uintptr_t)links_host[i].from & 15) == 0 &&
+            ((uintptr_t)links_host[i].to & 15) == 0);
+    hl[i] = links_host[i];
+    hf[i] = (unsigned)tot;
+    tot += (links_host[i].len + kChunk - 1) / kChunk;
+  }
+  BRK_ARG(tot <= 0x7fffffffull);
+  if (tot == 0) return 0;
+  BRK_CUDA(cudaSetDevice(ctx->device));
+  StaticLinkTable *tab = nullptr;
+  if (int rc = static_table(ctx->device, &tab)) return rc;
+  cudaStream_t s = ctx->streams[stream];
+  /* stream-ordered behind earlier work of THIS stream (an earlier call's kernel included); the
+   * entries past n keep the last call's contents and are never read.  Pageable source: the call
+   * returns once the bytes are staged, so the stack table may die at return. */
+  BRK_CUDA(cudaMemcpyAsync(tab->links, hl, sizeof(bricks_region_link) * n, cudaMemcpyHostToDevice, s));
+  BRK_CUDA(cudaMemcpyAsync(tab->chunk_first, hf, sizeof(unsigned) * n, cudaMemcpyHostToDevice, s));
+  copy_regions_kernel<<<(unsigned)tot, kCopyThreads, 0, s>>>(tab->links, tab->chunk_first, n, nullptr, nullptr);
+  BRK_CUDA(cudaGetLastError());
+  ++bricks::g_launches;
+  return 0;
 }
 
 int bricks_comm_unique_id(void *id128) {

@@ -129,6 +129,18 @@ int bricks_links_upload(bricks_ctx *ctx, const bricks_region_link *links_host, i
 int bricks_copy_regions(bricks_ctx *ctx, const bricks_region_link *links_dev, int n, int stream);
 /* release a table made by bricks_links_upload (after the copies that use it have completed) */
 int bricks_links_free(bricks_ctx *ctx, bricks_region_link *links_dev);
+/* The same region copies for callers that may not allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * links_host (HOST memory, absolute device addresses in from / to) is staged into a table
+ * that lives in a file-scope `static __device__` array of the library -- 56 KiB held by every GPU that
+ * loads the library until the process exits -- and the copy kernel of bricks_copy_regions runs over it:
+ * no cudaMalloc / cudaFree / allocating routine on this path.  n > BRICKS_COPY_STATIC_MAX_LINKS is
+ * rejected with an error (-1; use bricks_links_upload + bricks_copy_regions for longer tables).  Every
+ * call on a device shares the one table: calls on the SAME stream are ordered, calls that overlap on
+ * the GPU (different streams, or host threads driving the same device) race on it.  The table keeps
+ * the last call's entries past n; they are never read.  Asynchronous on `stream`. */
+#define BRICKS_COPY_STATIC_MAX_LINKS 2048
+int bricks_copy_regions_static(bricks_ctx *ctx, const bricks_region_link *links_host, int n, int stream);
 
 /* ---- array <-> brick copies on the device: replaces copyToBrick<3> / copyFromBrick<3>
  * (include/bricksetup.h:172-221; cell range and strides of iter_grid, :139-160) for arrays that
