@@ -707,15 +707,38 @@ def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
     import ctypes as C
     from bricklib_b200 import capi
     n = sub.dec.nbricks * 512
-    ptrs = []
+    ptrs, node = [], C.c_int(-1)
     for _ in range(3):
         p = C.c_void_p()
-        capi.check(capi.lib().bricks_host_alloc(C.byref(p), n * 8))
+        if args.e2e_plain_alloc:  # pinned, wherever the pages land (for comparison)
+            capi.check(capi.lib().bricks_host_alloc(C.byref(p), n * 8))
+        else:  # pinned on the NUMA node of this rank's GPU
+            capi.check(capi.lib().bricks_host_alloc_local(ctx._h, C.byref(p), n * 8, C.byref(node)))
         ptrs.append(p)
     h_in, h_out0, h_out1 = (np.ctypeslib.as_array((C.c_double * n).from_address(p.value)) for p in ptrs)
     h_in[:] = field
     steps = max(2, min(args.steps, args.e2e_steps))
     overlap = not args.no_overlap
+    # the host link alone, all ranks at once: H2D, then D2H, then both directions together
+    nb_own = int(sub.dec.sep_pos[1]) * 512 * 8
+    alone = {}
+    for name, fn in (("h2d", lambda: ctx.h2d(sub.d_b, h_in, stream=capi.STREAM_H2D, nbytes=nb_own)),
+                     ("d2h", lambda: ctx.d2h(h_out0, sub.d_b, stream=capi.STREAM_D2H, nbytes=nb_own)),
+                     ("both", lambda: (ctx.h2d(sub.d_b, h_in, stream=capi.STREAM_H2D, nbytes=nb_own),
+                                       ctx.d2h(h_out1, sub.d_a, stream=capi.STREAM_D2H, nbytes=nb_own)))):
+        fn()
+        barrier()
+        U, D = capi.STREAM_H2D, capi.STREAM_D2H
+        ctx.stream_wait(U, D)
+        ctx.timer_start(4, U)          # CUDA events on the copy stream; D2H work is folded in below
+        ctx.stream_wait(D, U)
+        for _ in range(2):
+            fn()
+        ctx.stream_wait(U, D)
+        ctx.timer_stop(4, U)
+        dt = ctx.timer_ms(4) * 1e-3 / 2
+        barrier()
+        alone[name] = nb_own / max_over_ranks(dt) * 1e-9
     sub.host_steps(h_in, [h_out0, h_out1], 2, overlap)
     barrier()
     ctx.timer_start(2)
@@ -729,10 +752,16 @@ def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
     for p in ptrs:
         capi.check(capi.lib().bricks_host_free(p))
     per_dir = sub.host_step_bytes / (ms / steps * 1e-3) * 1e-9
+    link = {"h2d_alone_gbs": alone["h2d"], "d2h_alone_gbs": alone["d2h"], "both_directions_gbs_each": alone["both"],
+            "pcie_frac": per_dir / alone["both"], "numa_node_of_pinned_buffers": node.value,
+            "pinned_alloc": "bricks_host_alloc" if args.e2e_plain_alloc else "bricks_host_alloc_local",
+            "what": "GB/s per direction per GPU with every rank copying at once (max time over ranks); pcie_frac = the "
+                    "e2e step's rate per direction / the rate of both directions copying with nothing else running"}
     return {"value": pts_step / (ms / steps * 1e-3) * 1e-9, "unit": "GStencil/s",
             "h2d_bytes_per_step": sub.host_step_bytes, "d2h_bytes_per_step": sub.host_step_bytes,
             "ms_per_step": ms / steps, "steps": steps, "result_finite": ok,
             "host_link_gbs_per_direction_per_gpu": per_dir,
+            "host_link": link,
             "what": "per step and GPU: H2D of the input field (all owned bricks; ghost bricks are filled by the "
                     "exchange) from pinned host memory, exchange + sweeps, D2H of the result field (all owned bricks); "
                     "steps software-pipelined over two device buffer sets and two copy streams (upload n+1 and "
@@ -776,6 +805,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--e2e-plain-alloc", action="store_true",
+                    help="e2e: pinned host buffers from bricks_host_alloc (no NUMA placement), for comparison")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity block in front of the timed loop")
     ap.add_argument("--no-all-stencils", action="store_true", help="skip the kernel-only numbers for 7/13/25/125-point")
     ap.add_argument("--all-stencils", action="store_true", help="(the default now; kept for old command lines)")

@@ -42,6 +42,7 @@ _SIGS = {
     "bricks_free": (C.c_int, [_vp, _vp]),
     "bricks_memset": (C.c_int, [_vp, _vp, C.c_int, C.c_size_t]),
     "bricks_host_alloc": (C.c_int, [_vpp, C.c_size_t]),
+    "bricks_host_alloc_local": (C.c_int, [_vp, _vpp, C.c_size_t, C.POINTER(C.c_int)]),
     "bricks_host_free": (C.c_int, [_vp]),
     "bricks_h2d": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),
     "bricks_d2h": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int]),

@@ -1,6 +1,11 @@
 // Context, memory, copies, streams, timers of libbricks_b200.so.
 // Replaces the gpu* macro layer of the reference (include/brick-cuda.h:12-24,
 // include/brick-gpu.h:23-99, stencils/cudaarray.h:11-31).
+#include <sched.h>
+
+#include <cctype>
+#include <cstring>
+
 #include "common.cuh"
 
 namespace bricks {
@@ -117,6 +122,59 @@ int bricks_memset(bricks_ctx *c, void *dptr, int value, size_t bytes) {
 int bricks_host_alloc(void **hptr, size_t bytes) {
   BRK_ARG(hptr);
   BRK_CUDA(cudaMallocHost(hptr, bytes ? bytes : 16));
+  return 0;
+}
+
+/* CPUs of the NUMA node the device hangs off (sysfs), empty when the box does not say */
+static bool device_local_cpus(int device, cpu_set_t *set, int *node_out) {
+  char bus[32] = "";
+  if (cudaDeviceGetPCIBusId(bus, sizeof bus, device) != cudaSuccess) return false;
+  for (char *c = bus; *c; ++c) *c = (char)tolower(*c);
+  char path[160];
+  snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/numa_node", bus);
+  FILE *f = fopen(path, "r");
+  int node = -1;
+  if (f) {
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+  }
+  if (node < 0) return false;
+  snprintf(path, sizeof path, "/sys/devices/system/node/node%d/cpulist", node);
+  f = fopen(path, "r");
+  if (!f) return false;
+  char list[4096] = "";
+  const bool got = fgets(list, sizeof list, f) != nullptr;
+  fclose(f);
+  if (!got) return false;
+  CPU_ZERO(set);
+  int n = 0;
+  for (char *tok = strtok(list, ",\n"); tok; tok = strtok(nullptr, ",\n")) {
+    int a = 0, b = 0;
+    const int k = sscanf(tok, "%d-%d", &a, &b);
+    if (k == 1) b = a;
+    if (k < 1) continue;
+    for (int c = a; c <= b && c < CPU_SETSIZE; ++c) CPU_SET(c, set), ++n;
+  }
+  if (node_out) *node_out = node;
+  return n > 0;
+}
+
+int bricks_host_alloc_local(bricks_ctx *c, void **hptr, size_t bytes, int *numa_node) {
+  BRK_ARG(c && hptr);
+  if (numa_node) *numa_node = -1;
+  BRK_CUDA(cudaSetDevice(c->device));
+  /* first touch decides where pinned pages live: allocate and touch them from a CPU of the
+   * device's NUMA node, then give the calling thread its own affinity back */
+  cpu_set_t local, saved;
+  int node = -1;
+  const bool have = device_local_cpus(c->device, &local, &node) &&
+                    sched_getaffinity(0, sizeof saved, &saved) == 0 &&
+                    sched_setaffinity(0, sizeof local, &local) == 0;
+  const cudaError_t e = cudaMallocHost(hptr, bytes ? bytes : 16);
+  if (e == cudaSuccess) memset(*hptr, 0, bytes ? bytes : 16);
+  if (have) sched_setaffinity(0, sizeof saved, &saved);
+  BRK_CUDA(e);
+  if (numa_node && have) *numa_node = node;
   return 0;
 }
 

@@ -67,6 +67,12 @@ int bricks_malloc(bricks_ctx *ctx, void **dptr, size_t bytes);
 int bricks_free(bricks_ctx *ctx, void *dptr);
 int bricks_memset(bricks_ctx *ctx, void *dptr, int value, size_t bytes);
 int bricks_host_alloc(void **hptr, size_t bytes); /* pinned */
+/* pinned AND placed on the NUMA node the context's device hangs off (first touch from one of that
+ * node's CPUs; the calling thread keeps its affinity): with one rank per GPU and a launcher that pins
+ * nothing, host<->device copies of all ranks otherwise share whatever node the pages landed on.
+ * *numa_node (optional) = that node, or -1 when the box does not expose one (then == bricks_host_alloc).
+ * Replaces the malloc'ed staging buffers of weak/main.cu:251-275. */
+int bricks_host_alloc_local(bricks_ctx *ctx, void **hptr, size_t bytes, int *numa_node);
 int bricks_host_free(void *hptr);
 int bricks_h2d(bricks_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes, int stream);
 int bricks_d2h(bricks_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes, int stream);
