@@ -341,10 +341,20 @@ def init_ranks(args):
         dist.all_gather(outs, t)
         return [o.cpu().numpy() for o in outs]
 
+    def allgather_bytes(b):
+        """every rank's byte string (same length on all ranks), in rank order"""
+        if world == 1:
+            return [b]
+        t = torch.frombuffer(bytearray(b), dtype=torch.uint8).cuda()
+        outs = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(outs, t)
+        return [bytes(o.cpu().numpy().tobytes()) for o in outs]
+
+    gather.bytes = allgather_bytes
     return ctx, rank, world, local, dist, barrier, max_over_ranks, gather
 
 
-def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False):
+def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False, p2p=False):
     """Correctness evidence inside the run the driver times (module docstring).  Same code path as
     the timed loop -- WeakSubdomain over the C ABI, NCCL between the ranks -- on PARITY_DIMS per
     rank.  Checked on rank 0 against (1) the oracle's restatement of BrickDecomp::exchange
@@ -354,7 +364,7 @@ def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False):
     dims = PARITY_DIMS
     procdims = capi.cart_dims(world)
     out = {"nranks": world, "subdomain_per_rank": list(dims), "process_grid": list(procdims), "tolerance": REL_TOL,
-           "schedule": {"overlap": overlap, "early_exchange": early, "exchange": kind, "unsplit": unsplit},
+           "schedule": {"overlap": overlap, "early_exchange": early, "exchange": kind, "unsplit": unsplit, "p2p": p2p},
            "checker": "oracle/oracle.py exchange() (bit-exact) and the global periodic array through the oracle's "
                       "array stencil"}
     ok = True
@@ -365,6 +375,8 @@ def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False):
 
     # (1) one bare exchange of a random storage
     sub = weak.WeakSubdomain(ctx, dims, 7, rank=rank, procdims=procdims, exchange=kind)
+    if p2p:
+        sub.enable_p2p(gather.bytes)
     nb = sub.dec.nbricks
     f = capi.uniform(nb * 512, seed=9000 + rank)
     sub.upload(f)
@@ -372,6 +384,7 @@ def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False):
     ctx.sync()
     got = gather(sub.download())
     fields = gather(f)
+    gather(np.zeros(1))  # every rank is done with its peers' memory before anybody unmaps it
     sub.close()
     if rank == 0:
         exp = O.exchange([x.copy() for x in fields], odec, procdims)
@@ -394,6 +407,8 @@ def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False):
     nsteps = 2
     for which in (7, 125):
         sub = weak.WeakSubdomain(ctx, dims, which, rank=rank, procdims=procdims, exchange=kind)
+        if p2p:
+            sub.enable_p2p(gather.bytes)
         f0 = sub.host_field()
         sub.upload(f0)
         for _ in range(nsteps):
@@ -401,6 +416,7 @@ def parity_block(ctx, rank, world, gather, overlap, early, kind, unsplit=False):
         ctx.sync()
         res = gather(sub.download())
         f0s = gather(f0)
+        gather(np.zeros(1))
         sub.close()
         if rank == 0:
             def interior_of(field):
@@ -444,9 +460,10 @@ def run_gpu(args, which):
     overlap = not args.no_overlap
     early = (not args.no_early) and world > 1 and overlap
 
+    p2p = bool(args.p2p) and world > 1 and args.exchange != "packed"
     parity = None
     if not args.no_parity:
-        parity = parity_block(ctx, rank, world, gather, overlap, early, args.exchange, args.unsplit)
+        parity = parity_block(ctx, rank, world, gather, overlap, early, args.exchange, args.unsplit, p2p)
         bad = 0.0 if (rank != 0 or parity["ok"]) else 1.0
         if max_over_ranks(bad) > 0:
             if rank == 0:
@@ -454,6 +471,8 @@ def run_gpu(args, which):
             return 3
 
     sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims, exchange=args.exchange)
+    if p2p:
+        sub.enable_p2p(gather.bytes)
     field = sub.host_field()
     sub.upload(field)
 
@@ -511,6 +530,7 @@ def run_gpu(args, which):
     clocks = sampler.summary() if sampler else None
     exchange_bytes = sub.exchange_bytes
     exchange_kind = sub.exchange_kind
+    barrier()  # nobody unmaps a storage its peers may still be copying into
     sub.close()
 
     strong = None
@@ -527,7 +547,7 @@ def run_gpu(args, which):
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": make_config(which, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": roofline, "parity": parity,
-                "overlap": overlap, "early_exchange": early, "early_unsplit": bool(args.unsplit and early),
+                "overlap": overlap, "early_exchange": early, "early_unsplit": bool(args.unsplit and early), "p2p_copy_engine_exchange": p2p,
                 "nccl_max_ctas": int(os.environ.get("BRICKS_NCCL_MAX_CTAS", "0")),
                 "exchange_bytes_per_step_per_gpu": exchange_bytes, "exchange": exchange_kind}
         if kernels is not None:
@@ -795,11 +815,15 @@ def main():
                     help="weak workloads: the SHIFT exchange (3 stages, 6 messages) instead of one message per region")
     ap.add_argument("--exchange", default=None, choices=["regions", "packed", "shift"],
                     help="weak workloads: one send/recv pair per region (default), one packed message per peer, or SHIFT")
-    ap.add_argument("--unsplit", action="store_true", default=True,
+    ap.add_argument("--unsplit", action="store_true", default=False,
                     help="with the early exchange: run a first sweep whose exchange is already in flight as ONE launch "
-                         "(default: measured faster at 2 GPUs, profiles/r03_scaling/)")
+                         "(+1.5 %% at 2 GPUs, -3.5 %% at 8 where the exchange outlasts the sweep it hides behind: "
+                         "profiles/r03_scaling/)")
     ap.add_argument("--no-unsplit", dest="unsplit", action="store_false",
-                    help="keep the inner + shell split of every first sweep")
+                    help="keep the inner + shell split of every first sweep (default)")
+    ap.add_argument("--p2p", action="store_true", default=False,
+                    help="N > 1: the copy-engine exchange (cudaMemcpyAsync into peer-mapped ghost bricks) instead of NCCL")
+    ap.add_argument("--no-p2p", dest="p2p", action="store_false")
     ap.add_argument("--trace", default=None, metavar="FILE",
                     help="write every rank's timeline of one traced step (bricks_step_trace) to FILE.rank<r>.json")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -86,6 +86,8 @@ _SIGS = {
     "bricks_step_exchange": (C.c_int, [_vp, _vp]),
     "bricks_step_sweep": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_int]),
     "bricks_step_reset": (C.c_int, [_vp]),
+    "bricks_step_p2p_export": (C.c_int, [_vp, _vp, C.c_int, _vp]),
+    "bricks_step_p2p_connect": (C.c_int, [_vp, C.c_int, _vp]),
     "bricks_step_trace": (C.c_int, [_vp, C.c_int]),
     "bricks_step_trace_read": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int), _vp, _vp, _vp]),
     # include/bricks_b200_probe.h
@@ -417,6 +419,18 @@ class Step(object):
 
     def reset(self):
         check(lib().bricks_step_reset(self._h))
+
+    def p2p_export(self, field0, rank):
+        """256-byte descriptor of the storage this rank exchanges (bricks_step_p2p_export)"""
+        buf = C.create_string_buffer(256)
+        check(lib().bricks_step_p2p_export(self._h, C.c_void_p(field0), rank, buf))
+        return buf.raw
+
+    def p2p_connect(self, descs):
+        """descs: the descriptors of ALL ranks, in rank order (bricks_step_p2p_connect)"""
+        blob = b"".join(descs)
+        assert len(blob) == 256 * len(descs)
+        check(lib().bricks_step_p2p_connect(self._h, len(descs), C.create_string_buffer(blob, len(blob))))
 
     def trace(self, enable=True):
         check(lib().bricks_step_trace(self._h, 1 if enable else 0))

@@ -147,8 +147,27 @@ int link_blob_run(bricks_ctx *ctx, const LinkBlob &b, char *src_base, char *dst_
 void link_blob_free(LinkBlob *b);
 }  // namespace bricks
 
+namespace bricks {
+/* Peer-to-peer state of a step's exchanges (exchange.cu, "copy-engine exchange"): the peers' field
+ * storages and flag words mapped into this process (CUDA IPC between processes, direct pointers
+ * between threads of one process), and the sequence number that orders the exchanges of all ranks. */
+constexpr int kP2PMaxRanks = 64;
+struct P2PState {
+  double *field = nullptr;        /* the local storage the mappings belong to */
+  unsigned *flags = nullptr;      /* local: ready[kP2PMaxRanks] then done[kP2PMaxRanks], written by the peers */
+  char *peer_field[kP2PMaxRanks] = {};
+  unsigned *peer_flags[kP2PMaxRanks] = {};
+  bool mapped_ipc[kP2PMaxRanks] = {}; /* opened with cudaIpcOpenMemHandle (to close) */
+  void *ipc_field[kP2PMaxRanks] = {}, *ipc_flags[kP2PMaxRanks] = {};
+  unsigned seq = 0;
+  int rank = 0, nranks = 1;
+  bool connected = false;
+};
+}  // namespace bricks
+
 struct bricks_exchange {
   bricks_ctx *ctx = nullptr;
+  bricks::P2PState *p2p = nullptr; /* borrowed from the step that owns this exchange, or null */
   int rank = 0;
   struct Msg {
     size_t recv_off, send_off, recv_bytes, send_bytes;

@@ -308,6 +308,80 @@ int bricks_exchange_destroy(bricks_exchange *ex) {
   return 0;
 }
 
+}  // extern "C"
+
+namespace {
+
+typedef CUresult (*StreamValueFn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+StreamValueFn lookup_stream_op(const char *name) {
+  void *p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+    return (StreamValueFn)p;
+  return nullptr;
+}
+
+/* The copy-engine exchange.  NCCL's send/recv kernel needs most of an SM per CTA and runs beside a
+ * sweep that keeps every SM full of one-warp CTAs: measured, an exchange of 104 MB that NVLink moves
+ * in ~0.15 ms takes 0.6 ms (2 GPUs) to 0.8 ms (8 GPUs) next to a sweep (profiles/r03_scaling/).
+ * Here every region is ONE cudaMemcpyAsync from this rank's skin straight into the peer's ghost
+ * bricks (peer-mapped memory, NVLink, copy engines: no SM is involved), ordered by two flag words
+ * per peer pair that carry the exchange's sequence number (stream memory operations):
+ *   receiver: ready[me] := seq in every sender's memory   -- my ghost bricks may be overwritten
+ *   sender  : wait ready[peer] >= seq; copy regions; done[me] := seq in the receiver's memory
+ *   receiver: wait done[peer] >= seq for every peer
+ * Every rank writes all its ready flags before its first wait, so no cycle of waits can form.
+ * All ranks hold the same region tables (equal subdomains), so region i lands at the receiver's
+ * recv_off[i] = this rank's recv_off[i]. */
+int exchange_run_p2p(bricks_exchange *ex, cudaStream_t s) {
+  static const StreamValueFn wait_fn = lookup_stream_op("cuStreamWaitValue32");
+  static const StreamValueFn write_fn = lookup_stream_op("cuStreamWriteValue32");
+  if (!wait_fn || !write_fn) {
+    bricks::set_error("stream memory operations are not available from this driver");
+    return -6;
+  }
+  bricks::P2PState *p = ex->p2p;
+  const unsigned seq = ++p->seq;
+  const int me = ex->rank;
+  bool recv_from[bricks::kP2PMaxRanks] = {}, send_to[bricks::kP2PMaxRanks] = {};
+  for (auto &m : ex->msgs) {
+    if (m.recv_peer != me && m.recv_bytes) recv_from[m.recv_peer] = true;
+    if (m.send_peer != me && m.send_bytes) send_to[m.send_peer] = true;
+  }
+  auto cu = [](CUresult r, const char *what) {
+    if (r == CUDA_SUCCESS) return 0;
+    bricks::set_error("%s failed with CUresult %d", what, (int)r);
+    return 3000 + (int)r;
+  };
+  /* 1. my ghost regions are free: tell every rank that sends to me */
+  for (int r = 0; r < p->nranks; ++r)
+    if (recv_from[r])
+      if (int rc = cu(write_fn(s, (CUdeviceptr)(p->peer_flags[r] + me), seq, CU_STREAM_WRITE_VALUE_DEFAULT), "cuStreamWriteValue32"))
+        return rc;
+  /* 2. per receiver: wait until it is ready, push my skin regions into its ghost bricks, say so */
+  char *base = (char *)p->field;
+  for (int r = 0; r < p->nranks; ++r) {
+    if (!send_to[r]) continue;
+    if (int rc = cu(wait_fn(s, (CUdeviceptr)(p->flags + r), seq, CU_STREAM_WAIT_VALUE_GEQ), "cuStreamWaitValue32")) return rc;
+    for (auto &m : ex->msgs)
+      if (m.send_peer == r && m.send_bytes)
+        BRK_CUDA(cudaMemcpyAsync(p->peer_field[r] + m.recv_off, base + m.send_off, m.send_bytes, cudaMemcpyDeviceToDevice, s));
+    if (int rc = cu(write_fn(s, (CUdeviceptr)(p->peer_flags[r] + bricks::kP2PMaxRanks + me), seq, CU_STREAM_WRITE_VALUE_DEFAULT),
+                    "cuStreamWriteValue32"))
+      return rc;
+  }
+  /* 3. everything bound for me has landed */
+  for (int r = 0; r < p->nranks; ++r)
+    if (recv_from[r])
+      if (int rc = cu(wait_fn(s, (CUdeviceptr)(p->flags + bricks::kP2PMaxRanks + r), seq, CU_STREAM_WAIT_VALUE_GEQ), "cuStreamWaitValue32"))
+        return rc;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
 /* Stream order is the only ordering between two runs of the same plan (and between a run and the
  * sweeps that read what it delivered): callers enqueue bricks_stream_wait between the streams. */
 int bricks_exchange_run(bricks_exchange *ex, double *storage, int stream) {
@@ -318,7 +392,10 @@ int bricks_exchange_run(bricks_exchange *ex, double *storage, int stream) {
   char *base = (char *)storage;
   bool remote = false;
   for (auto &m : ex->msgs) remote = remote || m.recv_peer != ex->rank || m.send_peer != ex->rank;
-  if (remote) {
+  if (remote && ex->p2p && ex->p2p->connected && ex->p2p->field == storage) {
+    /* the peers' copies of THIS storage are mapped here: copy engines over NVLink, no NCCL kernel */
+    if (int rc = exchange_run_p2p(ex, s)) return rc;
+  } else if (remote) {
     if (!ctx->comm) {
       bricks::set_error("exchange has remote peers but bricks_comm_init was not called");
       return -4;

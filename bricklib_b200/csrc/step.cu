@@ -15,6 +15,10 @@
 // of region-copy tables and exchange plans so that the weak driver (exchange straight out of the
 // brick storage, or one packed message per peer), the SHIFT exchange (three stages) and the strong
 // driver (pack -> per-peer messages -> unpack -> intra-GPU links) share the code.
+#include <unistd.h>
+
+#include <cstring>
+
 #include "common.cuh"
 
 struct bricks_step {
@@ -40,6 +44,7 @@ struct bricks_step {
     int code; /* BRICKS_TRACE_* + detail */
     cudaEvent_t e0, e1;
   };
+  bricks::P2PState *p2p = nullptr; /* copy-engine exchange (bricks_step_p2p_*), owned */
   bool trace = false;
   std::vector<Rec> recs;
   std::vector<cudaEvent_t> pool; /* events are reused between traced steps */
@@ -47,6 +52,51 @@ struct bricks_step {
 };
 
 namespace {
+
+/* what a rank publishes about the storage it exchanges (bricks_step_p2p_export): 256 bytes */
+struct P2PDesc {
+  int pid, device, rank, reserved;
+  unsigned long long signature; /* of the region tables: every rank must hold the same ones */
+  void *field, *flags;
+  cudaIpcMemHandle_t hfield, hflags;
+  char pad[256 - 4 * 4 - 8 - 2 * 8 - 2 * sizeof(cudaIpcMemHandle_t)];
+};
+static_assert(sizeof(P2PDesc) == 256, "P2P descriptor is 256 bytes");
+
+/* the exchanges of the program that move bytes of the field itself with equal send / receive sizes */
+bool p2p_eligible(const bricks_step::Op &op) {
+  if (op.kind != 1 || op.base != BRICKS_BASE_FIELD) return false;
+  for (auto &m : op.ex->msgs)
+    if (m.recv_bytes != m.send_bytes) return false;
+  return true;
+}
+
+unsigned long long p2p_signature(const bricks_step *st) {
+  unsigned long long h = 0xCBF29CE484222325ull;
+  auto mix = [&](unsigned long long v) {
+    h ^= v;
+    h *= 0x100000001B3ull;
+  };
+  for (auto &op : st->comm)
+    if (p2p_eligible(op))
+      for (auto &m : op.ex->msgs) mix(m.recv_off), mix(m.send_off), mix(m.recv_bytes);
+  return h;
+}
+
+void p2p_release(bricks_step *st) {
+  bricks::P2PState *p = st->p2p;
+  if (!p) return;
+  for (auto &op : st->comm)
+    if (op.kind == 1) op.ex->p2p = nullptr;
+  for (int r = 0; r < bricks::kP2PMaxRanks; ++r)
+    if (p->mapped_ipc[r]) {
+      cudaIpcCloseMemHandle(p->ipc_field[r]);
+      cudaIpcCloseMemHandle(p->ipc_flags[r]);
+    }
+  cudaFree(p->flags);
+  delete p;
+  st->p2p = nullptr;
+}
 
 char *resolve_base(const bricks_step *st, int kind, double *field0) {
   switch (kind) {
@@ -176,6 +226,7 @@ int bricks_step_destroy(bricks_step *st) {
   if (!st) return 0;
   cudaSetDevice(st->ctx->device);
   for (int i = 4; i >= 0; --i) bricks_plan_destroy(st->plans[i]); /* derived plans before their parent */
+  p2p_release(st);
   for (cudaEvent_t e : st->pool) cudaEventDestroy(e);
   for (auto &op : st->comm) {
     if (op.kind == 0) bricks::link_blob_free(&op.links);
@@ -243,6 +294,84 @@ int bricks_step_sweep(bricks_step *st, int which, int stencil_id, int nfields, c
                       double *const *out, const double *coeff_host, int stream) {
   BRK_ARG(st && which >= 0 && which < 5 && st->plans[which]);
   return bricks_stencil(st->plans[which], stencil_id, nfields, in, out, 512, 512, coeff_host, stream);
+}
+
+int bricks_step_p2p_export(bricks_step *st, double *field0, int rank, void *desc256) {
+  BRK_ARG(st && field0 && desc256 && rank >= 0 && rank < bricks::kP2PMaxRanks);
+  BRK_CUDA(cudaSetDevice(st->ctx->device));
+  p2p_release(st);
+  bricks::P2PState *p = new bricks::P2PState;
+  st->p2p = p;
+  p->field = field0;
+  p->rank = rank;
+  const size_t fb = 2 * bricks::kP2PMaxRanks * sizeof(unsigned);
+  BRK_CUDA(cudaMalloc(&p->flags, fb));
+  BRK_CUDA(cudaMemset(p->flags, 0, fb));
+  BRK_CUDA(cudaDeviceSynchronize());
+  P2PDesc d;
+  memset(&d, 0, sizeof d);
+  d.pid = (int)getpid();
+  d.device = st->ctx->device;
+  d.rank = rank;
+  d.signature = p2p_signature(st);
+  d.field = field0;
+  d.flags = p->flags;
+  /* handles of the whole allocations: field0 must be the start of one (cudaMalloc / bricks_malloc) */
+  BRK_CUDA(cudaIpcGetMemHandle(&d.hfield, field0));
+  BRK_CUDA(cudaIpcGetMemHandle(&d.hflags, p->flags));
+  memcpy(desc256, &d, sizeof d);
+  return 0;
+}
+
+int bricks_step_p2p_connect(bricks_step *st, int nranks, const void *descs) {
+  BRK_ARG(st && st->p2p && descs && nranks >= 1 && nranks <= bricks::kP2PMaxRanks);
+  BRK_CUDA(cudaSetDevice(st->ctx->device));
+  bricks::P2PState *p = st->p2p;
+  p->nranks = nranks;
+  const P2PDesc *d = (const P2PDesc *)descs;
+  const unsigned long long sig = p2p_signature(st);
+  bool peer[bricks::kP2PMaxRanks] = {};
+  int eligible = 0;
+  for (auto &op : st->comm) {
+    if (!p2p_eligible(op)) continue;
+    ++eligible;
+    for (auto &m : op.ex->msgs) {
+      BRK_ARG(m.recv_peer >= 0 && m.recv_peer < nranks && m.send_peer >= 0 && m.send_peer < nranks);
+      if (m.recv_peer != p->rank) peer[m.recv_peer] = true;
+      if (m.send_peer != p->rank) peer[m.send_peer] = true;
+    }
+  }
+  if (!eligible) {
+    bricks::set_error("bricks_step_p2p_connect: the communication program has no exchange of the field itself "
+                      "(packed exchanges go through an arena and stay on NCCL)");
+    return -1;
+  }
+  for (int r = 0; r < nranks; ++r) {
+    if (!peer[r]) continue;
+    if (d[r].rank != r || d[r].signature != sig) {
+      bricks::set_error("bricks_step_p2p_connect: rank %d holds other region tables (unequal subdomains?)", r);
+      return -1;
+    }
+    if (d[r].pid == (int)getpid()) { /* a thread of this process: its pointers are valid here */
+      if (d[r].device != st->ctx->device) {
+        const cudaError_t e = cudaDeviceEnablePeerAccess(d[r].device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else BRK_CUDA(e);
+      }
+      p->peer_field[r] = (char *)d[r].field;
+      p->peer_flags[r] = (unsigned *)d[r].flags;
+    } else {
+      BRK_CUDA(cudaIpcOpenMemHandle(&p->ipc_field[r], d[r].hfield, cudaIpcMemLazyEnablePeerAccess));
+      BRK_CUDA(cudaIpcOpenMemHandle(&p->ipc_flags[r], d[r].hflags, cudaIpcMemLazyEnablePeerAccess));
+      p->mapped_ipc[r] = true;
+      p->peer_field[r] = (char *)p->ipc_field[r];
+      p->peer_flags[r] = (unsigned *)p->ipc_flags[r];
+    }
+  }
+  for (auto &op : st->comm)
+    if (p2p_eligible(op)) op.ex->p2p = p;
+  p->connected = true;
+  return 0;
 }
 
 int bricks_step_trace(bricks_step *st, int enable) {

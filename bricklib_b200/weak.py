@@ -109,6 +109,15 @@ class WeakSubdomain(object):
         self.launches_per_step = capi.launch_count() - n0
         return self.launches_per_step
 
+    def enable_p2p(self, allgather):
+        """Copy-engine exchange (bricks_step_p2p_*): the region messages of d_a become cudaMemcpyAsync
+        over NVLink into the peers' ghost bricks instead of NCCL send/recv.  `allgather(bytes)` returns
+        every rank's bytes in rank order (collective: call on all ranks).  Storages other than d_a
+        (the second pair of host_steps) keep the NCCL path."""
+        desc = self.step_obj.p2p_export(self.d_a, self.rank)
+        self.step_obj.p2p_connect(allgather(desc))
+        self.exchange_kind += ", copy engines into peer-mapped ghost bricks (no NCCL kernel)"
+
     def exchange_only(self, storage=None):
         """the communication program alone, on the communication stream"""
         self.step_obj.exchange(self.d_a if storage is None else storage)

@@ -232,6 +232,19 @@ int bricks_step_exchange(bricks_step *step, double *field0);
 /* one sweep over one of the step's plans */
 int bricks_step_sweep(bricks_step *step, int which, int stencil_id, int nfields, const double *const *in,
                       double *const *out, const double *coeff_host, int stream);
+/* Copy-engine exchange: the region messages of a step as cudaMemcpyAsync over NVLink straight into the
+ * peers' ghost bricks (peer-mapped memory; CUDA IPC between processes, direct pointers between threads of
+ * one process), ordered by flag words and stream memory operations -- no SM-resident send/recv kernel
+ * competing with the sweep the exchange hides behind (replaces the CUDA-aware MPI path of
+ * weak/main.cu:270-275 the way NVLink wants it).  Every rank exports a 256-byte descriptor of the storage it
+ * exchanges (field0 = the a[0] its steps run on, the start of a bricks_malloc allocation), the host layer
+ * gathers the descriptors of all ranks (MPI_Allgather's role; torch.distributed in bench.py, shared memory
+ * in the drivers) and hands them to connect.  Afterwards the exchanges of that storage take this path;
+ * exchanges of any other storage, and packed exchanges, stay on NCCL.  All ranks must hold the same region
+ * tables (equal subdomains; checked).  Call connect on every rank before the first step; destroy the step
+ * only after all ranks have synchronised. */
+int bricks_step_p2p_export(bricks_step *step, double *field0, int rank, void *desc256);
+int bricks_step_p2p_connect(bricks_step *step, int nranks, const void *descs /* nranks x 256 bytes, by rank */);
 /* Timeline of a step, for profiles: with tracing on, bricks_step_run puts a CUDA event pair around every
  * operation it enqueues (replaces the per-phase cudaEvent / MPI_Wtime pairs of weak/main.cu:251-286).
  * bricks_step_trace_read synchronises the device and returns, for the LAST traced step, one record per

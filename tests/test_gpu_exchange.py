@@ -338,3 +338,87 @@ def test_step_trace_gives_one_record_per_operation(ctx, built):
     sub.step(overlap=True)  # untraced steps leave the last timeline alone
     assert [n for n, _, _ in sub.step_obj.trace_read()] == names
     sub.close()
+
+
+def _thread_allgather(nranks):
+    """allgather for ranks that are threads of this process: a slot per rank and a barrier"""
+    slots, bar = [None] * nranks, threading.Barrier(nranks)
+
+    def make(r):
+        def allgather(b):
+            slots[r] = b
+            bar.wait()
+            out = list(slots)
+            bar.wait()
+            return out
+        return allgather
+    return make, bar
+
+
+@pytest.mark.parametrize("kind", ("regions", "shift"))
+@pytest.mark.parametrize("nranks", (2, 4, 8))
+def test_copy_engine_exchange_is_bit_exact_and_steps_like_the_global_array(built, oracle, nranks, kind):
+    """bricks_step_p2p_*: the region messages as cudaMemcpyAsync into the peers' ghost bricks, ordered
+    by flag words.  (1) one bare exchange leaves every rank's storage bit-identical to the oracle's
+    emulation of BrickDecomp::exchange; (2) three steps with the early schedule == periodic sweeps of
+    the assembled global array (weak/main.cu:321-323)."""
+    if _ndev(built) < nranks:
+        pytest.skip("needs %d GPUs" % nranks)
+    from bricklib_b200 import weak
+    dims, which, nsteps = (32, 32, 32), 13, 3
+    procdims = built.cart_dims(nranks)
+    nb = built.Decomp(dims, 8).nbricks
+    fields = [built.uniform(nb * 512, seed=900 + r) for r in range(nranks)]
+    make, bar = _thread_allgather(nranks)
+    f0 = [None] * nranks
+    stepped = [None] * nranks
+
+    def fn(r, c):
+        sub = weak.WeakSubdomain(c, dims, which, rank=r, procdims=procdims, exchange=kind)
+        sub.enable_p2p(make(r))
+        assert "copy engines" in sub.exchange_kind
+        sub.upload(fields[r])
+        bar.wait()
+        sub.exchange_only()
+        c.sync()
+        out = sub.download()
+        bar.wait()
+        f0[r] = sub.host_field()
+        sub.upload(f0[r])
+        bar.wait()
+        for _ in range(nsteps):
+            sub.step(overlap=True, early=True)
+        c.sync()
+        stepped[r] = sub.download()
+        bar.wait()  # nobody unmaps while a peer may still copy
+        sub.close()
+        return out
+
+    got = _ranks_in_threads(built, nranks, fn)
+    odec = oracle.Decomp(dims, 8)
+    exp = oracle.exchange([f.copy() for f in fields], odec, procdims)
+    for r in range(nranks):
+        assert np.array_equal(got[r].view(np.uint64), exp[r].view(np.uint64)), r
+
+    ext = [48, 48, 48]
+
+    def interior_of(field):
+        a = np.zeros((48, 48, 48))
+        oracle.copy_brick(False, ext, [0, 0, 0], [0, 0, 0], a, odec.grid, field)
+        return a[8:-8, 8:-8, 8:-8]
+
+    pk, pj, pi = procdims
+
+    def where(r):
+        c = built.cart_coords(r, procdims)
+        return [(-c[a]) % procdims[a] for a in range(3)]
+
+    glob = np.zeros((32 * pk, 32 * pj, 32 * pi))
+    for r in range(nranks):
+        ck, cj, ci = where(r)
+        glob[32 * ck:32 * ck + 32, 32 * cj:32 * cj + 32, 32 * ci:32 * ci + 32] = interior_of(f0[r])
+    want = _periodic_reference(oracle, which, glob, nsteps * built.ST_ITER[which])
+    for r in range(nranks):
+        ck, cj, ci = where(r)
+        e = want[32 * ck:32 * ck + 32, 32 * cj:32 * cj + 32, 32 * ci:32 * ci + 32]
+        assert relerr(interior_of(stepped[r]), e) <= REL_TOL, r

@@ -36,6 +36,12 @@ E2E=4 run regions_unsplit_plainalloc X=1 -- --unsplit --e2e-plain-alloc
 run regions_early X=1 -- --no-unsplit
 run packed_early_unsplit X=1 -- --exchange packed --unsplit
 run shift_early_unsplit X=1 -- --exchange shift --unsplit
+if [ "$QUICK" = ce ]; then  # NCCL P2P through the copy engines instead of an SM-resident kernel
+run regions_noearly X=1 -- --no-early
+run ce_regions_early NCCL_P2P_USE_CUDA_MEMCPY=1 --
+run ce_regions_noearly NCCL_P2P_USE_CUDA_MEMCPY=1 -- --no-early
+run ce_packed_noearly NCCL_P2P_USE_CUDA_MEMCPY=1 -- --exchange packed --no-early
+fi
 if [ -z "$QUICK" ]; then
 run regions_noearly X=1 -- --no-early
 run packed_early X=1 -- --exchange packed --no-unsplit
