@@ -458,9 +458,8 @@ def run_gpu(args, which):
     # start the next step's exchange behind the last sweep's skin bricks: pays off when the
     # exchange crosses NVLink (N > 1); on one GPU the plain schedule is faster (measured)
     overlap = not args.no_overlap
-    early = (not args.no_early) and world > 1 and overlap
-
     p2p = bool(args.p2p) and world > 1 and args.exchange != "packed"
+    early = world > 1 and overlap and not args.no_early and (args.early or not p2p)
     parity = None
     if not args.no_parity:
         parity = parity_block(ctx, rank, world, gather, overlap, early, args.exchange, args.unsplit, p2p)
@@ -821,9 +820,11 @@ def main():
                          "profiles/r03_scaling/)")
     ap.add_argument("--no-unsplit", dest="unsplit", action="store_false",
                     help="keep the inner + shell split of every first sweep (default)")
-    ap.add_argument("--p2p", action="store_true", default=False,
-                    help="N > 1: the copy-engine exchange (cudaMemcpyAsync into peer-mapped ghost bricks) instead of NCCL")
-    ap.add_argument("--no-p2p", dest="p2p", action="store_false")
+    ap.add_argument("--p2p", action="store_true", default=True,
+                    help="N > 1: the copy-engine exchange (cudaMemcpyAsync into peer-mapped ghost bricks; default)")
+    ap.add_argument("--no-p2p", dest="p2p", action="store_false", help="N > 1: NCCL send/recv instead")
+    ap.add_argument("--early", action="store_true", help="start each exchange behind the previous step's last sweep "
+                    "(default with NCCL, whose exchange outlasts the sweep it hides behind; off with the copy engines)")
     ap.add_argument("--trace", default=None, metavar="FILE",
                     help="write every rank's timeline of one traced step (bricks_step_trace) to FILE.rank<r>.json")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -162,6 +162,10 @@ struct P2PState {
   unsigned seq = 0;
   int rank = 0, nranks = 1;
   bool connected = false;
+  /* regions of at least ce_min bytes travel as one copy-engine copy each (no SM, ~10 us per copy
+   * whatever its size), smaller ones together in ONE store kernel of small CTAs into peer memory:
+   * 0 = every region by copy engine, SIZE_MAX = every region in the kernel */
+  size_t ce_min = 1u << 20;
 };
 }  // namespace bricks
 
@@ -175,6 +179,7 @@ struct bricks_exchange {
   };
   std::vector<Msg> msgs;
   bricks::LinkBlob self; /* self neighbours: offsets relative to the storage base */
+  bricks::LinkBlob push; /* P2P: this rank's skin regions -> the peers' ghost bricks, absolute addresses */
 };
 
 namespace bricks {

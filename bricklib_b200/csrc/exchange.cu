@@ -304,6 +304,7 @@ int bricks_exchange_destroy(bricks_exchange *ex) {
   if (!ex) return 0;
   cudaSetDevice(ex->ctx->device);
   bricks::link_blob_free(&ex->self);
+  bricks::link_blob_free(&ex->push);
   delete ex;
   return 0;
 }
@@ -321,15 +322,16 @@ StreamValueFn lookup_stream_op(const char *name) {
   return nullptr;
 }
 
-/* The copy-engine exchange.  NCCL's send/recv kernel needs most of an SM per CTA and runs beside a
+/* The peer-memory exchange.  NCCL's send/recv kernel needs most of an SM per CTA and runs beside a
  * sweep that keeps every SM full of one-warp CTAs: measured, an exchange of 104 MB that NVLink moves
  * in ~0.15 ms takes 0.6 ms (2 GPUs) to 0.8 ms (8 GPUs) next to a sweep (profiles/r03_scaling/).
- * Here every region is ONE cudaMemcpyAsync from this rank's skin straight into the peer's ghost
- * bricks (peer-mapped memory, NVLink, copy engines: no SM is involved), ordered by two flag words
- * per peer pair that carry the exchange's sequence number (stream memory operations):
+ * Here this rank's skin regions go straight into the peers' ghost bricks (peer-mapped memory over
+ * NVLink): each large region as ONE cudaMemcpyAsync on the copy engines, the small ones together in
+ * one store kernel, ordered by two flag words per peer pair that carry the exchange's sequence number
+ * (stream memory operations):
  *   receiver: ready[me] := seq in every sender's memory   -- my ghost bricks may be overwritten
- *   sender  : wait ready[peer] >= seq; copy regions; done[me] := seq in the receiver's memory
- *   receiver: wait done[peer] >= seq for every peer
+ *   sender  : wait ready[peer] >= seq for all receivers; move regions; done[me] := seq in each receiver's memory
+ *   receiver: wait done[peer] >= seq for every sender
  * Every rank writes all its ready flags before its first wait, so no cycle of waits can form.
  * All ranks hold the same region tables (equal subdomains), so region i lands at the receiver's
  * recv_off[i] = this rank's recv_off[i]. */
@@ -358,18 +360,25 @@ int exchange_run_p2p(bricks_exchange *ex, cudaStream_t s) {
     if (recv_from[r])
       if (int rc = cu(write_fn(s, (CUdeviceptr)(p->peer_flags[r] + me), seq, CU_STREAM_WRITE_VALUE_DEFAULT), "cuStreamWriteValue32"))
         return rc;
-  /* 2. per receiver: wait until it is ready, push my skin regions into its ghost bricks, say so */
+  /* 2. once every receiver is ready: the large regions by copy engine (no SM involved; a copy costs
+   * ~10 us whatever its size, so 42 copies to 7 peers took 0.7 ms, profiles/r03_scaling/p2p_n8), the
+   * many small ones in ONE kernel of 256-thread CTAs that stores into the peers' memory (they
+   * interleave with the sweep's one-warp CTAs; all bytes that way cost the sweep 12 %,
+   * profiles/r03_scaling/p2p_modes_n2) */
+  for (int r = 0; r < p->nranks; ++r)
+    if (send_to[r])
+      if (int rc = cu(wait_fn(s, (CUdeviceptr)(p->flags + r), seq, CU_STREAM_WAIT_VALUE_GEQ), "cuStreamWaitValue32")) return rc;
   char *base = (char *)p->field;
-  for (int r = 0; r < p->nranks; ++r) {
-    if (!send_to[r]) continue;
-    if (int rc = cu(wait_fn(s, (CUdeviceptr)(p->flags + r), seq, CU_STREAM_WAIT_VALUE_GEQ), "cuStreamWaitValue32")) return rc;
-    for (auto &m : ex->msgs)
-      if (m.send_peer == r && m.send_bytes)
-        BRK_CUDA(cudaMemcpyAsync(p->peer_field[r] + m.recv_off, base + m.send_off, m.send_bytes, cudaMemcpyDeviceToDevice, s));
-    if (int rc = cu(write_fn(s, (CUdeviceptr)(p->peer_flags[r] + bricks::kP2PMaxRanks + me), seq, CU_STREAM_WRITE_VALUE_DEFAULT),
-                    "cuStreamWriteValue32"))
-      return rc;
-  }
+  for (auto &m : ex->msgs)
+    if (m.send_peer != me && m.send_bytes && m.send_bytes >= p->ce_min)
+      BRK_CUDA(cudaMemcpyAsync(p->peer_field[m.send_peer] + m.recv_off, base + m.send_off, m.send_bytes,
+                               cudaMemcpyDeviceToDevice, s));
+  if (int rc = bricks::link_blob_run(ex->ctx, ex->push, nullptr, nullptr, s)) return rc;
+  for (int r = 0; r < p->nranks; ++r)
+    if (send_to[r])
+      if (int rc = cu(write_fn(s, (CUdeviceptr)(p->peer_flags[r] + bricks::kP2PMaxRanks + me), seq, CU_STREAM_WRITE_VALUE_DEFAULT),
+                      "cuStreamWriteValue32"))
+        return rc;
   /* 3. everything bound for me has landed */
   for (int r = 0; r < p->nranks; ++r)
     if (recv_from[r])

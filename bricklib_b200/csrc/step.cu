@@ -17,6 +17,7 @@
 // driver (pack -> per-peer messages -> unpack -> intra-GPU links) share the code.
 #include <unistd.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -87,7 +88,10 @@ void p2p_release(bricks_step *st) {
   bricks::P2PState *p = st->p2p;
   if (!p) return;
   for (auto &op : st->comm)
-    if (op.kind == 1) op.ex->p2p = nullptr;
+    if (op.kind == 1) {
+      op.ex->p2p = nullptr;
+      bricks::link_blob_free(&op.ex->push);
+    }
   for (int r = 0; r < bricks::kP2PMaxRanks; ++r)
     if (p->mapped_ipc[r]) {
       cudaIpcCloseMemHandle(p->ipc_field[r]);
@@ -368,8 +372,25 @@ int bricks_step_p2p_connect(bricks_step *st, int nranks, const void *descs) {
       p->peer_flags[r] = (unsigned *)p->ipc_flags[r];
     }
   }
-  for (auto &op : st->comm)
-    if (p2p_eligible(op)) op.ex->p2p = p;
+  /* experiments: BRICKS_P2P_MODE=ce (every region by copy engine) / push (every region in the store kernel) */
+  const char *mode = getenv("BRICKS_P2P_MODE");
+  if (mode && strcmp(mode, "ce") == 0) p->ce_min = 0;
+  if (mode && strcmp(mode, "push") == 0) p->ce_min = (size_t)-1;
+  for (auto &op : st->comm) {
+    if (!p2p_eligible(op)) continue;
+    std::vector<bricks_region_link> links;
+    for (auto &m : op.ex->msgs)
+      if (m.send_peer != p->rank && m.send_bytes && m.send_bytes < p->ce_min) {
+        bricks_region_link l;
+        l.from = (double *)((char *)p->field + m.send_off);
+        l.to = (double *)(p->peer_field[m.send_peer] + m.recv_off);
+        l.len = m.send_bytes;
+        links.push_back(l);
+      }
+    if (!links.empty())
+      if (int rc = bricks::link_blob_upload(st->ctx, links.data(), (int)links.size(), &op.ex->push)) return rc;
+    op.ex->p2p = p;
+  }
   p->connected = true;
   return 0;
 }
@@ -424,9 +445,17 @@ int bricks_step_run(bricks_step *st, int stencil_id, int st_iter, int nfields, d
   /* the exchange reads the skin written by the previous step's last sweep -- unless that step
    * already started it behind its own last sweep (EARLY) */
   const bool arrived_early = st->in_flight == a[0];
+  const bool split_first = overlap && !(arrived_early && (flags & BRICKS_STEP_EARLY_UNSPLIT));
+  /* The communication program is ordered behind the compute stream HERE (event recorded now), but
+   * where a sweep runs beside it that sweep is enqueued first: an exchange can be ~50 host calls
+   * (one copy per region), and the sweep it hides behind should not wait for them to be issued. */
+  bool comm_pending = false;
   if (!arrived_early) {
     if ((rc = bricks_stream_wait(ctx, X, C))) return rc;
-    if ((rc = run_comm(st, a[0]))) return rc;
+    if (split_first)
+      comm_pending = true;
+    else if ((rc = run_comm(st, a[0])))
+      return rc;
   }
   st->in_flight = nullptr;
   double *const *src = a, *const *dst = b;
@@ -438,8 +467,9 @@ int bricks_step_run(bricks_step *st, int stencil_id, int st_iter, int nfields, d
       });
     };
     if (it == 0) {
-      if (overlap && !(arrived_early && (flags & BRICKS_STEP_EARLY_UNSPLIT))) {
+      if (split_first) {
         if ((rc = sweep(1))) return rc;
+        if (comm_pending && (rc = run_comm(st, a[0]))) return rc;
         if ((rc = bricks_stream_wait(ctx, C, X))) return rc;
         if ((rc = sweep(2))) return rc;
       } else {
@@ -450,10 +480,10 @@ int bricks_step_run(bricks_step *st, int stencil_id, int st_iter, int nfields, d
       }
     } else if (last && early) {
       if ((rc = sweep(4))) return rc;
-      if ((rc = bricks_stream_wait(ctx, X, C))) return rc;
+      if ((rc = bricks_stream_wait(ctx, X, C))) return rc; /* behind the skin bricks, not behind the inner box */
+      if ((rc = sweep(1))) return rc;
       if ((rc = run_comm(st, dst[0]))) return rc; /* dst == a: the input of the next step */
       st->in_flight = dst[0];
-      if ((rc = sweep(1))) return rc;
     } else if (last) {
       if ((rc = sweep(3))) return rc;
     } else {

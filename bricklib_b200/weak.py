@@ -116,7 +116,7 @@ class WeakSubdomain(object):
         (the second pair of host_steps) keep the NCCL path."""
         desc = self.step_obj.p2p_export(self.d_a, self.rank)
         self.step_obj.p2p_connect(allgather(desc))
-        self.exchange_kind += ", copy engines into peer-mapped ghost bricks (no NCCL kernel)"
+        self.exchange_kind += ", stored straight into peer-mapped ghost bricks over NVLink (no NCCL kernel)"
 
     def exchange_only(self, storage=None):
         """the communication program alone, on the communication stream"""

@@ -44,7 +44,9 @@ const char *help =
     "  -E: no early exchange (default with more than one GPU: the next step's exchange starts behind the\n"
     "      last sweep's skin bricks)\n"
     "  -m: SHIFT exchange (three stages, six messages) instead of one message per region\n"
-    "  -p: one packed message per peer rank (pack kernel, send/recv, unpack kernel)\n"
+    "  -p: one packed message per peer rank (pack kernel, send/recv, unpack kernel; NCCL)\n"
+    "  -N: NCCL send/recv for the region messages instead of copy-engine copies into peer-mapped ghost bricks\n"
+    "  -e: early exchange also with the copy engines\n"
     "Example usage:\n"
     "  %s -G 8 -s 512,512,512 -S 125\n";
 
@@ -55,8 +57,9 @@ double now() { return std::chrono::duration<double>(std::chrono::steady_clock::n
 int main(int argc, char **argv) {
   std::vector<unsigned> dom(3, 64);
   int sel = 0, iters = 100, ngpus = 1, which = 7, c;
-  bool bin = false, validate = false, overlap = true, shift = false, packed = false, no_early = false;
-  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vnmpE")) != -1) {
+  bool bin = false, validate = false, overlap = true, shift = false, packed = false, no_early = false, nccl = false;
+  bool force_early = false;
+  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vnmpENe")) != -1) {
     switch (c) {
       case 'b': bin = true; break;
       case 'd': drv::parse_tuple(optarg, dom, 3); sel = sel ? -2 : 1; break;
@@ -69,6 +72,8 @@ int main(int argc, char **argv) {
       case 'm': shift = true; break;
       case 'p': packed = true; break;
       case 'E': no_early = true; break;
+      case 'e': force_early = true; break;
+      case 'N': nccl = true; break;
       default: printf("Unknown options %c\n", c);  // fall through
       case 'h': printf(help, argv[0], iters, argv[0]); sel = sel ? -2 : -1;
     }
@@ -162,10 +167,35 @@ int main(int argc, char **argv) {
     for (size_t i = 0; i < bDecomp.ghost.size(); ++i)
       tsize += (size_t)(bDecomp.ghost[i].len - bDecomp.ghost[i].first_pad - bDecomp.ghost[i].last_pad) * bStorage.step *
                sizeof(bElem);
-    const bool early = overlap && !no_early && nranks > 1;
+    // copy-engine exchange (bricks_step_p2p_*): needs equal subdomains on all ranks (-s, or -d that divides evenly)
+    bool p2p = nranks > 1 && !nccl && !packed;
+    if (p2p) {
+      static std::vector<unsigned char> descs;  // the ranks are threads: "allgather" = a shared table + barrier
+      static std::vector<unsigned> doms;
+      static std::mutex descs_mutex;
+      {
+        std::lock_guard<std::mutex> lk(descs_mutex);
+        descs.resize((size_t)nranks * 256);
+        doms.resize((size_t)nranks * 3);
+      }
+      rk.barrier->wait();
+      for (int a = 0; a < 3; ++a) doms[rk.rank * 3 + a] = dom_size[a];
+      gpuCheck(bricks_step_p2p_export(step, bStorage_dev.dat.get(), rk.rank, descs.data() + (size_t)rk.rank * 256));
+      rk.barrier->wait();
+      bool equal = true;
+      for (int r = 0; r < nranks; ++r)
+        for (int a = 0; a < 3; ++a) equal = equal && doms[r * 3 + a] == doms[a];
+      if (equal)
+        gpuCheck(bricks_step_p2p_connect(step, nranks, descs.data()));
+      else
+        p2p = false;  // unequal split: every rank takes the same decision, the exchange stays on NCCL
+      rk.barrier->wait();
+    }
+    const bool early = overlap && !no_early && nranks > 1 && (force_early || !p2p);
     const int flags = (overlap ? BRICKS_STEP_OVERLAP : 0) | (early ? BRICKS_STEP_EARLY : 0);
     if (rk.rank == 0)
-      std::cout << "exchange: " << exchange_text << (early ? ", started early behind the last sweep" : "") << std::endl;
+      std::cout << "exchange: " << exchange_text << (p2p ? ", stored straight into peer-mapped ghost bricks" : "")
+                << (early ? ", started early behind the last sweep" : "") << std::endl;
 
     double *fa[1] = {bStorage_dev.dat.get()}, *fb[1] = {bStorageOut_dev.dat.get()};
     double calltime_l = 0;
@@ -308,6 +338,7 @@ int main(int argc, char **argv) {
                   << rk.stats(7).max << std::endl;
     }
     gpuCheck(bricks_sync(rk.ctx, -1));
+    rk.barrier->wait();  // nobody unmaps a storage its peers may still be copying into
     bricks_step_destroy(step);
   });
   return rc ? rc : (failures ? 1 : 0);

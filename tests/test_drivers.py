@@ -109,5 +109,9 @@ def test_drivers_multi_gpu_validate(drivers, built, ngpus):
     assert rc == 0 and "mismatch" not in out, out
     rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "25", "-v", "-E")
     assert rc == 0 and "mismatch" not in out, out
+    rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "125", "-v", "-N")
+    assert rc == 0 and "mismatch" not in out and "peer-mapped" not in out, out
+    rc, out = _run(os.path.join(drivers, "weak"), "-G", str(ngpus), "-s", "64", "-I", "3", "-S", "7", "-v", "-e")
+    assert rc == 0 and "mismatch" not in out and "peer-mapped" in out, out
     rc, out = _run(os.path.join(drivers, "strong"), "-G", str(ngpus), "-d", "128", "-s", "32", "-I", "3", "-v")
     assert rc == 0 and "Validated" in out, out

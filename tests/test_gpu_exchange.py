@@ -376,7 +376,7 @@ def test_copy_engine_exchange_is_bit_exact_and_steps_like_the_global_array(built
     def fn(r, c):
         sub = weak.WeakSubdomain(c, dims, which, rank=r, procdims=procdims, exchange=kind)
         sub.enable_p2p(make(r))
-        assert "copy engines" in sub.exchange_kind
+        assert "peer-mapped ghost bricks" in sub.exchange_kind
         sub.upload(fields[r])
         bar.wait()
         sub.exchange_only()
