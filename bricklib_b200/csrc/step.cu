@@ -376,6 +376,8 @@ int bricks_step_p2p_connect(bricks_step *st, int nranks, const void *descs) {
   const char *mode = getenv("BRICKS_P2P_MODE");
   if (mode && strcmp(mode, "ce") == 0) p->ce_min = 0;
   if (mode && strcmp(mode, "push") == 0) p->ce_min = (size_t)-1;
+  if (const char *e = getenv("BRICKS_P2P_CE_MIN")) /* bytes; tests lower it so small subdomains take both paths */
+    if (atoll(e) > 0) p->ce_min = (size_t)atoll(e);
   for (auto &op : st->comm) {
     if (!p2p_eligible(op)) continue;
     std::vector<bricks_region_link> links;

@@ -355,15 +355,22 @@ def _thread_allgather(nranks):
     return make, bar
 
 
+@pytest.mark.parametrize("ce_min", (None, 16384))
 @pytest.mark.parametrize("kind", ("regions", "shift"))
 @pytest.mark.parametrize("nranks", (2, 4, 8))
-def test_copy_engine_exchange_is_bit_exact_and_steps_like_the_global_array(built, oracle, nranks, kind):
+def test_copy_engine_exchange_is_bit_exact_and_steps_like_the_global_array(built, oracle, monkeypatch, nranks, kind, ce_min):
     """bricks_step_p2p_*: the region messages as cudaMemcpyAsync into the peers' ghost bricks, ordered
     by flag words.  (1) one bare exchange leaves every rank's storage bit-identical to the oracle's
     emulation of BrickDecomp::exchange; (2) three steps with the early schedule == periodic sweeps of
     the assembled global array (weak/main.cu:321-323)."""
     if _ndev(built) < nranks:
         pytest.skip("needs %d GPUs" % nranks)
+    if ce_min is not None:
+        # regions of >= 16 KiB (the faces of a 32^3 subdomain) by copy engine, edges and corners in the
+        # store kernel: both halves of the production path (threshold 1 MiB) in one exchange
+        monkeypatch.setenv("BRICKS_P2P_CE_MIN", str(ce_min))
+    else:
+        monkeypatch.delenv("BRICKS_P2P_CE_MIN", raising=False)
     from bricklib_b200 import weak
     dims, which, nsteps = (32, 32, 32), 13, 3
     procdims = built.cart_dims(nranks)
