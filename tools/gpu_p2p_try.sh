@@ -10,7 +10,7 @@ if [ "$2" != notest ]; then
     echo "pytest $mode: $(tail -1 $O/pytest_$mode.log)"
   done
 fi
-for v in "hybrid_default X=1" "ce_default BRICKS_P2P_MODE=ce"; do
+for v in "hybrid_default X=1" ${ALSO_CE:+"ce_default BRICKS_P2P_MODE=ce"}; do
   set -- $v; name=$1; envv=$2; shift 2
   env $envv timeout 100 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29500 + RANDOM % 400)) \
     bench.py --gpus $N --steps 40 --warmup 3 --no-strong --no-all-stencils --no-cpu --e2e-steps 2 --trace $O/trace_$name "$@" \
