@@ -99,36 +99,76 @@ def dims_create(nnodes, ndims=3):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons during the timed region (B200_PROFILING.md), through NVML in
+    this process.  Forking nvidia-smi every few milliseconds instead stalls the driver calls of the
+    rank that does it (fork of a process with a CUDA context) and, on a periodic process grid, every
+    rank that waits for it; nvidia-smi stays as the fallback where NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = [0x8, 0x40, 0x20, 0x4]  # nvmlClocksEventReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
 
-    def __init__(self, index):
+    def __init__(self, index, pci_bus_id=None):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
+        self.nvml = self.handle = None
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            if pci_bus_id:
+                try:
+                    h = pynvml.nvmlDeviceGetHandleByPciBusId(pci_bus_id.encode() if isinstance(pci_bus_id, str) else pci_bus_id)
+                except Exception:  # noqa: BLE001
+                    h = None
+            if h is None:
+                h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self.nvml, self.handle = pynvml, h
+        except Exception:  # noqa: BLE001
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n, h = self.nvml, self.handle
+        mhz = float(n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM))
+        try:
+            mask = int(n.nvmlDeviceGetCurrentClocksEventReasons(h))
+        except Exception:  # noqa: BLE001 -- older binding name
+            mask = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+        return [mhz, self.max_mhz] + [bool(mask & b) for b in self.BITS]
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+        parts = [x.strip() for x in out.strip().split(",")]
+        if len(parts) < 6:
+            return None
+        return [float(parts[0]), float(parts[1])] + [p.lower().startswith("active") for p in parts[2:6]]
 
     def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                parts = [x.strip() for x in out.strip().split(",")]
-                if len(parts) >= 6:
-                    self.rows.append(parts)
+                row = self._sample_nvml() if self.nvml else self._sample_smi()
+                if row:
+                    self.rows.append(row)
             except Exception:  # noqa: BLE001
                 pass
-            time.sleep(0.02)
+            time.sleep(0.004 if self.nvml else 0.05)
+
+    def reset(self):
+        """forget what was sampled so far (the sampler is started before the timed region)"""
+        self.rows = []
 
     def summary(self):
         self.stop_flag = True
         self.join(timeout=6)
         if not self.rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        sm = sorted(float(r[0]) for r in self.rows)
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock samples"]}
+        sm = sorted(r[0] for r in self.rows)
+        reasons = [n for i, n in enumerate(self.NAMES) if any(r[2 + i] for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.rows[0][1], "reasons": reasons,
+                "samples": len(self.rows), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------
@@ -488,10 +528,12 @@ def run_gpu(args, which):
             json.dump({"rank": rank, "nranks": world, "workload": args.workload, "exchange": sub.exchange_kind,
                        "early": early, "unsplit": args.unsplit,
                        "timeline_ms": [{"op": n, "start": a, "end": b} for n, a, b in tl]}, f, indent=1)
-    barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
+    barrier()
+    if sampler:
+        sampler.reset()
     n0 = capi.launch_count()
     ctx.timer_start(0)
     for _ in range(args.steps):
@@ -634,10 +676,12 @@ def run_gpu_strong(args, which):
     ctx.sync()
     for _ in range(max(args.warmup, 3)):
         sd.step(overlap=not args.no_overlap)
-    barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
+    barrier()
+    if sampler:
+        sampler.reset()
     n0 = capi.launch_count()
     ctx.timer_start(0)
     for _ in range(args.steps):
