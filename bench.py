@@ -510,8 +510,10 @@ def run_gpu(args, which):
             return 3
 
     sub = weak.WeakSubdomain(ctx, SUBDOMAIN, which, rank=rank, procdims=procdims, exchange=args.exchange)
-    if p2p:
-        sub.enable_p2p(gather.bytes)
+    p2p_note = None
+    if p2p and not sub.enable_p2p(gather.bytes):
+        p2p, p2p_note = False, "fell back to NCCL: %s" % sub.p2p_error
+        early = world > 1 and overlap and not args.no_early  # NCCL's exchange wants the early schedule
     field = sub.host_field()
     sub.upload(field)
 
@@ -588,7 +590,7 @@ def run_gpu(args, which):
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": make_config(which, world), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": roofline, "parity": parity,
-                "overlap": overlap, "early_exchange": early, "early_unsplit": bool(args.unsplit and early), "p2p_copy_engine_exchange": p2p,
+                "overlap": overlap, "early_exchange": early, "early_unsplit": bool(args.unsplit and early), "peer_memory_exchange": p2p, "peer_memory_exchange_note": p2p_note,
                 "nccl_max_ctas": int(os.environ.get("BRICKS_NCCL_MAX_CTAS", "0")),
                 "exchange_bytes_per_step_per_gpu": exchange_bytes, "exchange": exchange_kind}
         if kernels is not None:

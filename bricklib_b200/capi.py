@@ -88,6 +88,7 @@ _SIGS = {
     "bricks_step_reset": (C.c_int, [_vp]),
     "bricks_step_p2p_export": (C.c_int, [_vp, _vp, C.c_int, _vp]),
     "bricks_step_p2p_connect": (C.c_int, [_vp, C.c_int, _vp]),
+    "bricks_step_p2p_disable": (C.c_int, [_vp]),
     "bricks_step_trace": (C.c_int, [_vp, C.c_int]),
     "bricks_step_trace_read": (C.c_int, [_vp, C.c_int, C.POINTER(C.c_int), _vp, _vp, _vp]),
     # include/bricks_b200_probe.h
@@ -431,6 +432,9 @@ class Step(object):
         blob = b"".join(descs)
         assert len(blob) == 256 * len(descs)
         check(lib().bricks_step_p2p_connect(self._h, len(descs), C.create_string_buffer(blob, len(blob))))
+
+    def p2p_disable(self):
+        check(lib().bricks_step_p2p_disable(self._h))
 
     def trace(self, enable=True):
         check(lib().bricks_step_trace(self._h, 1 if enable else 0))

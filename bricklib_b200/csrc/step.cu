@@ -327,9 +327,27 @@ int bricks_step_p2p_export(bricks_step *st, double *field0, int rank, void *desc
   return 0;
 }
 
+int bricks_step_p2p_disable(bricks_step *st) {
+  BRK_ARG(st);
+  BRK_CUDA(cudaSetDevice(st->ctx->device));
+  p2p_release(st);
+  return 0;
+}
+
 int bricks_step_p2p_connect(bricks_step *st, int nranks, const void *descs) {
   BRK_ARG(st && st->p2p && descs && nranks >= 1 && nranks <= bricks::kP2PMaxRanks);
   BRK_CUDA(cudaSetDevice(st->ctx->device));
+  {
+    /* the exchange is ordered by stream memory operations: refuse here, where the caller can still
+     * fall back to NCCL on every rank, not at the first step */
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    for (const char *name : {"cuStreamWaitValue32", "cuStreamWriteValue32"})
+      if (cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+        bricks::set_error("bricks_step_p2p_connect: %s is not available from this driver", name);
+        return -6;
+      }
+  }
   bricks::P2PState *p = st->p2p;
   p->nranks = nranks;
   const P2PDesc *d = (const P2PDesc *)descs;

@@ -110,13 +110,35 @@ class WeakSubdomain(object):
         return self.launches_per_step
 
     def enable_p2p(self, allgather):
-        """Copy-engine exchange (bricks_step_p2p_*): the region messages of d_a become cudaMemcpyAsync
-        over NVLink into the peers' ghost bricks instead of NCCL send/recv.  `allgather(bytes)` returns
-        every rank's bytes in rank order (collective: call on all ranks).  Storages other than d_a
-        (the second pair of host_steps) keep the NCCL path."""
-        desc = self.step_obj.p2p_export(self.d_a, self.rank)
-        self.step_obj.p2p_connect(allgather(desc))
+        """Peer-memory exchange (bricks_step_p2p_*): the region messages of d_a are stored straight
+        into the peers' ghost bricks over NVLink instead of going through NCCL send/recv.
+        `allgather(bytes)` returns every rank's bytes in rank order (collective: call on all ranks).
+        All-or-nothing: if export or connect fails on ANY rank (CUDA IPC disabled in a container, no
+        peer access, no stream memory operations) every rank goes back to NCCL and this returns False
+        with the reason in self.p2p_error.  Storages other than d_a (the second pair of host_steps)
+        keep the NCCL path."""
+        self.p2p_error = None
+        desc = b"\0" * 256
+        try:
+            desc = self.step_obj.p2p_export(self.d_a, self.rank)
+        except capi.BricksError as e:
+            self.p2p_error = str(e)
+        descs = allgather(desc + (b"\1" if self.p2p_error is None else b"\0"))
+        if all(d[256:] == b"\1" for d in descs):
+            try:
+                self.step_obj.p2p_connect([d[:256] for d in descs])
+            except capi.BricksError as e:
+                self.p2p_error = str(e)
+        elif self.p2p_error is None:
+            self.p2p_error = "a peer could not export its storage"
+        oks = allgather(b"\1" if self.p2p_error is None else b"\0")
+        if not all(o == b"\1" for o in oks):
+            if self.p2p_error is None:
+                self.p2p_error = "a peer could not map this rank's storage"
+            self.step_obj.p2p_disable()
+            return False
         self.exchange_kind += ", stored straight into peer-mapped ghost bricks over NVLink (no NCCL kernel)"
+        return True
 
     def exchange_only(self, storage=None):
         """the communication program alone, on the communication stream"""

@@ -245,6 +245,10 @@ int bricks_step_sweep(bricks_step *step, int which, int stencil_id, int nfields,
  * only after all ranks have synchronised. */
 int bricks_step_p2p_export(bricks_step *step, double *field0, int rank, void *desc256);
 int bricks_step_p2p_connect(bricks_step *step, int nranks, const void *descs /* nranks x 256 bytes, by rank */);
+/* back to NCCL for every exchange of the step (unmaps the peers).  Setting the path up is all-or-nothing
+ * across ranks: when export or connect fails on ANY rank (CUDA IPC disabled in a container, no peer access),
+ * every rank must call this -- bench.py and bricklib_b200/weak.py agree on it with one more allgather. */
+int bricks_step_p2p_disable(bricks_step *step);
 /* Timeline of a step, for profiles: with tracing on, bricks_step_run puts a CUDA event pair around every
  * operation it enqueues (replaces the per-phase cudaEvent / MPI_Wtime pairs of weak/main.cu:251-286).
  * bricks_step_trace_read synchronises the device and returns, for the LAST traced step, one record per
