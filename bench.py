@@ -530,7 +530,7 @@ def run_gpu(args, which):
             json.dump({"rank": rank, "nranks": world, "workload": args.workload, "exchange": sub.exchange_kind,
                        "early": early, "unsplit": args.unsplit,
                        "timeline_ms": [{"op": n, "start": a, "end": b} for n, a, b in tl]}, f, indent=1)
-    sampler = ClockSampler(local) if rank == 0 else None
+    sampler = ClockSampler(local) if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS") else None  # (diagnosis switch)
     if sampler:
         sampler.start()
     barrier()
