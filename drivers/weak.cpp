@@ -40,7 +40,8 @@ const char *help =
     "  -I: number of iterations, default %d\n"
     "  -S: stencil 7|13|25|125, default 7\n"
     "  -v: validate against the array computation on the host (periodic exchange between the ranks' arrays)\n"
-    "  -n: no overlap (exchange, then sweeps)\n"
+    "  -n: no overlap (exchange, then sweeps); the default on one GPU\n"
+    "  -o: overlap on one GPU too\n"
     "  -E: no early exchange (default with more than one GPU: the next step's exchange starts behind the\n"
     "      last sweep's skin bricks)\n"
     "  -m: SHIFT exchange (three stages, six messages) instead of one message per region\n"
@@ -57,9 +58,9 @@ double now() { return std::chrono::duration<double>(std::chrono::steady_clock::n
 int main(int argc, char **argv) {
   std::vector<unsigned> dom(3, 64);
   int sel = 0, iters = 100, ngpus = 1, which = 7, c;
-  bool bin = false, validate = false, overlap = true, shift = false, packed = false, no_early = false, nccl = false;
+  bool bin = false, validate = false, overlap_flag = true, force_overlap = false, shift = false, packed = false, no_early = false, nccl = false;
   bool force_early = false;
-  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vnmpENe")) != -1) {
+  while ((c = getopt(argc, argv, "d:s:I:hbG:S:vnmpENeo")) != -1) {
     switch (c) {
       case 'b': bin = true; break;
       case 'd': drv::parse_tuple(optarg, dom, 3); sel = sel ? -2 : 1; break;
@@ -68,7 +69,8 @@ int main(int argc, char **argv) {
       case 'G': ngpus = std::stoi(optarg); break;
       case 'S': which = std::stoi(optarg); break;
       case 'v': validate = true; break;
-      case 'n': overlap = false; break;
+      case 'n': overlap_flag = false; break;
+      case 'o': force_overlap = true; break;
       case 'm': shift = true; break;
       case 'p': packed = true; break;
       case 'E': no_early = true; break;
@@ -85,6 +87,9 @@ int main(int argc, char **argv) {
     return 1;
   }
   const int st_iter = drv::stencil_iters(which);
+  // one rank: the exchange is an on-device copy of 0.04 ms; hiding it behind a split first sweep costs more than
+  // it saves (profiles/r03_scaling/diag_n1), so the serial schedule is the default there (-o forces the overlap)
+  const bool overlap = overlap_flag && (ngpus > 1 || force_overlap);
 
   // process grid (weak/args.cpp:92-105)
   int pdims[3] = {1, 1, 1};
