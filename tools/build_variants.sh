@@ -7,7 +7,7 @@ declare -A FLAGS=(
   # add an entry per experiment: [name]="-DSOME_FLAG ..." (the flag must exist in csrc/); experiment
   # builds also get -DMARCH_WAIT_TRAP (a stage that never arrives traps instead of hanging) and
   # -DBRICKS_EXPERIMENT (BRICKS_MAXCOL overrides the column length)
-  [maxcol]=""
+  [maxcol]="-DBRICKS_MAXCOL_BUILD"
   [nomath]="-DMARCH_EXP_NOMATH"
   [cube160]="-DMARCH_CUBE_REGS=160"
   [star4r200]="-DMARCH_STAR4_REGS=200"
