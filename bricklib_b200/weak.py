@@ -137,7 +137,8 @@ class WeakSubdomain(object):
                 self.p2p_error = "a peer could not map this rank's storage"
             self.step_obj.p2p_disable()
             return False
-        self.exchange_kind += ", stored straight into peer-mapped ghost bricks over NVLink (no NCCL kernel)"
+        self.exchange_kind = (self.exchange_kind.replace("one ncclSend/ncclRecv pair per region", "one message per region")
+                              + ", stored straight into peer-mapped ghost bricks over NVLink (no NCCL kernel)")
         return True
 
     def exchange_only(self, storage=None):
