@@ -59,6 +59,8 @@ _SIGS = {
     "bricks_plan_device_tables": (C.c_int, [_vp, _vpp, _vpp]),
     "bricks_stencil": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
     "bricks_stencil_naive": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
+    "bricks_stencil_f32": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
+    "bricks_stencil_naive_f32": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
     "bricks_launch_count": (C.c_int, [C.POINTER(C.c_ulonglong)]),
     "bricks_links_upload": (C.c_int, [_vp, _vp, C.c_int, _vpp]),
     "bricks_copy_regions": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
@@ -297,6 +299,13 @@ class Plan(object):
 
     def stencil_naive(self, stencil, ins, outs, in_step=512, out_step=512, coeff=None, stream=STREAM_COMPUTE):
         self._run(lib().bricks_stencil_naive, stencil, ins, outs, in_step, out_step, coeff, stream)
+
+    def stencil_f32(self, stencil, ins, outs, in_step=512, out_step=512, coeff=None, stream=STREAM_COMPUTE):
+        """fp32 bricks (bElem = float): ins / outs are device pointers to float storages"""
+        self._run(lib().bricks_stencil_f32, stencil, ins, outs, in_step, out_step, coeff, stream)
+
+    def stencil_naive_f32(self, stencil, ins, outs, in_step=512, out_step=512, coeff=None, stream=STREAM_COMPUTE):
+        self._run(lib().bricks_stencil_naive_f32, stencil, ins, outs, in_step, out_step, coeff, stream)
 
 
 class Exchange(object):

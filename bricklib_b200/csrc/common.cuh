@@ -189,5 +189,5 @@ unsigned column_length(int stencil_id);
 /* the plan's item list for that column length (built and uploaded on first use) */
 int plan_items(bricks_plan *plan, unsigned maxcol, const MarchItem **items_dev, int *nitems);
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
-               unsigned bj, unsigned bk, bool swizzle64, unsigned bb = 1);
+               unsigned bj, unsigned bk, bool swizzle64, unsigned bb = 1, unsigned elem_bytes = 8);
 }

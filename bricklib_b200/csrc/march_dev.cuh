@@ -128,17 +128,29 @@ __device__ __forceinline__ void st_quad_if(double *p, const double (&v)[4], bool
       "}\n" ::"l"(p),
       "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]), "r"((int)on));
 }
+/* fp32 bricks: a lane's quad is 16 bytes, one 128-bit streaming store; a warp row still covers whole lines */
+__device__ __forceinline__ void st_quad_if(float *p, const float (&v)[4], bool on) {
+  asm volatile(
+      "{\n"
+      ".reg .pred q;\n"
+      "setp.ne.b32 q, %5, 0;\n"
+      "@q st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};\n"
+      "}\n" ::"l"(p),
+      "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "r"((int)on));
+}
 /* cp.async without the compiler memory barrier: ordering against the loads of a stage comes from
  * cp_async_wait / __syncwarp, which keep theirs */
 __device__ __forceinline__ void cp_async16_nb(uint32_t dst, const void *src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
 }
 
-/* Byte layout of one pipeline stage.  P = planes per main stage (4 or 8). */
-template <int R, bool CUBE, int P>
+/* Byte layout of one pipeline stage.  P = planes per main stage (4 or 8); T = element type (double, or
+ * float for fp32 bricks: 32-byte rows, 2 KiB bricks). */
+template <int R, bool CUBE, int P, typename T = double>
 struct StageLayout {
-  static constexpr int HW = R > 2 ? 4 : 2;      /* i-face width in elements (16-byte multiple) */
-  static constexpr int C_PL = 512, I_PL = 64 * HW, J_PL = 64 * R, X_PL = 8 * R * HW; /* B/plane */
+  static constexpr int EB = (int)sizeof(T);     /* element bytes */
+  static constexpr int HW = (R > 2 ? 4 : 2) * EB >= 16 ? (R > 2 ? 4 : 2) : 16 / EB; /* i-face width in elements (16-byte multiple) */
+  static constexpr int C_PL = 64 * EB, I_PL = 8 * EB * HW, J_PL = 8 * EB * R, X_PL = EB * R * HW; /* B/plane */
   /* 25-point star (R = 4): both j-face boxes are four rows copied with SWIZZLE_64B, which stores the
    * rows with their 16-byte chunks XORed by the row pair index (plus 2 in odd planes): face rows
    * -4..-1 and 8..11 then continue the bank pattern of the centre image, and the two-way bank
@@ -146,9 +158,9 @@ struct StageLayout {
    * wavefronts were conflicts, L1TEX 90 % busy; 0.613 -> 0.542 ms per 66^3-brick sweep,
    * profiles/r03_experiments/variants_k_prepared.log).  For R = 2 (13-point star, cube) the same
    * trick needs a four-row box for a two-row face and measured slower, so it is not used there. */
-  static constexpr bool JLX = !CUBE && R == 4;
+  static constexpr bool JLX = !CUBE && R == 4 && EB == 8; /* fp32 rows are 32 bytes: four rows per 128-byte line, no swizzle */
   static constexpr bool JHX = JLX;
-  static constexpr int JL_ROWS = JLX ? 4 : R, JL_PL = 64 * JL_ROWS;
+  static constexpr int JL_ROWS = JLX ? 4 : R, JL_PL = 8 * EB * JL_ROWS;
   static constexpr int JSUM_PL = 2 * J_PL + 2 * JL_PL; /* the four j-face pieces, bytes per plane */
   static constexpr int C0 = 0, C1 = P * C_PL;
   static constexpr int IL = 2 * P * C_PL, IR = IL + P * I_PL;
@@ -173,9 +185,9 @@ struct PieceK {
   int useb1, di, dj, map, ci, cj, off, plane_bytes, pairmap;
 };
 
-template <int R, bool CUBE, int P>
+template <int R, bool CUBE, int P, typename T = double>
 __device__ __forceinline__ PieceK piece_of(int p) {
-  using L = StageLayout<R, CUBE, P>;
+  using L = StageLayout<R, CUBE, P, T>;
   PieceK k;
   k.useb1 = p & 1;
   const int grp = p >> 1; /* 0 C, 1 I, 2 JL, 3 JH, 4 X-low (LL,RL), 5 X-high (LH,RH) */
@@ -205,9 +217,9 @@ __device__ __forceinline__ PieceK piece_of(int p) {
 
 /* Per-lane addressing constants.  Row j+d of the lane's own brick lives either in the centre
  * piece (64B-swizzled by TMA: 16-byte chunk index ^= (row >> 1) & 3) or in a j-face piece. */
-template <int R, bool CUBE, int P>
+template <int R, bool CUBE, int P, typename T = double>
 struct LaneK {
-  using L = StageLayout<R, CUBE, P>;
+  using L = StageLayout<R, CUBE, P, T>;
   int bb, j, ih;
   int srcL, srcR;        /* shuffle sources for the left / right i-neighbour quads */
   bool halo;             /* this lane loads the i-face (left if bb==0, right if bb==1) */
@@ -229,6 +241,26 @@ struct LaneK {
     for (int d = -R; d <= R; ++d) {
       const int jj = j + d, a = d + R;
       jx[a] = 0;
+      if constexpr (sizeof(T) == 4) {
+        /* fp32: rows of 32 bytes, the lane's quad is the 16-byte half `ih` of its row; the eight lanes of
+         * a quarter-warp read four consecutive rows = 128 contiguous bytes, so nothing is swizzled */
+        constexpr int ROWB = 8 * L::EB, HROWB = L::HW * L::EB;
+        if (jj >= 0 && jj < 8) {
+          row0[a] = (bb ? L::C1 : L::C0) + jj * ROWB + ih * 16;
+          rpitch[a] = L::C_PL;
+          hrow[a] = (bb ? L::IR : L::IL) + jj * HROWB;
+          hpitch[a] = L::I_PL;
+        } else {
+          const bool low = jj < 0;
+          const int rr = low ? jj + R : jj - 8;
+          row0[a] = (low ? (bb ? L::JL1 : L::JL0) : (bb ? L::JH1 : L::JH0)) + rr * ROWB + ih * 16;
+          rpitch[a] = L::J_PL;
+          hrow[a] = (low ? (bb ? L::XRL : L::XLL) : (bb ? L::XRH : L::XLH)) + rr * HROWB;
+          hpitch[a] = L::X_PL;
+        }
+        row1[a] = row0[a];
+        continue;
+      }
       if (L::JHX && jj > 7) {
         const int rr = jj - 8;
         const int base = (bb ? L::JH1 : L::JH0) + rr * 64, x0 = (rr >> 1) & 3;
@@ -274,6 +306,13 @@ struct LaneK {
   }
 };
 
+__device__ __forceinline__ void ld_quad(const char *st, int off0, int /*off1*/, float (&v)[4]) {
+  const float4 a = *reinterpret_cast<const float4 *>(st + off0); /* the whole quad is one 16-byte chunk */
+  v[0] = a.x;
+  v[1] = a.y;
+  v[2] = a.z;
+  v[3] = a.w;
+}
 __device__ __forceinline__ void ld_quad(const char *st, int off0, int off1, double (&v)[4]) {
   const double2 a = *reinterpret_cast<const double2 *>(st + off0);
   const double2 b = *reinterpret_cast<const double2 *>(st + off1);

@@ -31,17 +31,18 @@ static EncodeTiledFn get_encode() {
 /* A field is viewed as the 4-D tensor [brick][k][j][i] of fp64 with strides
  * (step*8, 512, 64, 8) bytes: the layout contract of include/brick.h:229-246 for fold <4,8>. */
 int encode_map(CUtensorMap *m, const void *base, unsigned nbricks, size_t step_elems, unsigned bi,
-               unsigned bj, unsigned bk, bool swizzle64, unsigned bb) {
+               unsigned bj, unsigned bk, bool swizzle64, unsigned bb, unsigned elem_bytes) {
   EncodeTiledFn fn = get_encode();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from this driver");
     return -3;
   }
   cuuint64_t dims[4] = {8, 8, 8, nbricks};
-  cuuint64_t strides[3] = {64, 512, (cuuint64_t)step_elems * 8};
+  /* fp64: rows of 64 bytes, planes of 512; fp32 bricks (bElem = float): 32 and 256 */
+  cuuint64_t strides[3] = {8ull * elem_bytes, 64ull * elem_bytes, (cuuint64_t)step_elems * elem_bytes};
   cuuint32_t box[4] = {bi, bj, bk, bb};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<void *>(base), dims, strides, box,
+  CUresult r = fn(m, elem_bytes == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void *>(base), dims, strides, box,
                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

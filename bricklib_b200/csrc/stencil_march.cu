@@ -19,10 +19,10 @@
 
 namespace {
 
-template <int R, bool CUBE, int VAR, int P>
+template <int R, bool CUBE, int VAR, int P, typename T>
 /* register cap for the cube: measured best on B200 (profiles/r01_maxnreg_sweep.txt) */
 __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R == 1 ? 128 : (R == 2 ? 168 : MARCH_STAR4_REGS))) march_kernel(const __grid_constant__ MarchParams prm) {
-  using L = dev::StageLayout<R, CUBE, P>;
+  using L = dev::StageLayout<R, CUBE, P, T>;
   constexpr int H = 8 / P;
   extern __shared__ __align__(1024) char smem[];
   const int lane = threadIdx.x;
@@ -49,9 +49,9 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     col1 = it.valid1 ? prm.grid[cell + 1] : prm.adj[(size_t)col0 * 27 + 14];
   }
 
-  dev::LaneK<R, CUBE, P> lk;
+  dev::LaneK<R, CUBE, P, T> lk;
   lk.init(lane);
-  const dev::PieceK pk = dev::piece_of<R, CUBE, P>(lane < 12 ? lane : 0);
+  const dev::PieceK pk = dev::piece_of<R, CUBE, P, T>(lane < 12 ? lane : 0);
   constexpr int MAIN_PLANE_BYTES =
       2 * L::C_PL + 2 * L::I_PL + L::JSUM_PL + (CUBE ? 4 * L::X_PL : 0);
   constexpr int ROLL_PLANE_BYTES = CUBE ? MAIN_PLANE_BYTES : 2 * L::C_PL;
@@ -94,13 +94,13 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     }
   };
 
-  double carry[2 * R][4];
+  T carry[2 * R][4];
 #pragma unroll
   for (int a = 0; a < 2 * R; ++a)
 #pragma unroll
     for (int m = 0; m < 4; ++m) carry[a][m] = 0.0;
 
-  dev::OutPtrs o;
+  dev::OutPtrs<T> o;
   o.cur = o.prev = nullptr;
   o.curv = o.prevv = false;
   const int lane_off = lk.j * 8 + lk.ih * 4;
@@ -108,8 +108,19 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
    * fd.out / fd.out_step from global memory every layer (LDG.128 + a long-scoreboard wait in front
    * of the first store: 125-point 0.575 -> 0.562 ms, 25-point 0.629 -> 0.613 ms, the other kernels
    * unchanged; profiles/r02_experiments/variants_h_*, variants_i_*) */
-  double *const out_base = fd.out;
+  T *const out_base = (T *)fd.out;
   const unsigned long long out_stride = fd.out_step;
+
+  /* coefficients in the element type: fp32 bricks compute in float as the reference's generated code does */
+  const T *cc;
+  T cf[27];
+  if constexpr (sizeof(T) == 8) {
+    cc = prm.c;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 27; ++i) cf[i] = (T)prm.c[i];
+    cc = cf;
+  }
 
   unsigned nbn = load_nb(0);
   issue(0, nbn);
@@ -143,35 +154,35 @@ __global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R ==
     }
     if constexpr (CUBE && R == 1) {
       if (mode == 1)
-        dev::cube27_step<P, P, 1>(st, lk, prm.c, carry, o, zbase);
+        dev::cube27_step<P, P, 1, T>(st, lk, cc, carry, o, zbase);
       else if (mode == 0)
-        dev::cube27_step<P, R, 0>(st, lk, prm.c, carry, o, zbase);
+        dev::cube27_step<P, R, 0, T>(st, lk, cc, carry, o, zbase);
       else
-        dev::cube27_step<P, R, 2>(st, lk, prm.c, carry, o, zbase);
+        dev::cube27_step<P, R, 2, T>(st, lk, cc, carry, o, zbase);
     } else if constexpr (CUBE) {
       if (mode == 1)
-        dev::cube_step<P, P, 1>(st, lk, prm.c, carry, o, zbase);
+        dev::cube_step<P, P, 1, T>(st, lk, cc, carry, o, zbase);
       else if (mode == 0)
-        dev::cube_step<P, R, 0>(st, lk, prm.c, carry, o, zbase);
+        dev::cube_step<P, R, 0, T>(st, lk, cc, carry, o, zbase);
       else
-        dev::cube_step<P, R, 2>(st, lk, prm.c, carry, o, zbase);
+        dev::cube_step<P, R, 2, T>(st, lk, cc, carry, o, zbase);
     } else {
       if (mode == 1)
-        dev::star_step<R, VAR, P, P, 1>(st, lk, prm.c, carry, o, zbase);
+        dev::star_step<R, VAR, P, P, 1, T>(st, lk, cc, carry, o, zbase);
       else if (mode == 0)
-        dev::star_step<R, VAR, P, R, 0>(st, lk, prm.c, carry, o, zbase);
+        dev::star_step<R, VAR, P, R, 0, T>(st, lk, cc, carry, o, zbase);
       else
-        dev::star_step<R, VAR, P, R, 2>(st, lk, prm.c, carry, o, zbase);
+        dev::star_step<R, VAR, P, R, 2, T>(st, lk, cc, carry, o, zbase);
     }
     __syncwarp();
   }
 }
 
-template <int R, bool CUBE, int VAR, int P>
+template <int R, bool CUBE, int VAR, int P, typename T>
 int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfields, const double *c, cudaStream_t s) {
-  using L = dev::StageLayout<R, CUBE, P>;
+  using L = dev::StageLayout<R, CUBE, P, T>;
   const int smem = 2 * L::BYTES + 64;
-  auto kern = march_kernel<R, CUBE, VAR, P>;
+  auto kern = march_kernel<R, CUBE, VAR, P, T>;
   /* per device, once; host threads that drive different devices may be here concurrently (setting
    * the attributes twice is harmless, the mask only saves the calls) */
   static std::atomic<unsigned long long> configured{0};
@@ -201,11 +212,14 @@ int launch(bricks_plan *plan, int stencil_id, const FieldDev *fields, int nfield
 constexpr int kPlanes = 4;
 
 /* build (or find) the device FieldDev array for these storages and this kernel variant */
-int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const double *const *in,
-               double *const *out, size_t in_step, size_t out_step, cudaStream_t s,
+template <typename T>
+int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const T *const *in,
+               T *const *out, size_t in_step, size_t out_step, cudaStream_t s,
                const FieldDev **dev_out) {
+  constexpr unsigned EB = sizeof(T);
+  constexpr bool f64 = EB == 8;
   FieldKey key;
-  key.variant = stencil_id * 16 + P;
+  key.variant = stencil_id * 16 + P + (f64 ? 0 : 8);
   key.in_step = in_step;
   key.out_step = out_step;
   for (int f = 0; f < nfields; ++f) {
@@ -219,30 +233,30 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
   }
   const int R = stencil_id == 13 || stencil_id == 125 ? 2 : (stencil_id == 25 ? 4 : 1);
   const bool cube = stencil_id == 125 || stencil_id == BRICKS_ST_27PT_COEFF;
-  const int HW = R > 2 ? 4 : 2;
+  const int HW = (R > 2 || !f64) ? 4 : 2; /* i-face width in elements: a 16-byte multiple (StageLayout::HW) */
+  const bool jswz = f64 && !cube && R == 4; /* swizzled four-row j-face box (march_dev.cuh StageLayout::JLX) */
   std::vector<FieldDev> host(nfields);
   for (int f = 0; f < nfields; ++f) {
     FieldDev &fd = host[f];
     memset(&fd, 0, sizeof fd);
-    fd.out = out[f];
+    fd.out = (double *)out[f]; /* the kernel casts it back to its element type */
     fd.out_step = out_step;
-    fd.in = in[f];
+    fd.in = (const double *)in[f];
     fd.in_step = in_step;
     for (int roll = 0; roll < 2; ++roll) {
       CUtensorMap *m = roll ? fd.maps.roll : fd.maps.main;
       const unsigned pk = roll ? R : P;
-      int rc = bricks::encode_map(&m[0], in[f], plan->nbricks, in_step, 8, 8, pk, true);
-      if (!rc) rc = bricks::encode_map(&m[1], in[f], plan->nbricks, in_step, HW, 8, pk, false);
-      if (!rc) rc = bricks::encode_map(&m[2], in[f], plan->nbricks, in_step, 8, R, pk, false);
-      if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false);
-      if (!rc && !cube && R == 4) /* swizzled four-row j-face box (march_dev.cuh StageLayout::JLX) */
-        rc = bricks::encode_map(&m[4], in[f], plan->nbricks, in_step, 8, 4, pk, true);
+      /* the centre image is 64B-swizzled for fp64 (64-byte rows); fp32 rows are 32 bytes: dense */
+      int rc = bricks::encode_map(&m[0], in[f], plan->nbricks, in_step, 8, 8, pk, f64, 1, EB);
+      if (!rc) rc = bricks::encode_map(&m[1], in[f], plan->nbricks, in_step, HW, 8, pk, false, 1, EB);
+      if (!rc) rc = bricks::encode_map(&m[2], in[f], plan->nbricks, in_step, 8, R, pk, false, 1, EB);
+      if (!rc) rc = bricks::encode_map(&m[3], in[f], plan->nbricks, in_step, HW, cube ? R : 8, pk, false, 1, EB);
+      if (!rc && jswz) rc = bricks::encode_map(&m[4], in[f], plan->nbricks, in_step, 8, 4, pk, true, 1, EB);
       if (rc) return rc;
     }
-    int rc = bricks::encode_map(&fd.maps.pair[0], in[f], plan->nbricks, in_step, 8, 8, P, true, 2);
-    if (!rc) rc = bricks::encode_map(&fd.maps.pair[1], in[f], plan->nbricks, in_step, 8, R, P, false, 2);
-    if (!rc && !cube && R == 4)
-      rc = bricks::encode_map(&fd.maps.pair[2], in[f], plan->nbricks, in_step, 8, 4, P, true, 2);
+    int rc = bricks::encode_map(&fd.maps.pair[0], in[f], plan->nbricks, in_step, 8, 8, P, f64, 2, EB);
+    if (!rc) rc = bricks::encode_map(&fd.maps.pair[1], in[f], plan->nbricks, in_step, 8, R, P, false, 2, EB);
+    if (!rc && jswz) rc = bricks::encode_map(&fd.maps.pair[2], in[f], plan->nbricks, in_step, 8, 4, P, true, 2, EB);
     if (rc) return rc;
   }
   FieldDev *d = nullptr;
@@ -256,15 +270,19 @@ int get_fields(bricks_plan *plan, int stencil_id, int P, int nfields, const doub
 
 }  // namespace
 
-extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, const double *const *in,
-                              double *const *out, size_t in_step, size_t out_step,
-                              const double *coeff_host, int stream) {
+namespace {
+
+/* the body of bricks_stencil / bricks_stencil_f32: T = element type of the bricks */
+template <typename T>
+int run_stencil(bricks_plan *plan, int stencil_id, int nfields, const T *const *in, T *const *out, size_t in_step,
+                size_t out_step, const double *coeff_host, int stream) {
   BRK_ARG(plan && in && out && nfields > 0 && nfields < 65536);
   BRK_ARG(stream >= 0 && stream < bricks::kNumStreams);
   BRK_ARG(in_step >= 512 && in_step % 2 == 0 && out_step >= 512 && out_step % 4 == 0);
   for (int f = 0; f < nfields; ++f) {
     BRK_ARG(in[f] && out[f] && in[f] != out[f]);
-    BRK_ARG(((uintptr_t)in[f] & 15) == 0 && ((uintptr_t)out[f] & 31) == 0);
+    /* TMA needs the field 16-byte aligned; a lane stores its quad as one 32-byte (fp64) / 16-byte (fp32) vector */
+    BRK_ARG(((uintptr_t)in[f] & 15) == 0 && ((uintptr_t)out[f] & (4 * sizeof(T) - 1)) == 0);
   }
   switch (stencil_id) { /* before anything is built or cached for it */
     case BRICKS_ST_7PT: case BRICKS_ST_13PT: case BRICKS_ST_25PT: case BRICKS_ST_125PT: break;
@@ -284,34 +302,48 @@ extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, co
     case BRICKS_ST_7PT_COEFF:
       BRK_ARG(coeff_host);
       for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
-      return launch<1, false, 1, P>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, false, 1, P, T>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_COND: /* cond.py (d3cond, stencils/3axis.cpp:94-163): coeff[0..6] as 7pt.py */
       BRK_ARG(coeff_host);
       for (int i = 0; i < 7; ++i) c[i] = coeff_host[i];
-      return launch<1, false, 2, P>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, false, 2, P, T>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_27PT_COEFF: /* d3pt27 (stencils/3axis.cpp:165-247) */
       BRK_ARG(coeff_host);
       for (int i = 0; i < 27; ++i) c[i] = coeff_host[i];
       /* the reference reads term 16 at (k+1, j+1, i), the place of term 25, not at (k, j+1, i) */
       c[25] += c[16];
       c[16] = 0.0;
-      return launch<1, true, 1, P>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, true, 1, P, T>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_7PT: /* MPI_ALPHA, MPI_BETA (stencils/fake.h:11-12) */
       c[0] = 0.4, c[1] = 0.1;
-      return launch<1, false, 0, P>(plan, stencil_id, fields, nfields, c, s);
+      return launch<1, false, 0, P, T>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_13PT: /* MPI_B0..B2 (fake.h:20-22) */
       c[0] = 0.4, c[1] = 0.07, c[2] = 0.03;
-      return launch<2, false, 0, P>(plan, stencil_id, fields, nfields, c, s);
+      return launch<2, false, 0, P, T>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_25PT: /* MPI_A0..A4 (fake.h:14-18) */
       c[0] = 0.1, c[1] = 0.06, c[2] = 0.045, c[3] = 0.03, c[4] = 0.015;
-      return launch<4, false, 0, P>(plan, stencil_id, fields, nfields, c, s);
+      return launch<4, false, 0, P, T>(plan, stencil_id, fields, nfields, c, s);
     case BRICKS_ST_125PT: { /* MPI_C0..C9 (fake.h:24-33) */
       const double cc[10] = {0.1, 0.04, 0.03, 0.01, 0.006, 0.004, 0.005, 0.002, 0.003, 0.001};
       for (int i = 0; i < 10; ++i) c[i] = cc[i];
-      return launch<2, true, 0, P>(plan, stencil_id, fields, nfields, c, s);
+      return launch<2, true, 0, P, T>(plan, stencil_id, fields, nfields, c, s);
     }
     default:
       bricks::set_error("unknown stencil id %d", stencil_id);
       return -1;
   }
+}
+
+}  // namespace
+
+extern "C" int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, const double *const *in,
+                              double *const *out, size_t in_step, size_t out_step,
+                              const double *coeff_host, int stream) {
+  return run_stencil<double>(plan, stencil_id, nfields, in, out, in_step, out_step, coeff_host, stream);
+}
+
+extern "C" int bricks_stencil_f32(bricks_plan *plan, int stencil_id, int nfields, const float *const *in,
+                                  float *const *out, size_t in_step, size_t out_step,
+                                  const double *coeff_host, int stream) {
+  return run_stencil<float>(plan, stencil_id, nfields, in, out, in_step, out_step, coeff_host, stream);
 }

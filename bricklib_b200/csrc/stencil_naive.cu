@@ -7,11 +7,12 @@
 
 namespace {
 
+template <typename T>
 struct NaiveParams {
   const unsigned *adj;
   const unsigned *blist;
-  const double *in;
-  double *out;
+  const T *in;
+  T *out;
   unsigned long long in_step, out_step;
   int npts;
   int cond; /* cond.py: max(in, 0) per term, |sum| */
@@ -20,19 +21,23 @@ struct NaiveParams {
 __constant__ int c_off[125 * 3];
 __constant__ double c_coef[125];
 
-__global__ void __launch_bounds__(512) naive_kernel(NaiveParams p) {
+/* T = double, or float for fp32 bricks (bElem = float, include/vecscatter.h:12-14): same point set, the
+ * coefficients rounded to T, every term accumulated in T as the reference's generated code does */
+template <typename T>
+__global__ void __launch_bounds__(512) naive_kernel(NaiveParams<T> p) {
   const unsigned b = p.blist[blockIdx.x];
   const int i = threadIdx.x & 7, j = (threadIdx.x >> 3) & 7, k = threadIdx.x >> 6;
   const unsigned *row = p.adj + (size_t)b * 27;
-  double acc = 0.0;
+  T acc = 0;
   for (int t = 0; t < p.npts; ++t) {
     const int ii = i + c_off[3 * t] + 8, jj = j + c_off[3 * t + 1] + 8, kk = k + c_off[3 * t + 2] + 8;
     const unsigned nb = row[((kk >> 3) * 3 + (jj >> 3)) * 3 + (ii >> 3)];
-    double v = p.in[(size_t)nb * p.in_step + (kk & 7) * 64 + (jj & 7) * 8 + (ii & 7)];
-    if (p.cond) v = fmax(v, 0.0);
-    acc = t ? acc + c_coef[t] * v : c_coef[t] * v;
+    T v = p.in[(size_t)nb * p.in_step + (kk & 7) * 64 + (jj & 7) * 8 + (ii & 7)];
+    if (p.cond) v = fmax(v, (T)0);
+    const T c = (T)c_coef[t];
+    acc = t ? acc + c * v : c * v;
   }
-  p.out[(size_t)b * p.out_step + threadIdx.x] = p.cond ? fabs(acc) : acc;
+  p.out[(size_t)b * p.out_step + threadIdx.x] = p.cond ? (T)fabs(acc) : acc;
 }
 
 int build_points(int id, const double *coeff, int *off, double *cf) {
@@ -80,11 +85,9 @@ int build_points(int id, const double *coeff, int *off, double *cf) {
   return n;
 }
 
-}  // namespace
-
-extern "C" int bricks_stencil_naive(bricks_plan *plan, int stencil_id, int nfields,
-                                    const double *const *in, double *const *out, size_t in_step,
-                                    size_t out_step, const double *coeff_host, int stream) {
+template <typename T>
+int run_naive(bricks_plan *plan, int stencil_id, int nfields, const T *const *in, T *const *out, size_t in_step,
+              size_t out_step, const double *coeff_host, int stream) {
   BRK_ARG(plan && in && out && nfields > 0 && stream >= 0 && stream < bricks::kNumStreams);
   BRK_CUDA(cudaSetDevice(plan->ctx->device));
   cudaStream_t s = plan->ctx->streams[stream];
@@ -99,7 +102,7 @@ extern "C" int bricks_stencil_naive(bricks_plan *plan, int stencil_id, int nfiel
   BRK_CUDA(cudaMemcpyToSymbolAsync(c_coef, cf, sizeof(double) * n, 0, cudaMemcpyHostToDevice, s));
   BRK_CUDA(cudaStreamSynchronize(s)); /* off/cf are stack arrays */
   for (int f = 0; f < nfields; ++f) {
-    NaiveParams p;
+    NaiveParams<T> p;
     p.adj = plan->adj_dev;
     p.blist = plan->blist_dev;
     p.in = in[f];
@@ -108,9 +111,23 @@ extern "C" int bricks_stencil_naive(bricks_plan *plan, int stencil_id, int nfiel
     p.out_step = out_step;
     p.npts = n;
     p.cond = stencil_id == BRICKS_ST_COND;
-    naive_kernel<<<(unsigned)plan->nlist, 512, 0, s>>>(p);
+    naive_kernel<T><<<(unsigned)plan->nlist, 512, 0, s>>>(p);
     BRK_CUDA(cudaGetLastError());
     ++bricks::g_launches;
   }
   return 0;
+}
+
+}  // namespace
+
+extern "C" int bricks_stencil_naive(bricks_plan *plan, int stencil_id, int nfields,
+                                    const double *const *in, double *const *out, size_t in_step,
+                                    size_t out_step, const double *coeff_host, int stream) {
+  return run_naive<double>(plan, stencil_id, nfields, in, out, in_step, out_step, coeff_host, stream);
+}
+
+extern "C" int bricks_stencil_naive_f32(bricks_plan *plan, int stencil_id, int nfields,
+                                        const float *const *in, float *const *out, size_t in_step,
+                                        size_t out_step, const double *coeff_host, int stream) {
+  return run_naive<float>(plan, stencil_id, nfields, in, out, in_step, out_step, coeff_host, stream);
 }

@@ -104,17 +104,32 @@ inline void copyToBrickDevice(const std::vector<long> &dimlist, const std::vecto
                               const std::vector<long> &ghost, bElem *arr_dev, const unsigned *grid_dev, T &brick,
                               int stream = BRICKS_STREAM_COMPUTE) {
   static_assert(dims == 3, "device copies implement the 3-D case");
-  gpuCheck(bricks_copy_array(bricksContext(), 1, dimlist.data(), padding.data(), ghost.data(), arr_dev, grid_dev,
-                             brick.dat, brick.step, stream));
+  static_assert(sizeof(bElem) == 8, "bricks_copy_array moves fp64 elements; fp32 bricks use the host copyToBrick");
+  gpuCheck(bricks_copy_array(bricksContext(), 1, dimlist.data(), padding.data(), ghost.data(), (double *)arr_dev, grid_dev,
+                             (double *)brick.dat, brick.step, stream));
 }
 template <unsigned dims, typename T>
 inline void copyFromBrickDevice(const std::vector<long> &dimlist, const std::vector<long> &padding,
                                 const std::vector<long> &ghost, bElem *arr_dev, const unsigned *grid_dev, T &brick,
                                 int stream = BRICKS_STREAM_COMPUTE) {
   static_assert(dims == 3, "device copies implement the 3-D case");
-  gpuCheck(bricks_copy_array(bricksContext(), 0, dimlist.data(), padding.data(), ghost.data(), arr_dev, grid_dev,
-                             brick.dat, brick.step, stream));
+  static_assert(sizeof(bElem) == 8, "bricks_copy_array moves fp64 elements; fp32 bricks use the host copyToBrick");
+  gpuCheck(bricks_copy_array(bricksContext(), 0, dimlist.data(), padding.data(), ghost.data(), (double *)arr_dev, grid_dev,
+                             (double *)brick.dat, brick.step, stream));
 }
+
+namespace bricks_detail {
+/// bricks_stencil for the element type of the build: double, or float when the translation unit says
+/// `#define bElem float` before including the headers (include/vecscatter.h:12-14 of the reference)
+inline int stencil_call(bricks_plan *p, int id, int n, const double *const *in, double *const *out, size_t is, size_t os,
+                        const double *c, int stream) {
+  return bricks_stencil(p, id, n, in, out, is, os, c, stream);
+}
+inline int stencil_call(bricks_plan *p, int id, int n, const float *const *in, float *const *out, size_t is, size_t os,
+                        const double *c, int stream) {
+  return bricks_stencil_f32(p, id, n, in, out, is, os, c, stream);
+}
+}  // namespace bricks_detail
 
 /// A launch plan over boxes of a brick grid: the host side of
 /// `brick_kernel<<<dim3(strideb...), 32>>>` (weak/main.cu:277).  Owns the device copies of the
@@ -140,14 +155,15 @@ class BrickStencilPlan {
   /// out = stencil(in) for one pair of Brick views on DEVICE storages (asynchronous)
   template <typename B>
   void run(int stencil_id, B &in, B &out, const double *coeff = nullptr, int stream = BRICKS_STREAM_COMPUTE) {
-    const double *i[1] = {in.dat};
-    double *o[1] = {out.dat};
-    gpuCheck(bricks_stencil(plan_, stencil_id, 1, i, o, in.step, out.step, coeff, stream));
+    const bElem *i[1] = {in.dat};
+    bElem *o[1] = {out.dat};
+    gpuCheck(bricks_detail::stencil_call(plan_, stencil_id, 1, i, o, in.step, out.step, coeff, stream));
   }
   /// batched over many storage pairs that share the grid/adjacency (strong scaling)
-  void run(int stencil_id, const std::vector<const double *> &in, const std::vector<double *> &out, size_t in_step,
+  void run(int stencil_id, const std::vector<const bElem *> &in, const std::vector<bElem *> &out, size_t in_step,
            size_t out_step, const double *coeff = nullptr, int stream = BRICKS_STREAM_COMPUTE) {
-    gpuCheck(bricks_stencil(plan_, stencil_id, (int)in.size(), in.data(), out.data(), in_step, out_step, coeff, stream));
+    gpuCheck(bricks_detail::stencil_call(plan_, stencil_id, (int)in.size(), in.data(), out.data(), in_step, out_step, coeff,
+                                         stream));
   }
   bricks_plan *handle() { return plan_; }
   /// device copies of the grid and the adjacency list held by the plan

@@ -163,7 +163,7 @@ struct ExchangeView {
   /// enqueue on the communication stream; compute on interior bricks may proceed
   void start() {
     bricks_detail::require(bricks_stream_wait(comm.ctx, BRICKS_STREAM_COMM, BRICKS_STREAM_COMPUTE), "exchange");
-    bricks_detail::require(bricks_exchange_run(plan, storage_dev, BRICKS_STREAM_COMM), "exchange");
+    bricks_detail::require(bricks_exchange_run(plan, (double *)storage_dev, BRICKS_STREAM_COMM), "exchange");
   }
   /// make the compute stream wait for the exchange (no host block)
   void wait() { bricks_detail::require(bricks_stream_wait(comm.ctx, BRICKS_STREAM_COMPUTE, BRICKS_STREAM_COMM), "exchange"); }
@@ -188,7 +188,7 @@ struct MultiStageExchangeView {
   void start() {
     bricks_detail::require(bricks_stream_wait(comm.ctx, BRICKS_STREAM_COMM, BRICKS_STREAM_COMPUTE), "exchange");
     for (bricks_exchange *st : stages)
-      bricks_detail::require(bricks_exchange_run(st, storage_dev, BRICKS_STREAM_COMM), "exchange");
+      bricks_detail::require(bricks_exchange_run(st, (double *)storage_dev, BRICKS_STREAM_COMM), "exchange");
   }
   void wait() { bricks_detail::require(bricks_stream_wait(comm.ctx, BRICKS_STREAM_COMPUTE, BRICKS_STREAM_COMM), "exchange"); }
 };

@@ -121,6 +121,18 @@ int bricks_stencil(bricks_plan *plan, int stencil_id, int nfields, const double 
 int bricks_stencil_naive(bricks_plan *plan, int stencil_id, int nfields, const double *const *in,
                          double *const *out, size_t in_step, size_t out_step,
                          const double *coeff_host, int stream);
+/* fp32 bricks: the reference's element type is overridable (`#define bElem float`, include/vecscatter.h:12-14;
+ * include/bricks/brick.h honours the same macro).  A brick is then 8x8x8 floats = 2 KiB, rows of 32 bytes, same
+ * [k][j][i] order, `step` still in elements; everything that moves bytes (exchange, region copies, the step
+ * object's communication program) is element-size agnostic.  Same marching kernels instantiated for float
+ * (quads of 16 bytes, i-face pieces four elements wide, no swizzle: four rows make one 128-byte line); the
+ * coefficients are rounded to float and all arithmetic is float, as in the reference's generated code. */
+int bricks_stencil_f32(bricks_plan *plan, int stencil_id, int nfields, const float *const *in,
+                       float *const *out, size_t in_step, size_t out_step, const double *coeff_host,
+                       int stream);
+int bricks_stencil_naive_f32(bricks_plan *plan, int stencil_id, int nfields, const float *const *in,
+                             float *const *out, size_t in_step, size_t out_step,
+                             const double *coeff_host, int stream);
 /* number of kernels launched by this library so far in this process */
 int bricks_launch_count(unsigned long long *count);
 

@@ -66,6 +66,8 @@ def lib():
         L.oracle_points.argtypes = [C.c_int, vp, vp, vp]
         L.oracle_brick_sweep.restype = C.c_int
         L.oracle_brick_sweep.argtypes = [C.c_int, vp, vp, C.c_long, vp, C.c_long, vp, C.c_long, vp]
+        L.oracle_brick_sweep_f32.restype = C.c_int
+        L.oracle_brick_sweep_f32.argtypes = [C.c_int, vp, vp, C.c_long, vp, C.c_long, vp, C.c_long, vp]
         L.oracle_array_sweep.restype = C.c_int
         L.oracle_array_sweep.argtypes = [C.c_int, vp, vp] + [C.c_long] * 9 + [vp]
         L.oracle_copy_brick.argtypes = [C.c_int, vp, vp, vp, vp, vp, vp, C.c_long]
@@ -110,6 +112,19 @@ def brick_sweep(which, adj, blist, inp, out, in_step=512, out_step=512, coeff=No
                                  out_step, _p(cin))
     if r:
         raise ValueError("unknown stencil %r" % (which,))
+    return out
+
+
+def brick_sweep_f32(which, adj, blist, inp, out, in_step=512, out_step=512, coeff=None):
+    """fp32 bricks: out[b] = stencil(inp) computed in float (1-D float32 views, row-major bricks)."""
+    adj = np.ascontiguousarray(adj, np.uint32)
+    blist = np.ascontiguousarray(blist, np.uint32)
+    cin = None if coeff is None else np.ascontiguousarray(coeff, np.float64)
+    assert inp.dtype == np.float32 and out.dtype == np.float32
+    r = lib().oracle_brick_sweep_f32(which, _p(adj), _p(blist), blist.size, _p(inp), in_step, _p(out),
+                                     out_step, _p(cin))
+    if r:
+        raise ValueError("unknown stencil %r for fp32" % (which,))
     return out
 
 

@@ -20,7 +20,8 @@ _u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
 _i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
 _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
 
-STENCILS = (0, 1, 7, 13, 25, 125)  # 0 = stencils/7pt.py with coeff[], 1 = cond.py (same coeff[]); others = mpi<N>pt.py
+STENCILS = (0, 1, 7, 13, 25, 125)
+STENCILS_F32 = (7, 13, 25, 125)  # built with -DbElem=float (AVX-512 only): symbols reff<N>_*  # 0 = stencils/7pt.py with coeff[], 1 = cond.py (same coeff[]); others = mpi<N>pt.py
 
 
 def host_isa():
@@ -148,6 +149,35 @@ def array_sweep(which, inp, out, box, coeff=None):
     s2, s1, s0 = inp.shape
     getattr(L, "ref%d_array_sweep" % which)(inp.reshape(-1), out.reshape(-1), s0, s1, s2,
                                             *[int(x) for x in box], cp)
+    return out
+
+
+def available_f32():
+    """the fp32 build of the reference (bElem = float) exists for AVX-512 hosts only"""
+    if not available() or host_isa() != "avx512":
+        return False
+    try:
+        return hasattr(lib(), "reff125_brick_sweep_rm")
+    except OSError:
+        return False
+
+
+def brick_sweep_rm_f32(which, adj, blist, inp, out, step):
+    """One sweep of the reference's generated brick kernel built with bElem = float over row-major
+    float32 brick storages (in place on `out`)."""
+    L = lib()
+    fn = getattr(L, "reff%d_brick_sweep_rm" % which)
+    fn.argtypes = [_u32p, C.c_uint, _u32p, C.c_long, C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]
+    fn.restype = None
+    adj = np.ascontiguousarray(adj, dtype=np.uint32)
+    blist = np.ascontiguousarray(blist, dtype=np.uint32)
+    assert inp.dtype == np.float32 and out.dtype == np.float32
+    ai = aligned_empty(inp.size, np.float32)
+    ai[:] = inp.reshape(-1)
+    ao = aligned_empty(out.size, np.float32)
+    ao[:] = out.reshape(-1)
+    fn(adj.reshape(-1), adj.shape[0], blist, blist.size, ai.ctypes.data, ao.ctypes.data, step, None)
+    out.reshape(-1)[...] = ao
     return out
 
 

@@ -11,6 +11,11 @@
  * -DREF_WHICH=0 for stencils/7pt.py with the runtime `coeff[]` array, -DREF_WHICH=1 for
  * stencils/cond.py, the max/abs stencil of d3cond, stencils/3axis.cpp:94-163) into
  * oracle/_ref/.  Used by tests, oracle/gen_golden.py and bench.py's CPU baseline.
+ *
+ * fp32 bricks: built a second time with -DbElem=float -DREF_F32 (include/vecscatter.h:12-14 makes the
+ * element type overridable; the code generator takes it from the pragma and emits 16-wide float
+ * vectors).  Fold 2,8 = one AVX-512 float vector per two rows, which keeps a brick row-major.  The
+ * symbols of that build are reff<N>_*; data pointers are `bElem *` throughout.
  */
 #include <omp.h>
 #include <algorithm>
@@ -31,12 +36,25 @@
 #include "stencils/cpuvfold.h"
 #include <bricksetup.h>
 
+#ifdef REF_F32
+#ifndef __AVX512F__
+#error "the fp32 reference build is AVX-512 only (16 floats per vector, fold 2,8)"
+#endif
+#undef VFOLD
+#define VFOLD 2, 8
+#endif
+typedef bElem ref_elem;
+
 #define REF_BDIM 8, 8, 8
 typedef Brick<Dim<REF_BDIM>, Dim<VFOLD>> Brick3D;
 
 #define REF_CAT2(a, b) a##b
 #define REF_CAT(a, b) REF_CAT2(a, b)
+#ifdef REF_F32
+#define REFSYM(name) REF_CAT(REF_CAT(reff, REF_WHICH), _##name)
+#else
 #define REFSYM(name) REF_CAT(REF_CAT(ref, REF_WHICH), _##name)
+#endif
 
 #if REF_WHICH == 0 || REF_WHICH == 1
 static bElem *coeff = nullptr; /* the free identifier stencils/7pt.py and cond.py name (one per translation unit) */
@@ -47,7 +65,7 @@ using std::max; /* cond.py calls max(); stencils/3axis.cpp:12 */
 
 namespace {
 
-BrickStorage wrap(double *p, long chunks, long step) {
+BrickStorage wrap(ref_elem *p, long chunks, long step) {
   BrickStorage s;
   s.dat = std::shared_ptr<bElem>(p, [](bElem *) {});
   s.chunks = chunks;
@@ -72,7 +90,7 @@ void fold_table(unsigned *tab) {
   unsigned adj1[27];
   for (int i = 0; i < 27; ++i) adj1[i] = 0;
   InfoView iv(adj1, 1);
-  static double buf[512];
+  static ref_elem buf[512];
   BrickStorage st = wrap(buf, 1, 512);
   Brick3D b(&iv.info, st, 0);
   for (unsigned k = 0; k < 8; ++k)
@@ -99,7 +117,7 @@ void REFSYM(fold_table)(unsigned *tab512) { fold_table(tab512); }
 /* One sweep of the codegen brick kernel over blist[0..nlist); storages are in the
  * reference's own fold order for this build (see fold_table). */
 void REFSYM(brick_sweep)(const unsigned *adj, unsigned nbricks, const unsigned *blist, long nlist,
-                         double *in_dat, double *out_dat, long step, const double *coeff_in) {
+                         ref_elem *in_dat, ref_elem *out_dat, long step, const double *coeff_in) {
   InfoView iv(adj, nbricks);
   BrickStorage sin = wrap(in_dat, nbricks, step), sout = wrap(out_dat, nbricks, step);
 #if REF_WHICH == 0 || REF_WHICH == 1
@@ -119,18 +137,18 @@ void REFSYM(brick_sweep)(const unsigned *adj, unsigned nbricks, const unsigned *
 /* Same as brick_sweep but storages are row-major [k][j][i] bricks (the device layout);
  * converted through fold_table when this build folds differently. */
 void REFSYM(brick_sweep_rm)(const unsigned *adj, unsigned nbricks, const unsigned *blist, long nlist,
-                            const double *in_rm, double *out_rm, long step, const double *coeff_in) {
+                            const ref_elem *in_rm, ref_elem *out_rm, long step, const double *coeff_in) {
   unsigned tab[512];
   fold_table(tab);
   bool ident = true;
   for (unsigned e = 0; e < 512; ++e) ident = ident && (tab[e] == e);
   if (ident) {
-    REFSYM(brick_sweep)(adj, nbricks, blist, nlist, const_cast<double *>(in_rm), out_rm, step, coeff_in);
+    REFSYM(brick_sweep)(adj, nbricks, blist, nlist, const_cast<ref_elem *>(in_rm), out_rm, step, coeff_in);
     return;
   }
   size_t tot = (size_t)nbricks * step;
-  double *fin = (double *)aligned_alloc(64, tot * sizeof(double));
-  double *fout = (double *)aligned_alloc(64, tot * sizeof(double));
+  ref_elem *fin = (ref_elem *)aligned_alloc(64, tot * sizeof(ref_elem));
+  ref_elem *fout = (ref_elem *)aligned_alloc(64, tot * sizeof(ref_elem));
   long nfield = step / 512;
 #pragma omp parallel for
   for (long c = 0; c < (long)nbricks * nfield; ++c)
@@ -149,7 +167,7 @@ void REFSYM(brick_sweep_rm)(const unsigned *adj, unsigned nbricks, const unsigne
 /* `reps` ping-pong sweeps (in->out, out->in, ...) timed with omp_get_wtime after one
  * warm-up sweep; returns seconds per sweep.  All host threads OpenMP gives us. */
 double REFSYM(brick_sweep_timed)(const unsigned *adj, unsigned nbricks, const unsigned *blist,
-                                 long nlist, double *a, double *b, long step, const double *coeff_in,
+                                 long nlist, ref_elem *a, ref_elem *b, long step, const double *coeff_in,
                                  int reps) {
   REFSYM(brick_sweep)(adj, nbricks, blist, nlist, a, b, step, coeff_in);
   double t0 = omp_get_wtime();
@@ -166,7 +184,7 @@ int REFSYM(max_threads)() { return omp_get_max_threads(); }
 
 /* The reference's literal array stencil over the box [k0,k1) x [j0,j1) x [i0,i1) of a
  * padded array with extents (s0,s1,s2), contiguous dimension first. */
-void REFSYM(array_sweep)(const double *in_ptr, double *out_ptr, long s0, long s1, long s2, long k0,
+void REFSYM(array_sweep)(const ref_elem *in_ptr, ref_elem *out_ptr, long s0, long s1, long s2, long k0,
                          long k1, long j0, long j1, long i0, long i1, const double *coeff_in) {
   (void)s2;
   auto arrIn = (const bElem(*)[s1][s0])in_ptr;

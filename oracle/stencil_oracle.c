@@ -161,6 +161,38 @@ int oracle_brick_sweep(int which, const unsigned *adj, const unsigned *blist, lo
   return 0;
 }
 
+/* fp32 bricks (bElem = float, include/vecscatter.h:12-14): the same point set and term order, the
+ * coefficients rounded to float and every product and sum in float -- what the reference's generated
+ * code computes when it is built with -DbElem=float (the constants of stencils/fake.h are double
+ * literals, but the code generator emits them into float vectors).  Pinned by tests against that build
+ * (oracle/_ref, reff<N>_brick_sweep) to a few ulp: summation order inside a vector differs. */
+int oracle_brick_sweep_f32(int which, const unsigned *adj, const unsigned *blist, long nlist,
+                           const float *in, long in_step, float *out, long out_step,
+                           const double *coeff_in) {
+  static int off[MAXPTS * 3];
+  static double c[MAXPTS];
+  int np = oracle_points(which, coeff_in, off, c);
+  if (np < 0 || oracle_is_cond(which)) return -1;
+#pragma omp parallel for schedule(static)
+  for (long n = 0; n < nlist; ++n) {
+    unsigned b = blist[n];
+    for (int k = 0; k < 8; ++k)
+      for (int j = 0; j < 8; ++j)
+        for (int i = 0; i < 8; ++i) {
+          float acc = 0.0f;
+          for (int t = 0; t < np; ++t) {
+            int kk = k + off[3 * t + 2], jj = j + off[3 * t + 1], ii = i + off[3 * t + 0];
+            unsigned nb = adj[(size_t)b * 27 + (((kk + 8) / 8) * 3 + (jj + 8) / 8) * 3 + (ii + 8) / 8];
+            float v = in[(size_t)nb * in_step + ((kk + 8) % 8) * 64 + ((jj + 8) % 8) * 8 + (ii + 8) % 8];
+            float term = (float)c[t] * v;
+            acc = t ? acc + term : term;
+          }
+          out[(size_t)b * out_step + k * 64 + j * 8 + i] = acc;
+        }
+  }
+  return 0;
+}
+
 /* array twin on a padded array with extents (s0,s1,s2), contiguous first, over a box */
 int oracle_array_sweep(int which, const double *in, double *out, long s0, long s1, long s2, long k0,
                        long k1, long j0, long j1, long i0, long i1, const double *coeff_in) {
