@@ -17,11 +17,26 @@
 #define MARCH_CUBE_REGS 168
 #endif
 
+#ifndef MARCH_F32_CUBE_REGS /* float kernels: 145 / 158 registers as compiled (12 warps per SM); capped at 128 they have no spills and 16 warps: cube 0.441 -> 0.427 ms, 25-point 0.346 -> 0.342 ms, profiles/r03_fp32_kernels.log */
+#define MARCH_F32_CUBE_REGS 128
+#endif
+#ifndef MARCH_F32_STAR4_REGS
+#define MARCH_F32_STAR4_REGS 128
+#endif
+
+namespace dev {
+template <int R, bool CUBE, size_t EB>
+constexpr int reg_cap() {
+  if (EB == 8) return CUBE ? MARCH_CUBE_REGS : (R == 1 ? 128 : (R == 2 ? 168 : MARCH_STAR4_REGS));
+  return CUBE ? (R == 2 ? MARCH_F32_CUBE_REGS : 128) : (R == 4 ? MARCH_F32_STAR4_REGS : 128);
+}
+}  // namespace dev
+
 namespace {
 
 template <int R, bool CUBE, int VAR, int P, typename T>
 /* register cap for the cube: measured best on B200 (profiles/r01_maxnreg_sweep.txt) */
-__global__ void __launch_bounds__(32) __maxnreg__(CUBE ? MARCH_CUBE_REGS : (R == 1 ? 128 : (R == 2 ? 168 : MARCH_STAR4_REGS))) march_kernel(const __grid_constant__ MarchParams prm) {
+__global__ void __launch_bounds__(32) __maxnreg__((dev::reg_cap<R, CUBE, sizeof(T)>())) march_kernel(const __grid_constant__ MarchParams prm) {
   using L = dev::StageLayout<R, CUBE, P, T>;
   constexpr int H = 8 / P;
   extern __shared__ __align__(1024) char smem[];
