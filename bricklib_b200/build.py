@@ -13,7 +13,7 @@ LIBDIR = os.path.join(HERE, "lib")
 # product library (load it with BRICKS_LIB=...); the product build never sets these
 EXP = os.environ.get("BRICKS_EXP_NAME", "")
 LIB = os.path.join(LIBDIR, "libbricks_b200%s.so" % ("_" + EXP if EXP else ""))
-SOURCES = ["context.cu", "plan.cu", "stencil_march.cu", "stencil_naive.cu", "exchange.cu", "step.cu", "array_copy.cu", "probe.cu",
+SOURCES = ["context.cu", "plan.cu", "stencil_march.cu", "stencil_naive.cu", "stencil4d.cu", "exchange.cu", "step.cu", "array_copy.cu", "probe.cu",
            "host_capi.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

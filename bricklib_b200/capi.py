@@ -61,6 +61,10 @@ _SIGS = {
     "bricks_stencil_naive": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
     "bricks_stencil_f32": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
     "bricks_stencil_naive_f32": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_size_t, C.c_size_t, _vp, C.c_int]),
+    "bricks_plan4d_create": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint, _vpp]),
+    "bricks_plan4d_destroy": (C.c_int, [_vp]),
+    "bricks_stencil4d": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_size_t, C.c_uint, C.c_int]),
+    "bricks_stencil4d_naive": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_size_t, C.c_uint, C.c_int]),
     "bricks_launch_count": (C.c_int, [C.POINTER(C.c_ulonglong)]),
     "bricks_links_upload": (C.c_int, [_vp, _vp, C.c_int, _vpp]),
     "bricks_copy_regions": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
@@ -306,6 +310,37 @@ class Plan(object):
 
     def stencil_naive_f32(self, stencil, ins, outs, in_step=512, out_step=512, coeff=None, stream=STREAM_COMPUTE):
         self._run(lib().bricks_stencil_naive_f32, stencil, ins, outs, in_step, out_step, coeff, stream)
+
+
+class Plan4D(object):
+    """The 4-D path (weak/main-4d.cpp): grid + 81-slot adjacency of 4x4x4x4 bricks on the device
+    (bricks_plan4d_create); sweep() is one brick_stencil call of the reference."""
+
+    def __init__(self, ctx, grid, adj):
+        grid = np.ascontiguousarray(grid, np.uint32)
+        adj = np.ascontiguousarray(adj, np.uint32)
+        assert grid.ndim == 4 and adj.ndim == 2 and adj.shape[1] == 81
+        gd = np.array(grid.shape[::-1], np.uint32)
+        self.ctx, self.nbricks, self.gdims = ctx, adj.shape[0], tuple(int(x) for x in gd)
+        self._h = C.c_void_p()
+        check(lib().bricks_plan4d_create(ctx._h, _np_ptr(grid), _np_ptr(gd), _np_ptr(adj), adj.shape[0],
+                                         C.byref(self._h)))
+
+    def ncells(self, skip_bricks=0):
+        return int(np.prod([max(0, g - 2 * skip_bricks) for g in self.gdims]))
+
+    def sweep(self, in_dev, out_dev, skip_bricks=0, in_step=256, out_step=256, stream=STREAM_COMPUTE):
+        check(lib().bricks_stencil4d(self._h, C.c_void_p(in_dev), C.c_void_p(out_dev), in_step, out_step,
+                                     skip_bricks, stream))
+
+    def sweep_naive(self, in_dev, out_dev, skip_bricks=0, in_step=256, out_step=256, stream=STREAM_COMPUTE):
+        check(lib().bricks_stencil4d_naive(self._h, C.c_void_p(in_dev), C.c_void_p(out_dev), in_step, out_step,
+                                           skip_bricks, stream))
+
+    def close(self):
+        if self._h:
+            lib().bricks_plan4d_destroy(self._h)
+            self._h = C.c_void_p()
 
 
 class Exchange(object):
@@ -557,6 +592,13 @@ _SIGS.update({
     "bricks_zmort3_coord": (C.c_ulong, [C.c_ulong, C.c_ulong]),
     "bricks_zmort3_set": (C.c_ulong, [C.c_ulong, C.c_ulong, C.c_ulong]),
     "bricks_uniform_fill": (C.c_int, [_vp, C.c_size_t, C.c_uint64, C.c_uint64]),
+    "bricks_decomp4d_create": (C.c_int, [_vp, C.c_uint, C.c_int, _vpp]),
+    "bricks_decomp4d_destroy": (C.c_int, [_vp]),
+    "bricks_decomp4d_sizes": (C.c_int, [_vp, C.POINTER(C.c_uint), _vp, _vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "bricks_decomp4d_tables": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "bricks_decomp4d_rank_map": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "bricks_decomp4d_exchange_plan": (C.c_int, [_vp, C.c_size_t, _vp, _vp, _vp, _vp, _vp]),
+    "bricks_copy_brick4": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp, C.c_uint]),
 })
 
 
@@ -639,6 +681,70 @@ class Decomp(object):
             self.close()
         except Exception:
             pass
+
+
+class Decomp4D(object):
+    """BrickDecomp<4, 4,4,4,4>(dims, depth).initialize(allneighbors minus the centre) of
+    weak/main-4d.cpp:98-106 -- the product's own C++ template through bricks_decomp4d_*."""
+
+    def __init__(self, dims, depth=8, page_align=False):
+        L = lib()
+        d = np.asarray(dims, np.uint32)
+        assert len(d) == 4
+        self._h = C.c_void_p()
+        check(L.bricks_decomp4d_create(_np_ptr(d), depth, 1 if page_align else 0, C.byref(self._h)))
+        self.dims, self.depth = tuple(int(x) for x in dims), depth
+        nb, nr, ns = C.c_uint(), C.c_int(), C.c_int()
+        self.sep_pos = np.zeros(3, np.uint32)
+        gd = np.zeros(4, np.uint32)
+        check(L.bricks_decomp4d_sizes(self._h, C.byref(nb), _np_ptr(self.sep_pos), _np_ptr(gd), C.byref(nr),
+                                      C.byref(ns)))
+        self.nbricks, self.nregions = nb.value, nr.value
+        self.gdims = tuple(int(x) for x in gd)  # contiguous axis first
+        self.grid = np.zeros(self.gdims[::-1], np.uint32)
+        self.adj = np.zeros((self.nbricks, 81), np.uint32)
+        self.ghost = np.zeros(nr.value, REGION_DT)
+        self.skin = np.zeros(nr.value, REGION_DT)
+        self.skin_size = np.zeros(ns.value, np.int64)
+        check(L.bricks_decomp4d_tables(self._h, _np_ptr(self.grid), _np_ptr(self.adj), _np_ptr(self.ghost),
+                                       _np_ptr(self.skin), _np_ptr(self.skin_size)))
+
+    def rank_map(self, procdims, coo):
+        keys, ranks = np.zeros(81, np.uint64), np.zeros(81, np.int32)
+        pd, cc = np.asarray(procdims, np.int32), np.asarray(coo, np.int32)
+        check(lib().bricks_decomp4d_rank_map(self._h, _np_ptr(pd), _np_ptr(cc), _np_ptr(keys), _np_ptr(ranks)))
+        return {int(k): int(r) for k, r in zip(keys, ranks)}
+
+    def exchange_plan(self, step=256):
+        """(recv_off, send_off, nbytes, recv_peer, send_peer): the arguments of an Exchange, for the rank
+        map set by the last rank_map() call"""
+        n = self.nregions
+        ro, so, nb = (np.zeros(n, np.uint64) for _ in range(3))
+        rp, sp = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        check(lib().bricks_decomp4d_exchange_plan(self._h, step, _np_ptr(ro), _np_ptr(so), _np_ptr(nb),
+                                                  _np_ptr(rp), _np_ptr(sp)))
+        return ro, so, nb, rp, sp
+
+    def close(self):
+        if self._h:
+            lib().bricks_decomp4d_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def copy_brick4(to_brick, dimlist, padding, ghost, arr, grid, bdat, adj, step=256):
+    """copyToBrick<4> / copyFromBrick<4> between a padded 4-D array and row-major 4x4x4x4 bricks."""
+    d, p, g = (np.asarray(x, np.int64) for x in (dimlist, padding, ghost))
+    grid = np.ascontiguousarray(grid, np.uint32)
+    adj = np.ascontiguousarray(adj, np.uint32)
+    assert arr.flags["C_CONTIGUOUS"] and bdat.flags["C_CONTIGUOUS"]
+    check(lib().bricks_copy_brick4(1 if to_brick else 0, _np_ptr(d), _np_ptr(p), _np_ptr(g), _np_ptr(arr),
+                                   _np_ptr(grid), _np_ptr(bdat), step, _np_ptr(adj), adj.shape[0]))
 
 
 def init_grid(dimlist):

@@ -18,9 +18,15 @@ void set_error(const char *fmt, ...);
 
 typedef BrickDecomp<3, 8, 8, 8> Decomp3;
 typedef Brick<Dim<8, 8, 8>, Dim<8>> Brick3;
+typedef BrickDecomp<4, 4, 4, 4, 4> Decomp4;
+typedef Brick<Dim<4, 4, 4, 4>, Dim<4>> Brick4; /* fold <4> = row-major [l][k][j][i] */
+static_assert(Brick4::row_major(), "4-D bricks of the C ABI are row-major");
 
 struct bricks_decomp {
   Decomp3 *dec;
+};
+struct bricks_decomp4d {
+  Decomp4 *dec;
 };
 struct bricks_strong_plan {
   StrongPlan *plan;
@@ -39,7 +45,8 @@ int guarded(F f) {
   }
 }
 
-void flatten(const std::vector<Decomp3::g_region> &v, bricks_region *out) {
+template <typename Region>
+void flatten(const std::vector<Region> &v, bricks_region *out) {
   for (size_t i = 0; i < v.size(); ++i) {
     out[i].neighbor = v[i].neighbor.set;
     out[i].skin_st = v[i].skin_st;
@@ -212,6 +219,134 @@ int bricks_decomp_step_create(bricks_decomp *d, bricks_ctx *ctx, int rank, int n
     std::string text;
     *out = D.makeStep((Decomp3::StepExchange)exchange_kind, step, &text);
     if (what && what_len) snprintf(what, what_len, "%s", text.c_str());
+  });
+}
+
+int bricks_decomp4d_create(const unsigned dims[4], unsigned depth, int page_align, bricks_decomp4d **out) {
+  if (!dims || !out || !depth || depth % 4) {
+    bricks::set_error("bricks_decomp4d_create: bad argument (extents and depth must be multiples of 4)");
+    return -1;
+  }
+  for (int a = 0; a < 4; ++a)
+    if (dims[a] % 4 || dims[a] < 2 * depth) {
+      bricks::set_error("bricks_decomp4d_create: extent %u is not a multiple of 4 or smaller than two ghost depths",
+                        dims[a]);
+      return -1;
+    }
+  return guarded([&] {
+    std::unique_ptr<Decomp4> d(new Decomp4({dims[0], dims[1], dims[2], dims[3]}, depth));
+    d->page_align = page_align != 0;
+    std::vector<BitSet> skin; /* weak/main-4d.cpp:103-106 */
+    allneighbors(0, 1, 4, skin);
+    skin.erase(skin.begin() + (skin.size() / 2));
+    d->initialize(skin);
+    *out = new bricks_decomp4d{d.release()};
+  });
+}
+
+int bricks_decomp4d_destroy(bricks_decomp4d *d) {
+  if (d) {
+    delete d->dec;
+    delete d;
+  }
+  return 0;
+}
+
+int bricks_decomp4d_sizes(const bricks_decomp4d *d, unsigned *nbricks, unsigned sep_pos[3], unsigned gdims[4],
+                          int *nregions, int *nskin) {
+  if (!d) return -1;
+  if (nbricks) *nbricks = d->dec->sep_pos[2];
+  for (int a = 0; a < 3; ++a)
+    if (sep_pos) sep_pos[a] = d->dec->sep_pos[a];
+  for (int a = 0; a < 4; ++a)
+    if (gdims) gdims[a] = d->dec->gridDim(a);
+  if (nregions) *nregions = (int)d->dec->ghost.size();
+  if (nskin) *nskin = (int)d->dec->skinlist.size();
+  return 0;
+}
+
+int bricks_decomp4d_tables(const bricks_decomp4d *d, unsigned *grid, unsigned *adj, bricks_region *ghost,
+                           bricks_region *skin, long *skin_size) {
+  if (!d) return -1;
+  Decomp4 &D = *d->dec;
+  const size_t cells = (size_t)D.gridDim(0) * D.gridDim(1) * D.gridDim(2) * D.gridDim(3);
+  if (grid) memcpy(grid, D.gridData(), cells * sizeof(unsigned));
+  if (adj) memcpy(adj, D.getBrickInfo().adj, (size_t)D.sep_pos[2] * 81 * sizeof(unsigned));
+  if (ghost) flatten(D.ghost, ghost);
+  if (skin) flatten(D.skin, skin);
+  if (skin_size)
+    for (size_t i = 0; i < D.skin_size.size(); ++i) skin_size[i] = D.skin_size[i];
+  return 0;
+}
+
+int bricks_decomp4d_rank_map(bricks_decomp4d *d, const int procdims[4], const int coo_in[4], uint64_t keys[81],
+                             int ranks[81]) {
+  if (!d || !procdims || !coo_in) return -1;
+  BricksComm c;
+  c.ndims = 4;
+  c.size = 1;
+  for (int a = 0; a < 4; ++a) {
+    if (procdims[a] < 1) return -1;
+    c.dims[a] = procdims[a];
+    c.size *= procdims[a];
+  }
+  int coo[4] = {coo_in[0], coo_in[1], coo_in[2], coo_in[3]};
+  c.rank = cart_rank(c, coo);
+  c.ctx = d->dec->comm.ctx;
+  d->dec->comm = c;
+  d->dec->rank_map.clear();
+  populate(c, *d->dec, 0, 1, coo);
+  if (keys && ranks) {
+    std::vector<BitSet> nb;
+    allneighbors(0, 1, 4, nb);
+    for (size_t i = 0; i < nb.size(); ++i) {
+      keys[i] = nb[i].set;
+      ranks[i] = d->dec->rank_map[nb[i].set];
+    }
+  }
+  return 0;
+}
+
+int bricks_decomp4d_exchange_plan(bricks_decomp4d *d, size_t step, size_t *recv_off, size_t *send_off, size_t *nbytes,
+                                  int *recv_peer, int *send_peer) {
+  if (!d || !recv_off || !send_off || !nbytes || !recv_peer || !send_peer) return -1;
+  Decomp4 &D = *d->dec;
+  if (D.rank_map.empty()) {
+    bricks::set_error("bricks_decomp4d_exchange_plan: call bricks_decomp4d_rank_map first");
+    return -1;
+  }
+  const size_t sb = step * sizeof(double);
+  for (size_t i = 0; i < D.ghost.size(); ++i) {
+    const auto &g = D.ghost[i];
+    const auto &s = D.skin[i];
+    recv_off[i] = (size_t)(g.pos + g.first_pad) * sb;
+    send_off[i] = (size_t)(s.pos + s.first_pad) * sb;
+    nbytes[i] = (size_t)(g.len - g.first_pad - g.last_pad) * sb;
+    recv_peer[i] = D.rank_map[g.neighbor.set];
+    send_peer[i] = D.rank_map[s.neighbor.set];
+  }
+  return 0;
+}
+
+int bricks_copy_brick4(int to_brick, const long dimlist[4], const long padding[4], const long ghost[4], double *arr,
+                       const unsigned *grid, double *brick_dat, size_t step, const unsigned *adj, unsigned nbricks) {
+  if (!dimlist || !padding || !ghost || !arr || !grid || !brick_dat || !adj) return -1;
+  return guarded([&] {
+    BrickInfo<4> info(1);
+    void *own = info.adj;
+    info.adj = (BrickInfo<4>::adjlist) const_cast<unsigned *>(adj);
+    info.nbricks = nbricks;
+    BrickStorage st;
+    st.dat = std::shared_ptr<bElem>(brick_dat, [](bElem *) {});
+    st.chunks = nbricks;
+    st.step = step;
+    Brick4 b(&info, st, 0);
+    std::vector<long> dl(dimlist, dimlist + 4), pd(padding, padding + 4), gh(ghost, ghost + 4);
+    if (to_brick)
+      copyToBrick<4>(dl, pd, gh, arr, const_cast<unsigned *>(grid), b);
+    else
+      copyFromBrick<4>(dl, pd, gh, arr, const_cast<unsigned *>(grid), b);
+    free(own);
   });
 }
 

@@ -220,6 +220,14 @@ class BrickDecomp {
 
   BricksComm comm;
   std::unordered_map<uint64_t, int> rank_map;  ///< direction set -> rank
+  /// Region starts rounded up to whole pages (the reference's default build) or dense numbering
+  /// (its -DDECOMP_PAGEUNALIGN build, which the CUDA drivers use: weak/CMakeLists.txt:32).  The two
+  /// differ only for bricks smaller than a page (4x4x4x4 fp64 = 2 KiB).  Set before initialize().
+#ifdef DECOMP_PAGEUNALIGN
+  bool page_align = false;
+#else
+  bool page_align = true;
+#endif
 
   /// dims: interior extent in elements, contiguous axis first; depth: ghost depth in elements
   BrickDecomp(const std::vector<unsigned> &dims, const unsigned depth, unsigned numfield = 1)
@@ -262,15 +270,11 @@ class BrickDecomp {
     const long bsize = (long)cal_size<BDims...>::value * (long)sizeof(bElem) * numfield;
     if (std::max(bsize, pagesize) % std::min(bsize, pagesize) != 0)
       throw std::runtime_error("brick size must be a factor/multiple of pagesize.");
-#ifdef DECOMP_PAGEUNALIGN
-    const long factor = 1;  // numbering is dense; brick 0 is still reserved as the sentinel
-    (void)pagesize;
-    (void)bsize;
-    unsigned pos = (unsigned)(bsize < pagesize ? pagesize / bsize : 1);
-#else
-    const long factor = bsize < pagesize ? pagesize / bsize : 1;
-    unsigned pos = (unsigned)factor;
-#endif
+    // bricks smaller than a page: the first pagesize / bsize storage slots are reserved (slot 0 is
+    // the sentinel) and, in the page-aligned numbering, every region starts on a page boundary
+    const long reserved = bsize < pagesize ? pagesize / bsize : 1;
+    const long factor = page_align ? reserved : 1;
+    unsigned pos = (unsigned)reserved;
     auto round_up = [factor](unsigned p) { return (unsigned)((p + factor - 1) / factor * factor); };
     auto pad_of = [factor, this](BitSet region) -> unsigned {
       return (unsigned)(factor - (region_bricks(region) + factor - 1) % factor - 1);
@@ -345,7 +349,8 @@ class BrickDecomp {
     sep_pos[2] = pos;
 
     if (bInfo == nullptr) bInfo = new BrickInfo<dim>(pos);
-    memset(bInfo->adj[0], 0, sizeof(unsigned) * NSLOT);  // the sentinel brick has no neighbours
+    // rows of the sentinel brick and of padding slots stay zero: they have no neighbours
+    memset(bInfo->adj[0], 0, sizeof(unsigned) * NSLOT * (size_t)pos);
     for (unsigned c = 0; c < cells; ++c) fill_adjacency(c, bInfo->adj[grid[c]]);
     for (auto &kv : plans) bricks_exchange_destroy(kv.second);
     plans.clear();

@@ -49,6 +49,22 @@ BrickInfo<dims> init_grid(unsigned *&grid_ptr, const std::vector<long> &dimlist)
   return info;
 }
 
+namespace bricks_detail {
+/// brick[b][x_{n-1}]..[x_0] for a coordinate list given contiguous axis first
+template <typename B>
+inline bElem &brick_element(B &brick, unsigned b, const long *x) {
+  static_assert(B::NDIMS >= 1 && B::NDIMS <= 4, "brick_element: 1 to 4 axes");
+  if constexpr (B::NDIMS == 1)
+    return brick[b][(unsigned)x[0]];
+  else if constexpr (B::NDIMS == 2)
+    return brick[b][(unsigned)x[1]][(unsigned)x[0]];
+  else if constexpr (B::NDIMS == 3)
+    return brick[b][(unsigned)x[2]][(unsigned)x[1]][(unsigned)x[0]];
+  else
+    return brick[b][(unsigned)x[3]][(unsigned)x[2]][(unsigned)x[1]][(unsigned)x[0]];
+}
+}  // namespace bricks_detail
+
 /// Visit every element of the bricks covering the region `dimlist` (+ `ghost` on each side)
 /// of an array that carries `padding + ghost` extra elements on each side, calling
 /// f(brick_element_ref, array_element_ptr).  grid_ptr is the brick-index grid over
@@ -58,33 +74,42 @@ template <unsigned dims, typename F, typename T, unsigned... BDims>
 inline void iter_grid(const std::vector<long> &dimlist, const std::vector<long> &padding,
                       const std::vector<long> &ghost, bElem *arr, unsigned *grid_ptr,
                       Brick<Dim<BDims...>, T> &brick, F f) {
-  static_assert(dims == 3, "iter_grid: this build implements the 3-D case");
+  static_assert(dims == sizeof...(BDims), "iter_grid: one brick axis per array axis");
   std::vector<long> tile = {BDims...};
   std::reverse(tile.begin(), tile.end());  // contiguous axis first
-  long strideA[3], strideB[3], sA = 1, sB = 1;
-  for (unsigned a = 0; a < 3; ++a) {
+  long strideA[dims], strideB[dims], lo[dims], cnt[dims], sA = 1, sB = 1, nbricks = 1, nelem = 1;
+  for (unsigned a = 0; a < dims; ++a) {
     strideA[a] = sA;
     strideB[a] = sB;
     sA *= dimlist[a] + 2 * (padding[a] + ghost[a]);
     sB *= (dimlist[a] + 2 * ghost[a]) / tile[a];
-  }
-  long lo[3], hi[3];
-  for (unsigned a = 0; a < 3; ++a) {
     lo[a] = ghost[a] / tile[a];
-    hi[a] = (dimlist[a] + ghost[a]) / tile[a];
+    cnt[a] = (dimlist[a] + ghost[a]) / tile[a] - lo[a];
+    nbricks *= cnt[a];
+    nelem *= tile[a];
   }
+  // one flat loop over the visited bricks, a flat loop over the elements of each
 #pragma omp parallel for
-  for (long bk = lo[2]; bk < hi[2]; ++bk)
-    for (long bj = lo[1]; bj < hi[1]; ++bj)
-      for (long bi = lo[0]; bi < hi[0]; ++bi) {
-        const unsigned b = grid_ptr[bi * strideB[0] + bj * strideB[1] + bk * strideB[2]];
-        bElem *base = arr + (padding[0] + bi * tile[0]) * strideA[0] + (padding[1] + bj * tile[1]) * strideA[1] +
-                      (padding[2] + bk * tile[2]) * strideA[2];
-        for (long k = 0; k < tile[2]; ++k)
-          for (long j = 0; j < tile[1]; ++j)
-            for (long i = 0; i < tile[0]; ++i)
-              f(brick[b][(unsigned)k][(unsigned)j][(unsigned)i], base + i * strideA[0] + j * strideA[1] + k * strideA[2]);
+  for (long n = 0; n < nbricks; ++n) {
+    long rem = n, cell = 0;
+    bElem *base = arr;
+    for (unsigned a = 0; a < dims; ++a) {
+      const long c = lo[a] + rem % cnt[a];
+      rem /= cnt[a];
+      cell += c * strideB[a];
+      base += (padding[a] + c * tile[a]) * strideA[a];
+    }
+    const unsigned b = grid_ptr[cell];
+    for (long e = 0; e < nelem; ++e) {
+      long x[dims], r = e, off = 0;
+      for (unsigned a = 0; a < dims; ++a) {
+        x[a] = r % tile[a];
+        r /= tile[a];
+        off += x[a] * strideA[a];
       }
+      f(bricks_detail::brick_element(brick, b, x), base + off);
+    }
+  }
 }
 
 template <unsigned dims, typename T>

@@ -133,6 +133,29 @@ int bricks_stencil_f32(bricks_plan *plan, int stencil_id, int nfields, const flo
 int bricks_stencil_naive_f32(bricks_plan *plan, int stencil_id, int nfields, const float *const *in,
                              float *const *out, size_t in_step, size_t out_step,
                              const double *coeff_host, int stream);
+/* ---- the 4-D path: the 9-point star of stencils/mpi9pt.py on 4x4x4x4 fp64 bricks, the stencil of the
+ * reference's CPU-only driver weak/main-4d.cpp.  A brick is 256 doubles = 2 KiB, row-major [l][k][j][i];
+ * element (b,l,k,j,i) lives at dat[b*step + ((l*4 + k)*4 + j)*4 + i]; adj has 81 slots per brick,
+ * slot ((dl*3 + dk)*3 + dj)*3 + di with digit 1 = the brick itself (include/brick.h:229-246).
+ * bricks_plan4d_create replaces the host grid / BrickInfo pair of weak/main-4d.cpp:112-124: `grid_host`
+ * is the brick-index grid [gdims[3]][gdims[2]][gdims[1]][gdims[0]] (contiguous axis first in gdims),
+ * `adj_host` the adjacency list (nbricks x 81); both are copied to the device.  Rejected: a grid cell or
+ * an adjacency entry of a grid brick outside [0, nbricks), and adj[b][40] != b. */
+typedef struct bricks_plan4d bricks_plan4d;
+int bricks_plan4d_create(bricks_ctx *ctx, const unsigned *grid_host, const unsigned gdims[4],
+                         const unsigned *adj_host, unsigned nbricks, bricks_plan4d **plan);
+int bricks_plan4d_destroy(bricks_plan4d *plan);
+/* One sweep of brick_stencil (weak/main-4d.cpp:62-75): out = stencil(in) for every brick of the grid that
+ * is at least `skip_bricks` cells inside it on every side (the reference passes skip / TILE); bricks
+ * outside that box are not written.  Centre bricks come from the grid, every neighbour through adj.  in /
+ * out: DEVICE storages, 32-byte aligned, distinct; steps in elements, multiples of 4.  Asynchronous on
+ * `stream`. */
+int bricks_stencil4d(bricks_plan4d *plan, const double *in, double *out, size_t in_step, size_t out_step,
+                     unsigned skip_bricks, int stream);
+/* verification twin (one thread per point through the accessor arithmetic); never on the product path */
+int bricks_stencil4d_naive(bricks_plan4d *plan, const double *in, double *out, size_t in_step, size_t out_step,
+                           unsigned skip_bricks, int stream);
+
 /* number of kernels launched by this library so far in this process */
 int bricks_launch_count(unsigned long long *count);
 

@@ -77,6 +77,27 @@ int bricks_copy_brick3(int to_brick, const long dimlist[3], const long padding[3
 int bricks_compare_brick3(const long dimlist[3], const long padding[3], const long ghost[3], double *arr,
                           const unsigned *grid, double *brick_dat, size_t step, const unsigned *adj,
                           unsigned nbricks, int *match, double *max_rel);
+/* ---- the 4-D decomposition of weak/main-4d.cpp:98-124: BrickDecomp<4, 4,4,4,4>(dims, depth)
+ * .initialize(allneighbors minus the centre).  page_align != 0 gives the numbering of the reference's
+ * default build (4x4x4x4 fp64 bricks are half a page: two reserved slots, every region padded to whole
+ * pages), 0 the dense numbering of -DDECOMP_PAGEUNALIGN (what its CUDA drivers use).  Tables as for the
+ * 3-D calls above with 4 axes and 81 adjacency slots / direction sets. */
+typedef struct bricks_decomp4d bricks_decomp4d;
+int bricks_decomp4d_create(const unsigned dims[4], unsigned depth, int page_align, bricks_decomp4d **out);
+int bricks_decomp4d_destroy(bricks_decomp4d *d);
+int bricks_decomp4d_sizes(const bricks_decomp4d *d, unsigned *nbricks, unsigned sep_pos[3], unsigned gdims[4],
+                          int *nregions, int *nskin);
+int bricks_decomp4d_tables(const bricks_decomp4d *d, unsigned *grid, unsigned *adj, bricks_region *ghost,
+                           bricks_region *skin, long *skin_size);
+int bricks_decomp4d_rank_map(bricks_decomp4d *d, const int procdims[4], const int coo[4], uint64_t keys[81],
+                             int ranks[81]);
+int bricks_decomp4d_exchange_plan(bricks_decomp4d *d, size_t step, size_t *recv_off, size_t *send_off,
+                                  size_t *nbytes, int *recv_peer, int *send_peer);
+/* copyToBrick<4> (to_brick != 0) / copyFromBrick<4> (bricksetup.h:172-221) on row-major 4x4x4x4 bricks */
+int bricks_copy_brick4(int to_brick, const long dimlist[4], const long padding[4], const long ghost[4],
+                       double *arr, const unsigned *grid, double *brick_dat, size_t step, const unsigned *adj,
+                       unsigned nbricks);
+
 /* ---- strong scaling: two-level decomposition (strong/args.cpp:36-56,104-113; strong/main.cu:188-395).
  * A dom^3 domain in (dom/sdom)^3 subdomains named by Z-Morton id; rank r owns a contiguous id
  * range; all subdomains share the BrickDecomp `d` (built for sdom^3).  Offsets are bytes inside

@@ -6,6 +6,7 @@ brick kernels of stencils/*.py and the ST_CPU array forms of stencils/fake.h).  
 the build container, where /root/reference exists:
 
     make -C oracle all && python oracle/gen_golden.py && python oracle/gen_golden.py cond
+    python oracle/gen_golden.py d4        # the 4-D path
 
 The fixtures pin the oracle (tests/test_oracle_golden.py) and, through it, the CUDA path.
 Inputs are not stored: they are a pure function of the element index
@@ -149,8 +150,62 @@ def d3pt27_fixture():
     return fx
 
 
+D4_DECOMP = [((16, 16, 16, 16), 8), ((20, 20, 20, 20), 8), ((24, 16, 32, 20), 8), ((12, 20, 12, 16), 4),
+             ((28, 20, 12, 36), 4)]
+D4_RANK_CASES = [((1, 1, 1, 1), (0, 0, 0, 0)), ((2, 1, 1, 1), (1, 0, 0, 0)), ((2, 2, 2, 1), (0, 1, 1, 0)),
+                 ((2, 2, 2, 2), (1, 0, 1, 1)), ((3, 2, 1, 2), (2, 1, 0, 1))]
+D4_STENCIL_DIMS = [(16, 16, 16, 16), (16, 24, 16, 20)]
+
+
+def d4_fixtures():
+    """The 4-D path of weak/main-4d.cpp from oracle/_ref/libref4d*.so: BrickDecomp<4,4,4,4,4> tables in
+    both numberings (page-aligned, -DDECOMP_PAGEUNALIGN) and the generated mpi9pt.py kernel."""
+    from oracle import oracle4d as D
+    recs = []
+    for dims, gz in D4_DECOMP:
+        for pa in (True, False):
+            ref = D.Ref4D(dims, gz=gz, page_align=pa)
+            rec = {"dims": list(dims), "gz": gz, "page_align": pa, "nbricks": int(ref.nbricks),
+                   "sep_pos": [int(x) for x in ref.sep_pos], "skin_size": [int(x) for x in ref.skin_size],
+                   "adj_fnv": fnv1a64(ref.adj), "grid_fnv": fnv1a64(ref.grid)}
+            for name in ("ghost", "skin"):
+                rec[name] = {k: [int(x) for x in v] for k, v in ref.regions[name].items()}
+            if pa and gz == 8 and dims == D4_DECOMP[0][0]:
+                rec["rank_map"] = [{"procdims": list(pd), "coo": list(coo),
+                                    "map": {"%x" % k: v for k, v in sorted(ref.rank_map(pd, coo).items())}}
+                                   for pd, coo in D4_RANK_CASES]
+            ref.close()
+            recs.append(rec)
+    with open(os.path.join(GOLDEN, "decomp4d.json"), "w") as f:
+        json.dump({"generator": "oracle/gen_golden.py d4", "source": "oracle/_ref/libref4d.so, libref4d_unalign.so",
+                   "decomp": recs}, f, indent=0, separators=(",", ":"))
+    for dims in D4_STENCIL_DIMS:
+        ref = D.Ref4D(dims, page_align=False)
+        nb = ref.nbricks
+        inp = synth.uniform(nb * 256, seed=17)
+        out = {"dims": np.array(dims)}
+        for s in (0, 1, 2):  # the three sweep regions of one exchange period (skip // TILE)
+            blist = D.sweep_list(ref.grid, s)
+            res = np.zeros(nb * 256)
+            D.ref_brick_sweep(ref.adj, blist, inp, res)
+            pick = blist[::max(1, len(blist) // 64)]  # a sample keeps the fixture small
+            out["n_%d" % s] = np.array([len(blist)])
+            out["bricks_%d" % s] = pick
+            out["brick_%d" % s] = res.reshape(nb, 256)[pick].copy()
+            untouched = np.setdiff1d(np.arange(nb), blist)
+            assert not res.reshape(nb, 256)[untouched].any()  # nothing outside the list is written
+        ref.close()
+        np.savez_compressed(os.path.join(GOLDEN, "d4pt9_%dx%dx%dx%d.npz" % dims), **out)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    if "d4" in sys.argv[1:]:  # the 4-D path (weak/main-4d.cpp)
+        d4_fixtures()
+        for fn in sorted(os.listdir(GOLDEN)):
+            if "4d" in fn or "d4" in fn:
+                print(fn, os.path.getsize(os.path.join(GOLDEN, fn)))
+        return
     if "d3pt27" in sys.argv[1:]:  # the 27-point block (one ~20 s run of the reference's d3pt27())
         np.savez(os.path.join(GOLDEN, "d3pt27_block.npz"), **d3pt27_fixture())
         print("d3pt27_block.npz", os.path.getsize(os.path.join(GOLDEN, "d3pt27_block.npz")))
