@@ -86,6 +86,47 @@ inline void fill_ghost(double *mine, const std::vector<double *> &all, const lon
   }
 }
 
+/// The 4-D twin (weak/main-4d.cpp:171-193 array_stencil with exchangeArr<4>): out = 0.2 * in + 0.1 * (the
+/// eight axis neighbours) on [lo, hi)^4 of an array with `ext` elements per axis (i fastest)
+inline void sweep4d(const double *in, double *out, const long ext[4], const long lo[4], const long hi[4]) {
+  const long s1 = ext[0], s2 = s1 * ext[1], s3 = s2 * ext[2];
+#pragma omp parallel for collapse(2)
+  for (long l = lo[3]; l < hi[3]; ++l)
+    for (long k = lo[2]; k < hi[2]; ++k)
+      for (long j = lo[1]; j < hi[1]; ++j)
+        for (long i = lo[0]; i < hi[0]; ++i) {
+          const long p = l * s3 + k * s2 + j * s1 + i;
+          out[p] = 0.2 * in[p] + 0.1 * (in[p + 1] + in[p - 1] + in[p + s1] + in[p - s1] + in[p + s2] + in[p - s2] +
+                                        in[p + s3] + in[p - s3]);
+        }
+}
+
+/// fill_ghost for four axes; owner(sl, sk, sj, si)
+template <typename OwnerFn>
+inline void fill_ghost4d(double *mine, const std::vector<double *> &all, const long dom[4], long gz, OwnerFn owner) {
+  const long ext[4] = {dom[0] + 2 * gz, dom[1] + 2 * gz, dom[2] + 2 * gz, dom[3] + 2 * gz};
+  const long s1 = ext[0], s2 = s1 * ext[1], s3 = s2 * ext[2];
+  auto side = [&](long x, int a) { return x < gz ? -1 : (x >= gz + dom[a] ? 1 : 0); };
+#pragma omp parallel for collapse(2)
+  for (long l = 0; l < ext[3]; ++l)
+    for (long k = 0; k < ext[2]; ++k) {
+      const int sl = side(l, 3), sk = side(k, 2);
+      for (long j = 0; j < ext[1]; ++j) {
+        const int sj = side(j, 1);
+        for (long i = 0; i < ext[0]; ++i) {
+          const int si = side(i, 0);
+          if (!sl && !sk && !sj && !si) {
+            i = gz + dom[0] - 1;  // skip the interior of this row
+            continue;
+          }
+          const double *src = all[owner(sl, sk, sj, si)];
+          mine[l * s3 + k * s2 + j * s1 + i] =
+              src[(l - sl * dom[3]) * s3 + (k - sk * dom[2]) * s2 + (j - sj * dom[1]) * s1 + (i - si * dom[0])];
+        }
+      }
+    }
+}
+
 }  // namespace twin
 
 #endif  // BRICKS_B200_DRIVERS_HOST_TWIN_H

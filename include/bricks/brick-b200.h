@@ -182,4 +182,31 @@ class BrickStencilPlan {
   bricks_plan *plan_ = nullptr;
 };
 
+/// The 4-D path: the device side of brick_stencil(out, in, grid_ptr, skip) of weak/main-4d.cpp:62-75 for
+/// Brick<Dim<4,4,4,4>, Dim<4>> views (row-major bricks) on DEVICE storages.  Owns the device copies of
+/// the grid and the 81-slot adjacency list.
+class BrickStencilPlan4D {
+ public:
+  BrickStencilPlan4D(bricks_ctx *ctx, const unsigned *grid, const unsigned gdims[4], const unsigned *adj,
+                     unsigned nbricks) {
+    gpuCheck(bricks_plan4d_create(ctx, grid, gdims, adj, nbricks, &plan_));
+  }
+  BrickStencilPlan4D(const BrickStencilPlan4D &) = delete;
+  BrickStencilPlan4D &operator=(const BrickStencilPlan4D &) = delete;
+  ~BrickStencilPlan4D() { bricks_plan4d_destroy(plan_); }
+
+  /// out = mpi9pt(in) on every brick at least skip / 4 cells inside the grid (asynchronous); `skip` in
+  /// elements, as the reference passes it
+  template <typename B>
+  void run(B &out, B &in, long skip, int stream = BRICKS_STREAM_COMPUTE) {
+    static_assert(B::NDIMS == 4 && B::BRICKSIZE == 256 && B::row_major(), "4x4x4x4 row-major bricks");
+    static_assert(sizeof(bElem) == 8, "the 4-D kernels are fp64");
+    gpuCheck(bricks_stencil4d(plan_, in.dat, out.dat, in.step, out.step, (unsigned)(skip / 4), stream));
+  }
+  bricks_plan4d *handle() { return plan_; }
+
+ private:
+  bricks_plan4d *plan_ = nullptr;
+};
+
 #endif  // BRICKS_B200_BRICK_B200_H

@@ -226,6 +226,22 @@ def test_emulated_line_kernel_on_a_grid_that_is_not_a_lattice(built, o4, emul):
     dec.close()
 
 
+@pytest.mark.parametrize("flag", ["", "-a"])
+def test_driver_validation_pipeline_with_emulated_kernels(built, flag):
+    """tests/emul/weak4d_host_check.cpp: everything drivers/weak4d.cpp -v does on the host (decomposition,
+    brick fill, the array twin of drivers/host_twin.h, compareBrick<4>) with the device calls replaced by the
+    emulated kernel bodies and the one-rank periodic exchange by skin -> ghost copies"""
+    out = os.path.join(ROOT, "tests", "emul", "_build")
+    os.makedirs(out, exist_ok=True)
+    exe = os.path.join(out, "weak4d_host_check")
+    src = os.path.join(ROOT, "tests", "emul", "weak4d_host_check.cpp")
+    libdir = os.path.join(ROOT, "bricklib_b200", "lib")
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fopenmp", "-I" + os.path.join(ROOT, "include"), src, "-o", exe,
+                           "-L" + libdir, "-lbricks_b200", "-Wl,-rpath," + libdir])
+    r = subprocess.run([exe] + ([flag] if flag else []), capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "match 1" in r.stdout, r.stdout + r.stderr
+
+
 # ---------------------------------------------------------------- the kernels on a B200 ----
 def _worker(what, *args, timeout=300):
     cmd = [sys.executable, os.path.join(ROOT, "tests", "gpu4d_worker.py"), what] + [str(a) for a in args]
