@@ -583,6 +583,10 @@ def run_gpu(args, which):
         except Exception as e:  # noqa: BLE001 -- the extra block must not take the headline line down
             strong = {"error": repr(e)}
 
+    d4 = None
+    if world == 1 and not args.no_4d:
+        d4 = d4pt9_block(peak)
+
     line = None
     if rank == 0:
         line = {"metric": "fp64 GStencil/s", "value": value, "unit": "GStencil/s", "n_gpus": world,
@@ -597,6 +601,8 @@ def run_gpu(args, which):
             line["kernels"] = kernels
         if strong is not None:
             line["strong"] = strong
+        if d4 is not None:
+            line["d4pt9"] = d4
         if world == 1 and not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_reference_rate(which, budget_s=args.cpu_seconds)
@@ -833,6 +839,34 @@ def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
                     "download n-1 overlap the sweeps of n)"}
 
 
+def d4pt9_block(peak, dom=64, iters=10):
+    """The 4-D path (weak/main-4d.cpp): drivers/weak4d -s 64 -v in a process of its own
+    (plain C++ above the C ABI, no Python): one 64^4 subdomain (+ ghost: 20^4 bricks of 4x4x4x4, 328 MB per
+    field), validated against the host array twin, then exchange + 8 shrinking sweeps timed with CUDA events.
+    An extra block: a failure here is reported, it does not take the headline line down."""
+    import re
+    import subprocess
+    exe = os.path.join(ROOT, "drivers", "_build", "weak4d")
+    try:
+        r = subprocess.run([exe, "-s", str(dom), "-I", str(iters), "-v"], capture_output=True, text=True, timeout=180)
+        out = r.stdout
+        m_full = re.search(r"full-grid sweep \(ms\): ([0-9.e+-]+); HBM \(GB/s per GPU, 16 B per point\): ([0-9.e+-]+)", out)
+        m_perf = re.search(r"perf ([0-9.e+-]+) GStencil/s", out)
+        m_par = re.search(r"(result match|result mismatch): max relative error vs the host array twin ([0-9.e+-]+)", out)
+        if r.returncode != 0 or not (m_full and m_perf and m_par):
+            return {"error": "drivers/weak4d rc %d" % r.returncode, "tail": (out + r.stderr)[-400:]}
+        gbs = float(m_full.group(2))
+        return {"workload": "d4pt9: %d^4 subdomain per GPU, 4x4x4x4 bricks, ghost depth 8, 9-point star, exchange + 8 "
+                            "sweeps over shrinking regions (weak/main-4d.cpp)" % dom,
+                "parity": {"ok": m_par.group(1) == "result match", "max_relerr_vs_host_array_twin": float(m_par.group(2)),
+                           "bar": 1e-12},
+                "gstencil_per_s": float(m_perf.group(1)), "full_grid_sweep_ms": float(m_full.group(1)),
+                "achieved_gbs": gbs, "frac_of_measured_peak": gbs / peak if peak else None,
+                "algorithmic_bytes_per_point": 16, "kernel": "line_kernel (bricklib_b200/csrc/stencil4d.cu)"}
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)}
+
+
 def all_stencils(ctx, sub, peak):
     """Kernel-only numbers for every stencil of the path on the same 66^3-brick grid."""
     out = {}
@@ -884,6 +918,7 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the parity block in front of the timed loop")
     ap.add_argument("--no-all-stencils", action="store_true", help="skip the kernel-only numbers for 7/13/25/125-point")
     ap.add_argument("--all-stencils", action="store_true", help="(the default now; kept for old command lines)")
+    ap.add_argument("--no-4d", action="store_true", help="skip the 4-D block (drivers/weak4d on a 64^4 subdomain, N = 1 only)")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling block (1024^3 in 128^3, 125-point)")
     ap.add_argument("--dom", type=int, default=STRONG_DOM, help="strong workloads: global grid edge")
     ap.add_argument("--sdom", type=int, default=STRONG_SDOM, help="strong workloads: subdomain edge")
