@@ -16,6 +16,8 @@
 // gather_kernel (verification twin): one thread per point straight through the accessor arithmetic.
 // The bodies live in stencil4d_body.cuh, which also compiles as host code for a thread-by-thread emulation.
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 #include "stencil4d_body.cuh"
@@ -33,8 +35,35 @@ namespace {
 using s4::kNAdj;
 using s4::Sweep4;
 
-__global__ void __launch_bounds__(s4::kLineThreads, 3) line_kernel(const __grid_constant__ Sweep4 p) {
-  s4::line_body(p, blockIdx.x, threadIdx.x);
+/* LJ x LK lines per CTA; at 80 registers 768 threads fit an SM whatever the CTA size */
+template <int LJ, int LK, bool WIDE>
+__global__ void __launch_bounds__(64 * LJ * LK, 768 / (64 * LJ * LK)) line_kernel(const __grid_constant__ Sweep4 p) {
+  s4::line_body<LJ, LK, WIDE>(p, blockIdx.x, threadIdx.x);
+}
+
+struct LineVariant {
+  const char *name; /* "<LJ><LK><wide>" */
+  int lj, lk;
+  void (*fn)(const Sweep4);
+};
+const LineVariant kLineVariants[] = {
+    {"220", 2, 2, line_kernel<2, 2, false>}, {"221", 2, 2, line_kernel<2, 2, true>},
+    {"410", 4, 1, line_kernel<4, 1, false>}, {"411", 4, 1, line_kernel<4, 1, true>},
+    {"210", 2, 1, line_kernel<2, 1, false>}, {"211", 2, 1, line_kernel<2, 1, true>},
+    {"110", 1, 1, line_kernel<1, 1, false>}, {"111", 1, 1, line_kernel<1, 1, true>},
+};
+constexpr const char *kDefaultLineVariant = "221"; /* profiles/r03_4d/variants.log */
+
+/* BRICKS_4D_VARIANT=<LJ><LK><wide> picks another CTA shape / load width (experiments and tests) */
+const LineVariant *line_variant() {
+  static const LineVariant *chosen = [] {
+    const char *env = getenv("BRICKS_4D_VARIANT");
+    const char *want = env && *env ? env : kDefaultLineVariant;
+    for (const LineVariant &v : kLineVariants)
+      if (!strcmp(v.name, want)) return &v;
+    return (const LineVariant *)nullptr;
+  }();
+  return chosen;
 }
 
 __global__ void __launch_bounds__(256) gather_kernel(const __grid_constant__ Sweep4 p) {
@@ -131,15 +160,20 @@ int bricks_stencil4d(bricks_plan4d *plan, const double *in, double *out, size_t 
   if (int rc = fill_params(plan, in, out, in_step, out_step, skip_bricks, stream, &p, &empty)) return rc;
   if (empty) return 0;
   BRK_CUDA(cudaSetDevice(plan->ctx->device));
-  const unsigned long long nblocks = s4::line_blocks(&p);
+  const LineVariant *v = line_variant();
+  if (!v) {
+    bricks::set_error("BRICKS_4D_VARIANT=%s is not a built variant", getenv("BRICKS_4D_VARIANT"));
+    return -1;
+  }
+  const unsigned long long nblocks = s4::line_blocks(&p, v->lj, v->lk);
   BRK_ARG(nblocks < (1ull << 31));
   static std::atomic<unsigned> configured{0}; /* bit per device: all of L1 as cache (no shared memory used) */
   const unsigned bit = 1u << (plan->ctx->device & 31);
   if (!(configured.load() & bit)) {
-    BRK_CUDA(cudaFuncSetAttribute(line_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+    BRK_CUDA(cudaFuncSetAttribute(v->fn, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
     configured.fetch_or(bit);
   }
-  line_kernel<<<(unsigned)nblocks, s4::kLineThreads, 0, plan->ctx->streams[stream]>>>(p);
+  v->fn<<<(unsigned)nblocks, 64 * v->lj * v->lk, 0, plan->ctx->streams[stream]>>>(p);
   BRK_CUDA(cudaGetLastError());
   ++bricks::g_launches;
   return 0;

@@ -16,8 +16,6 @@
 namespace s4 {
 
 constexpr int kNAdj = 81;
-constexpr int kLJ = 2, kLK = 2; /* lines per CTA along j and k */
-constexpr int kLineThreads = 64 * kLJ * kLK;
 
 struct Sweep4 {
   const unsigned *grid; /* [n3][n2][n1][n0] */
@@ -50,10 +48,19 @@ S4_DEV double ld_f64(const double *p) {
 #endif
 }
 
-/* one 32-byte row as two 16-byte read-only loads */
+/* one 32-byte row through the read-only path.  WIDE: one 256-bit load (LDG.E.256), so that a warp's 32 rows
+ * are 8 full 128-byte lines per instruction; otherwise two 16-byte halves, each of which touches the same
+ * 8 lines and uses half of every sector (twice the L1 wavefronts: profiles/r03_4d/ncu_full_line4d_128.txt). */
+template <bool WIDE>
 S4_DEV Row load_row(const double *base, unsigned long long step, unsigned brick, int off) {
   const double *q = base + (size_t)brick * step + off;
 #ifdef __CUDA_ARCH__
+  if (WIDE) {
+    Row r;
+    /* not volatile: the input is read-only for the whole launch, the scheduler may move the load freely */
+    asm("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(r.v0), "=d"(r.v1), "=d"(r.v2), "=d"(r.v3) : "l"(q));
+    return r;
+  }
   const double2 *p = reinterpret_cast<const double2 *>(q);
   const double2 a = __ldg(p), b = __ldg(p + 1);
   return Row{a.x, a.y, b.x, b.y};
@@ -71,8 +78,11 @@ S4_DEV void store_row(double *p, double a, double b, double c, double d) {
 #endif
 }
 
-/* line_kernel: thread = one row position (l,k,j) of a line of bricks along the contiguous grid axis */
+/* line_kernel: thread = one row position (l,k,j) of a line of bricks along the contiguous grid axis; a CTA
+ * covers LJ x LK lines adjacent in j and k */
+template <int LJ, int LK, bool WIDE>
 S4_DEV void line_body(const Sweep4 &p, unsigned block, unsigned thread) {
+  constexpr int kLJ = LJ, kLK = LK;
   const unsigned r = thread & 63; /* row (l,k,j) inside the brick */
   const unsigned line = thread >> 6;
   unsigned bid = block;
@@ -103,7 +113,7 @@ S4_DEV void line_body(const Sweep4 &p, unsigned block, unsigned thread) {
   const unsigned *arow = p.adj + (size_t)b * kNAdj;
   unsigned aj = ld_u32(arow + sj), ak = ld_u32(arow + sk), al = ld_u32(arow + sl);
   unsigned a39 = ld_u32(arow + 39), a41 = ld_u32(arow + 41);
-  Row c = load_row(p.in, p.in_step, b, roff);
+  Row c = load_row<WIDE>(p.in, p.in_step, b, roff);
   double prev3 = ld_f64(p.in + (size_t)a39 * p.in_step + roff + 3);
 
   for (unsigned ti = lo;; ++ti) {
@@ -115,13 +125,13 @@ S4_DEV void line_body(const Sweep4 &p, unsigned block, unsigned thread) {
     const unsigned naj = ld_u32(nrow + sj), nak = ld_u32(nrow + sk), nal = ld_u32(nrow + sl);
     const unsigned na39 = ld_u32(nrow + 39), na41 = ld_u32(nrow + 41);
     /* the i+ neighbour's row: its first element is this step's halo, the whole row the next centre */
-    const Row nx = load_row(p.in, p.in_step, a41, roff);
-    const Row jm = load_row(p.in, p.in_step, j == 0 ? aj : b, o_jm);
-    const Row jp = load_row(p.in, p.in_step, j == 3 ? aj : b, o_jp);
-    const Row km = load_row(p.in, p.in_step, k == 0 ? ak : b, o_km);
-    const Row kp = load_row(p.in, p.in_step, k == 3 ? ak : b, o_kp);
-    const Row lm = load_row(p.in, p.in_step, l == 0 ? al : b, o_lm);
-    const Row lp = load_row(p.in, p.in_step, l == 3 ? al : b, o_lp);
+    const Row nx = load_row<WIDE>(p.in, p.in_step, a41, roff);
+    const Row jm = load_row<WIDE>(p.in, p.in_step, j == 0 ? aj : b, o_jm);
+    const Row jp = load_row<WIDE>(p.in, p.in_step, j == 3 ? aj : b, o_jp);
+    const Row km = load_row<WIDE>(p.in, p.in_step, k == 0 ? ak : b, o_km);
+    const Row kp = load_row<WIDE>(p.in, p.in_step, k == 3 ? ak : b, o_kp);
+    const Row lm = load_row<WIDE>(p.in, p.in_step, l == 0 ? al : b, o_lm);
+    const Row lp = load_row<WIDE>(p.in, p.in_step, l == 3 ? al : b, o_lp);
     /* term order of stencils/mpi9pt.py:17-26: centre, i+1, i-1, j+1, j-1, k+1, k-1, l+1, l-1 */
     double o0 = alpha * c.v0, o1 = alpha * c.v1, o2 = alpha * c.v2, o3 = alpha * c.v3;
     o0 += beta * c.v1, o1 += beta * c.v2, o2 += beta * c.v3, o3 += beta * nx.v0;
@@ -138,7 +148,7 @@ S4_DEV void line_body(const Sweep4 &p, unsigned block, unsigned thread) {
      * are already in registers.  Anything else (a grid that is not a lattice of adj) reloads them.  Both
      * tests are uniform over the 64 threads of a brick. */
     const double c3 = c.v3;
-    c = (bn == a41) ? nx : load_row(p.in, p.in_step, bn, roff);
+    c = (bn == a41) ? nx : load_row<WIDE>(p.in, p.in_step, bn, roff);
     prev3 = (na39 == b) ? c3 : ld_f64(p.in + (size_t)na39 * p.in_step + roff + 3);
     b = bn, aj = naj, ak = nak, al = nal, a39 = na39, a41 = na41;
   }
@@ -177,10 +187,10 @@ S4_DEV void gather_body(const Sweep4 &p, unsigned block, unsigned thread) {
 }
 
 /* launch shapes, shared by the launcher and the emulation */
-inline unsigned long long line_blocks(Sweep4 *p) {
+inline unsigned long long line_blocks(Sweep4 *p, int lj, int lk) {
   const unsigned w1 = p->n1 - 2 * p->s, w2 = p->n2 - 2 * p->s, w3 = p->n3 - 2 * p->s;
-  p->njg = (w1 + kLJ - 1) / kLJ;
-  p->nkg = (w2 + kLK - 1) / kLK;
+  p->njg = (w1 + lj - 1) / lj;
+  p->nkg = (w2 + lk - 1) / lk;
   return (unsigned long long)p->njg * p->nkg * w3;
 }
 inline unsigned long long gather_blocks(const Sweep4 &p) {

@@ -14,11 +14,18 @@ extern "C" int emul_stencil4d(int which, const unsigned *grid, const unsigned *g
   p.s = skip, p.njg = p.nkg = 0;
   for (int a = 0; a < 4; ++a)
     if (gdims[a] <= 2 * skip) return 0;
-  if (which == 0) {
-    const long long nb = (long long)s4::line_blocks(&p);
+  if (which == 0 || which >= 10) {
+    /* which = 0: the default shape; else <LJ><LK> in decimal (22, 41, 21, 11) */
+    const int lj = which ? which / 10 : 2, lk = which ? which % 10 : 2;
+    const long long nb = (long long)s4::line_blocks(&p, lj, lk);
 #pragma omp parallel for schedule(static)
     for (long long b = 0; b < nb; ++b)
-      for (unsigned t = 0; t < (unsigned)s4::kLineThreads; ++t) s4::line_body(p, (unsigned)b, t);
+      for (unsigned t = 0; t < (unsigned)(64 * lj * lk); ++t) {
+        if (lj == 2 && lk == 2) s4::line_body<2, 2, false>(p, (unsigned)b, t);
+        else if (lj == 4 && lk == 1) s4::line_body<4, 1, false>(p, (unsigned)b, t);
+        else if (lj == 2 && lk == 1) s4::line_body<2, 1, false>(p, (unsigned)b, t);
+        else s4::line_body<1, 1, false>(p, (unsigned)b, t);
+      }
   } else {
     const long long nb = (long long)s4::gather_blocks(p);
 #pragma omp parallel for schedule(static)

@@ -52,10 +52,10 @@ int main(int argc, char **argv) {
     s4::Sweep4 p;
     p.grid = grid, p.adj = &info.adj[0][0], p.in = in, p.out = out, p.in_step = p.out_step = 256;
     p.n0 = g[0], p.n1 = g[1], p.n2 = g[2], p.n3 = g[3], p.s = (unsigned)(skip / TILE);
-    const long long nb = (long long)s4::line_blocks(&p);
+    const long long nb = (long long)s4::line_blocks(&p, 2, 2);
 #pragma omp parallel for
     for (long long b = 0; b < nb; ++b)
-      for (unsigned t = 0; t < (unsigned)s4::kLineThreads; ++t) s4::line_body(p, (unsigned)b, t);
+      for (unsigned t = 0; t < 256; ++t) s4::line_body<2, 2, false>(p, (unsigned)b, t);
   };
   double *A = sa.dat.get(), *B = sb.dat.get();
   sweep(B, A, 0);

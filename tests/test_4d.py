@@ -200,7 +200,8 @@ def test_emulated_kernel_bodies_match_oracle_bit_for_bit(built, o4, emul, dims, 
     for s in (0, 1, 2, 3):
         exp = np.full(n, -7.0)
         o4.brick_sweep(dec.adj, o4.sweep_list(dec.grid, s), inp, exp)
-        for which in (0, 1):  # 0 = line_kernel (the product path), 1 = gather_kernel (the twin)
+        # 0 = line_kernel in its default CTA shape, 1 = gather_kernel (the twin), 41 / 21 / 11 = other shapes
+        for which in (0, 1, 41, 21, 11):
             got = np.full(n, -7.0)
             emul(which, dec.grid, dec.adj, inp, got, s)
             assert np.array_equal(got, exp), (s, which)
@@ -243,17 +244,24 @@ def test_driver_validation_pipeline_with_emulated_kernels(built, flag):
 
 
 # ---------------------------------------------------------------- the kernels on a B200 ----
-def _worker(what, *args, timeout=300):
+def _worker(what, *args, timeout=300, variant=None):
     cmd = [sys.executable, os.path.join(ROOT, "tests", "gpu4d_worker.py"), what] + [str(a) for a in args]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    env = dict(os.environ)
+    env.pop("BRICKS_4D_VARIANT", None)
+    if variant:
+        env["BRICKS_4D_VARIANT"] = variant
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=env)
     assert r.returncode == 0, "worker failed (rc %d):\n%s\n%s" % (r.returncode, r.stdout[-2000:], r.stderr[-4000:])
     line = [x for x in r.stdout.splitlines() if x.startswith("RESULT ")][-1]
     return json.loads(line[len("RESULT "):])
 
 
 @pytest.mark.gpu
-def test_gpu_4d_kernels_match_oracle(built):
-    res = _worker("parity")
+@pytest.mark.parametrize("variant", [None, "220", "211", "411", "111"])
+def test_gpu_4d_kernels_match_oracle(built, variant):
+    """None = the library's default (2 x 2 lines per CTA, 256-bit row loads); the others are the CTA shapes
+    and the 128-bit load width of profiles/r03_4d/variants.log, selected with BRICKS_4D_VARIANT"""
+    res = _worker("parity", variant=variant)
     assert len(res) == 3 * 4 * 2 + 4
     for r in res:
         assert r["relerr"] <= REL_TOL, r
