@@ -839,6 +839,33 @@ def end_to_end(ctx, sub, field, args, barrier, max_over_ranks, pts_step):
                     "download n-1 overlap the sweeps of n)"}
 
 
+def d4pt9_cpu_reference(dom=64, budget_s=4.0):
+    """The reference's generated mpi9pt.py kernel (AVX2, fold 2,2 -- what weak/main-4d.cpp builds on this host;
+    oracle/_ref/libref4d.so) under OpenMP on all host threads: full-grid sweeps over a dom^4 subdomain
+    (+ ghost bricks), in the build's own fold order as the reference times it."""
+    from oracle import oracle4d as D
+    if not D.ref_available():
+        raise RuntimeError("oracle/_ref/libref4d.so is not built for this host")
+    from oracle import refload as R
+    threads = use_all_host_threads()
+    dec = D.DecompND((dom,) * 4, page_align=False)
+    n = dec.nbricks * 256
+    a, b = R.aligned_empty(n), R.aligned_empty(n)
+    a[:] = synth_uniform(n, 1)
+    b[:] = 0.0
+    blist = D.sweep_list(dec.grid, 0)
+    t1 = D.ref_brick_sweep_timed(dec.adj, blist, a, b, 256, 2)
+    reps = int(max(2, min(200, budget_s / max(t1, 1e-4))))
+    reps += reps & 1
+    t = D.ref_brick_sweep_timed(dec.adj, blist, a, b, 256, reps)
+    pts = float(len(blist)) * 256
+    return {"full_grid_sweep_ms": t * 1e3, "gstencil_per_s_full_grid": pts / t * 1e-9, "cores": threads,
+            "kind": "reference",
+            "sample": "%d full-grid sweeps over one %d^4 subdomain (+ghost bricks: %d bricks), reference codegen "
+                      "kernel of stencils/mpi9pt.py (AVX2, fold 2,2) under OpenMP with %d threads" %
+                      (reps, dom, len(blist), threads)}
+
+
 def d4pt9_block(peak, dom=64, iters=10):
     """The 4-D path (weak/main-4d.cpp): drivers/weak4d -s 64 -v in a process of its own
     (plain C++ above the C ABI, no Python): one 64^4 subdomain (+ ghost: 20^4 bricks of 4x4x4x4, 328 MB per
@@ -856,7 +883,12 @@ def d4pt9_block(peak, dom=64, iters=10):
         if r.returncode != 0 or not (m_full and m_perf and m_par):
             return {"error": "drivers/weak4d rc %d" % r.returncode, "tail": (out + r.stderr)[-400:]}
         gbs = float(m_full.group(2))
-        return {"workload": "d4pt9: %d^4 subdomain per GPU, 4x4x4x4 bricks, ghost depth 8, 9-point star, exchange + 8 "
+        try:
+            cpu = d4pt9_cpu_reference(dom)
+            cpu["gpu_over_cpu_full_grid_sweep"] = cpu["full_grid_sweep_ms"] / float(m_full.group(1))
+        except Exception as e:  # noqa: BLE001
+            cpu = {"error": repr(e)}
+        return {"cpu_baseline": cpu, "workload": "d4pt9: %d^4 subdomain per GPU, 4x4x4x4 bricks, ghost depth 8, 9-point star, exchange + 8 "
                             "sweeps over shrinking regions (weak/main-4d.cpp)" % dom,
                 "parity": {"ok": m_par.group(1) == "result match", "max_relerr_vs_host_array_twin": float(m_par.group(2)),
                            "bar": 1e-12},
