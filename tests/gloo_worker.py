@@ -109,6 +109,27 @@ def strong(rank, world, outdir):
         np.save(os.path.join(outdir, "strong_out_%d.npy" % (plan.first_id + s)), out[s * per // 8:(s + 1) * per // 8])
 
 
+def weak4d(rank, world, outdir):
+    """the 4-D decomposition (weak/main-4d.cpp): 312 regions per rank on the process grid MPI_Dims_create
+    gives for 4 axes; region i is message i on both ends"""
+    import torch
+    import torch.distributed as dist
+    from bricklib_b200 import capi
+    dims = (16, 16, 16, 16)
+    procdims = capi.cart_dims(world, 4)
+    dec = capi.Decomp4D(dims, 8, False)
+    dec.rank_map(procdims, capi.cart_coords(rank, procdims))
+    ro, so, nb, rp, sp = dec.exchange_plan(256)
+    field = capi.uniform(dec.nbricks * 256, seed=700 + rank)
+    np.save(os.path.join(outdir, "weak4d_in_%d.npy" % rank), field)
+    buf = torch.from_numpy(field.view(np.uint8).copy())
+    n = len(ro)
+    _exchange_bytes(dist, torch, rank, buf,
+                    [(int(rp[i]), int(ro[i]), int(nb[i]), i) for i in range(n)],
+                    [(int(sp[i]), int(so[i]), int(nb[i]), i) for i in range(n)])
+    np.save(os.path.join(outdir, "weak4d_out_%d.npy" % rank), buf.numpy().view(np.float64))
+
+
 def main():
     rank, world, port, outdir = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4]
     import torch.distributed as dist
@@ -118,6 +139,8 @@ def main():
     shift(rank, world, outdir)
     dist.barrier()
     strong(rank, world, outdir)
+    dist.barrier()
+    weak4d(rank, world, outdir)
     dist.barrier()
     dist.destroy_process_group()
 

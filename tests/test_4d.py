@@ -159,6 +159,42 @@ def test_product_copy_brick4_and_exchange_plan(built, o4):
     dec.close()
 
 
+def test_oracle_exchange_assembles_the_periodic_global_field(o4):
+    """four virtual ranks on a (2,1,2,1) process grid: after the exchange every rank's storage, ghost bricks
+    included, equals its window of the periodic GLOBAL array -- the sign convention of populate()
+    (include/brick-mpi.h:730-753: "+d" is the neighbour at coordinate - 1) and the pairing of skin with ghost
+    regions, checked against something that is not a region table"""
+    dims, procdims, gz = (16, 16, 16, 16), (2, 1, 2, 1), 8
+    P = int(np.prod(procdims))
+    dec = o4.DecompND(dims, page_align=False)
+    # array axis a (0 = contiguous) belongs to direction-set axis a + 1, i.e. to Cartesian coordinate coo[3 - a]
+    pa = [procdims[3 - a] for a in range(4)]
+    glob = np.random.default_rng(8).random([dims[a] * pa[a] for a in range(4)][::-1])
+    ext = [d + 2 * gz for d in dims]
+    stores, where = [], []
+    for r in range(P):
+        coo, rr = [], r
+        for n in reversed(procdims):
+            coo.append(rr % n)
+            rr //= n
+        coo = coo[::-1]
+        blk = [(-coo[3 - a]) % pa[a] for a in range(4)]  # physical block of this rank along array axis a
+        where.append(blk)
+        own = glob[tuple(slice(blk[a] * dims[a], (blk[a] + 1) * dims[a]) for a in (3, 2, 1, 0))]
+        arr = np.zeros(ext[::-1])
+        arr[tuple(slice(gz, gz + dims[a]) for a in (3, 2, 1, 0))] = own
+        st = np.zeros(dec.nbricks * 256)
+        o4.copy_brick(True, dims, (0,) * 4, (gz,) * 4, arr, dec.grid, st)
+        stores.append(st)
+    o4.exchange(stores, dec, procdims)
+    for r in range(P):
+        back = np.zeros(ext[::-1])
+        o4.copy_brick(False, ext, (0,) * 4, (0,) * 4, back, dec.grid, stores[r])
+        idx = [(np.arange(-gz, dims[a] + gz) + where[r][a] * dims[a]) % (dims[a] * pa[a]) for a in range(4)]
+        want = glob[np.ix_(idx[3], idx[2], idx[1], idx[0])]
+        assert np.array_equal(back, want), r
+
+
 def test_plan4d_rejects_bad_arguments(built):
     with pytest.raises(built.BricksError):
         built.Decomp4D((16, 16, 18, 16))  # not a multiple of the brick edge

@@ -49,3 +49,14 @@ def test_two_rank_exchange_plans_over_gloo(built, oracle, tmp_path):
     for i in range(8):
         got = np.load(tmp_path / ("strong_out_%d.npy" % i))
         assert np.array_equal(got.view(np.uint64), sexp[i].view(np.uint64)), i
+
+    # 4-D (weak/main-4d.cpp): 2 ranks on the (2,1,1,1) grid, 312 regions each
+    from oracle import oracle4d as D
+    ddec = D.DecompND((16, 16, 16, 16), page_align=False)
+    dins = [np.load(tmp_path / ("weak4d_in_%d.npy" % r)) for r in range(world)]
+    dexp = [x.copy() for x in dins]
+    D.exchange(dexp, ddec, built.cart_dims(world, 4))
+    for r in range(world):
+        got = np.load(tmp_path / ("weak4d_out_%d.npy" % r))
+        assert np.array_equal(got.view(np.uint64), dexp[r].view(np.uint64)), r
+        assert not np.array_equal(got, dins[r])
