@@ -1,4 +1,4 @@
-"""The C++ drop-in drivers (drivers/{single,weak,strong}.cpp): they build from the host headers and
+"""The C++ drop-in drivers (drivers/{single,weak,strong,weak4d}.cpp): they build from the host headers and
 the C ABI alone, refuse to run without a GPU, and on a GPU validate themselves (-v) and print the
 reference's result lines (weak/main.cu:304-318, strong/main.cu:550-566)."""
 import os
@@ -13,7 +13,7 @@ BIN = os.path.join(ROOT, "drivers", "_build")
 
 @pytest.fixture(scope="module")
 def drivers(built):
-    have = all(os.path.exists(os.path.join(BIN, n)) for n in ("single", "weak", "strong"))
+    have = all(os.path.exists(os.path.join(BIN, n)) for n in ("single", "weak", "strong", "weak4d"))
     if not have or os.path.exists("/usr/bin/g++"):
         subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "drivers")])
     return BIN
@@ -25,7 +25,7 @@ def _run(path, *args, timeout=600):
 
 
 def test_drivers_build_without_cuda_headers(drivers):
-    for n in ("single", "weak", "strong"):
+    for n in ("single", "weak", "strong", "weak4d"):
         src = open(os.path.join(ROOT, "drivers", n + ".cpp")).read()
         assert "cuda_runtime" not in src and "<mpi.h>" not in src
         assert os.access(os.path.join(drivers, n), os.X_OK)
@@ -38,7 +38,8 @@ def test_drivers_refuse_to_run_without_a_gpu(drivers, built):
     n = ctypes.c_int()
     if built.lib().bricks_device_count(ctypes.byref(n)) == 0 and n.value > 0:
         pytest.skip("a GPU is present")
-    for n, args in (("single", ["-d", "32"]), ("weak", ["-s", "32", "-I", "1"]), ("strong", ["-d", "64", "-s", "32", "-I", "1"])):
+    for n, args in (("single", ["-d", "32"]), ("weak", ["-s", "32", "-I", "1"]), ("strong", ["-d", "64", "-s", "32", "-I", "1"]),
+                    ("weak4d", ["-s", "16", "-I", "1"])):
         rc, out = _run(os.path.join(drivers, n), *args)
         assert rc != 0 and "CUDA device" in out, (n, rc, out)
 
@@ -79,6 +80,20 @@ def test_weak_driver_validates_with_the_other_exchanges(drivers, flag):
     rc, out = _run(os.path.join(drivers, "weak"), "-s", "64,48,32", "-I", "3", "-S", "13", "-v", flag)
     assert rc == 0, out
     assert _perf(out) > 0 and "mismatch" not in out and "result match" in out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("args", (["-s", "32"], ["-s", "16,24,16,20", "-a"], ["-s", "20,20,28,16", "-t"]))
+def test_weak4d_driver_validates(drivers, args):
+    """the 4-D program (weak/main-4d.cpp): exchange + 8 shrinking sweeps against the host array twin; -a: the
+    page-aligned numbering, -t: the twin kernel"""
+    rc, out = _run(os.path.join(drivers, "weak4d"), *args, "-I", "3", "-v")
+    assert rc == 0, out
+    for key in ("d4pt9 on B200", "Bri: ", "calc ", "call ", "wait ", "  | MPI size (MB): ", "Total of 312 parts"):
+        assert key in out, out
+    assert _perf(out) > 0 and "mismatch" not in out
+    m = re.search(r"result match: max relative error vs the host array twin ([0-9.eE+-]+)", out)
+    assert m and float(m.group(1)) <= 1e-12, out
 
 
 @pytest.mark.gpu
