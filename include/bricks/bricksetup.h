@@ -100,14 +100,14 @@ inline void iter_grid(const std::vector<long> &dimlist, const std::vector<long> 
       base += (padding[a] + c * tile[a]) * strideA[a];
     }
     const unsigned b = grid_ptr[cell];
+    long x[dims];
+    for (unsigned a = 0; a < dims; ++a) x[a] = 0;
     for (long e = 0; e < nelem; ++e) {
-      long x[dims], r = e, off = 0;
-      for (unsigned a = 0; a < dims; ++a) {
-        x[a] = r % tile[a];
-        r /= tile[a];
-        off += x[a] * strideA[a];
-      }
+      long off = 0;
+      for (unsigned a = 0; a < dims; ++a) off += x[a] * strideA[a];
       f(bricks_detail::brick_element(brick, b, x), base + off);
+      unsigned a = 0;
+      while (a < dims && ++x[a] == tile[a]) x[a++] = 0;  // odometer, contiguous axis fastest
     }
   }
 }
