@@ -15,7 +15,6 @@
 // HBM-bound: 16 algorithmic bytes per point (8 read + 8 written), no shared memory, no barrier.
 // gather_kernel (verification twin): one thread per point straight through the accessor arithmetic.
 // The bodies live in stencil4d_body.cuh, which also compiles as host code for a thread-by-thread emulation.
-#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
