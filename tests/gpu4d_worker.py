@@ -68,6 +68,11 @@ def parity(ctx):
             got = run_sweep(ctx, plan, fn, inp, n, s)
             out.append({"dims": "permuted grid", "skip": s, "kernel": name, "relerr": relerr(got, exp),
                         "untouched_ok": bool(np.array_equal(got == SENTINEL, exp == SENTINEL)), "cells": plan.ncells(s)})
+    # a skip that leaves no brick: no launch, nothing written, no error
+    for name, fn in (("line", plan.sweep), ("naive", plan.sweep_naive)):
+        got = run_sweep(ctx, plan, fn, inp, n, 5)
+        out.append({"dims": "empty box", "skip": 5, "kernel": name, "relerr": 0.0,
+                    "untouched_ok": bool((got == SENTINEL).all()), "cells": plan.ncells(5)})
     plan.close()
     dec.close()
     return out

@@ -298,7 +298,8 @@ def test_gpu_4d_kernels_match_oracle(built, variant):
     """None = the library's default (2 x 2 lines per CTA, 256-bit row loads); the others are the CTA shapes
     and the 128-bit load width of profiles/r03_4d/variants.log, selected with BRICKS_4D_VARIANT"""
     res = _worker("parity", variant=variant)
-    assert len(res) == 3 * 4 * 2 + 4
+    assert len(res) == 3 * 4 * 2 + 4 + 2
+    assert res[-1]["cells"] == 0
     for r in res:
         assert r["relerr"] <= REL_TOL, r
         assert r["untouched_ok"], r
