@@ -164,3 +164,41 @@ def test_exchange_plan_matches_oracle_restatement(built, oracle):
             assert nb[i] == int(g["len"]) * 4096
             assert rp[i] == rm[int(g["neighbor"])] and sp[i] == rm[int(s["neighbor"])]
     d.close()
+
+
+def test_brickdecomp_random_shapes_against_the_compiled_reference(built, oracle):
+    """beyond the golden sizes: twelve random 3-D and ten random 4-D subdomain shapes (ghost depth of one to
+    three bricks, every skin order / both page settings), the product's numbering against the reference
+    itself where oracle/_ref is present (it travels to the GPU box); the 4-D shapes also against the oracle"""
+    from oracle import oracle4d as D4
+    from oracle import refload as R
+    rng = np.random.default_rng(2024)
+    for _ in range(12 if R.available() else 0):  # the oracle's 3-D restatement is pinned at the golden sizes only
+        gz = 8 * int(rng.integers(1, 4))
+        dims = tuple(int(2 * gz + 8 * rng.integers(0, 6)) for _ in range(3))
+        skin = int(rng.integers(0, 3))
+        mine = built.Decomp(dims, gz, skin)
+        ref = R.RefDecomp(dims, gz, skin)
+        assert mine.nbricks == ref.nbricks and list(mine.sep_pos) == list(ref.sep_pos), (dims, gz, skin)
+        assert np.array_equal(mine.grid, ref.grid) and np.array_equal(mine.adj[1:], ref.adj[1:]), (dims, gz, skin)
+        for name, tab in (("ghost", mine.ghost), ("skin", mine.skin)):
+            for k, v in ref.regions[name].items():
+                assert np.array_equal(tab[k].astype(np.uint64), v.astype(np.uint64)), (dims, gz, skin, name, k)
+        ref.close()
+        mine.close()
+    for _ in range(10):
+        gz = 4 * int(rng.integers(1, 4))
+        dims = tuple(int(2 * gz + 4 * rng.integers(0, 5)) for _ in range(4))
+        pa = bool(rng.integers(0, 2))
+        mine = built.Decomp4D(dims, gz, pa)
+        ref = D4.Ref4D(dims, gz=gz, page_align=pa) if D4.ref_available() else None
+        o = D4.DecompND(dims, depth=gz, page_align=pa)
+        assert mine.nbricks == o.nbricks and np.array_equal(mine.grid, o.grid) and np.array_equal(mine.adj, o.adj)
+        if ref is not None:
+            assert mine.nbricks == ref.nbricks and np.array_equal(mine.grid, ref.grid), (dims, gz, pa)
+            assert np.array_equal(mine.adj, ref.adj), (dims, gz, pa)
+            for name, tab in (("ghost", mine.ghost), ("skin", mine.skin)):
+                for k, v in ref.regions[name].items():
+                    assert np.array_equal(tab[k].astype(np.uint64), v.astype(np.uint64)), (dims, gz, pa, name, k)
+            ref.close()
+        mine.close()
