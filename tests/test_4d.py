@@ -263,11 +263,12 @@ def test_emulated_line_kernel_on_a_grid_that_is_not_a_lattice(built, o4, emul):
     dec.close()
 
 
-@pytest.mark.parametrize("flag", ["", "-a"])
+@pytest.mark.parametrize("flag", ["", "-a", "-P 4", "-P 6 -a"])
 def test_driver_validation_pipeline_with_emulated_kernels(built, flag):
     """tests/emul/weak4d_host_check.cpp: everything drivers/weak4d.cpp -v does on the host (decomposition,
     brick fill, the array twin of drivers/host_twin.h, compareBrick<4>) with the device calls replaced by the
-    emulated kernel bodies and the one-rank periodic exchange by skin -> ghost copies"""
+    emulated kernel bodies and the exchange by skin -> ghost copies between the emulated ranks of the periodic
+    process grid (-P 4: 2x2x1x1, -P 6: 3x2x1x1, where the two neighbours along an axis differ)"""
     out = os.path.join(ROOT, "tests", "emul", "_build")
     os.makedirs(out, exist_ok=True)
     exe = os.path.join(out, "weak4d_host_check")
@@ -275,8 +276,8 @@ def test_driver_validation_pipeline_with_emulated_kernels(built, flag):
     libdir = os.path.join(ROOT, "bricklib_b200", "lib")
     subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fopenmp", "-I" + os.path.join(ROOT, "include"), src, "-o", exe,
                            "-L" + libdir, "-lbricks_b200", "-Wl,-rpath," + libdir])
-    r = subprocess.run([exe] + ([flag] if flag else []), capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and "match 1" in r.stdout, r.stdout + r.stderr
+    r = subprocess.run([exe] + flag.split(), capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "match 1" in r.stdout and "match 0" not in r.stdout, r.stdout + r.stderr
 
 
 # ---------------------------------------------------------------- the kernels on a B200 ----
