@@ -894,6 +894,12 @@ def d4pt9_block(peak, dom=64, iters=10):
                            "bar": 1e-12},
                 "gstencil_per_s": float(m_perf.group(1)), "full_grid_sweep_ms": float(m_full.group(1)),
                 "achieved_gbs": gbs, "frac_of_measured_peak": gbs / peak if peak else None,
+                # SURVEY.md 8d counts interior points only: with ghost depth 8 around 64^4 the period's eight
+                # shrinking sweeps update 1.95 x the interior points (4 x 20^4 + 3 x 18^4 + 16^4 bricks)
+                "period_frac_interior": float(m_perf.group(1)) * 16.0 / peak if peak else None,
+                "definition": "frac_of_measured_peak = 16 B x every point of one full-grid sweep (20^4 bricks) / its "
+                              "time / peak; period_frac_interior = 16 B x interior GStencil/s of the whole period "
+                              "(exchange + 8 sweeps) / peak",
                 "algorithmic_bytes_per_point": 16, "kernel": "line_kernel (bricklib_b200/csrc/stencil4d.cu)"}
     except Exception as e:  # noqa: BLE001
         return {"error": repr(e)}
